@@ -1,0 +1,438 @@
+#!/usr/bin/env python
+"""bench.py — the measurement contract.
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload c2|c5|frame]
+
+Metric (BASELINE.json): Msamples/s (and ms/frame).  One sample = one evaluation of the per-pixel
+tracing path (Test.hlsl CSMain).  Workloads:
+
+  c2     BASELINE configs[1]: default scene, 1920x1080, 64 spp per step (jittered samples summed
+         in-kernel into the float4 accumulation buffer, then resolved to RGBA8).  DEFAULT at N=1.
+         At N>1 every rank renders a disjoint 64-sample range of the same frame per step (weak
+         scaling in spp); the per-rank accumulation buffers are merged with one NCCL reduce + one
+         resolve at the end of the K steps, INSIDE the timed total.
+  c5     BASELINE configs[4]: 3840x2160, 1024 spp per step split across the N ranks (strong
+         scaling), NCCL reduce + resolve every step.
+  frame  the literal reference frame: 1 spp, no jitter, RGBA8 store (Renderer.ComputeFrame).
+
+A "step" is one pass of the hot path over one frame.  `value` is device-timed (CUDA events on the
+launching stream, L2 flushed between timed steps, max over ranks); `e2e` goes through the C ABI
+with HOST buffers (device->pinned-host read of the image every step, wall clock, max over ranks).
+`--impl reference` times the CPU restatement of the reference kernel (oracle/, all host threads)
+on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+FLOP_PER_SAMPLE = 31.0          # 27 (miss) + 0.1472 * 27 (hit extra), algorithmic
+ACCUM_BYTES_PER_PIXEL = 32.0    # float4 read-modify-write per launch
+RGBA8_BYTES_PER_PIXEL = 4.0
+
+WORKLOADS = {
+    "c2": dict(width=1920, height=1080, spp=64, name="BASELINE configs[1]: default scene 1920x1080, 64 spp/step"),
+    "c5": dict(width=3840, height=2160, spp=1024, name="BASELINE configs[4]: default scene 3840x2160, 1024 spp/step"),
+    "frame": dict(width=1920, height=1080, spp=1, name="literal reference frame: 1920x1080, 1 spp, no jitter, RGBA8"),
+}
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return {"hbm_gbs": float(p["hbm_gbs"]), "sm_max_mhz": float(p.get("sm_max_mhz", 1965.0)), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.index)],
+                stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            for line in open(self.path):
+                f = [x.strip() for x in line.split(",")]
+                if len(f) < 9:
+                    continue
+                try:
+                    sm.append(float(f[1]))
+                    mx.append(float(f[2]))
+                except ValueError:
+                    continue
+                for n, v in zip(names, f[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            os.unlink(self.path)
+        except Exception:
+            pass
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), samples=len(sm))
+        out["reasons"] = sorted(reasons)
+        return out
+
+
+# ------------------------------------------------------------------------------------------------
+def cpu_sample(width, height, spp_sample, steps, warmup, jitter=True):
+    """Times the CPU oracle (the C restatement of Test.hlsl CSMain) with all host threads on
+    `spp_sample` samples per pixel of the workload's frame per step.  -> (Msamples/s, ms/step, threads)"""
+    import numpy as np
+    from oracle import pt_oracle as O
+    p = O.frame_params(width, height)
+    acc = np.zeros((height, width, 4), np.float32)
+    threads = O.max_threads()
+    first = 0
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        if jitter:
+            O.accumulate(p, first, spp_sample, 0, True, accum=acc)
+            O.resolve(acc, first + spp_sample)
+        else:
+            O.csmain_frame(p, want_f32=False, want_rgba8=True, want_hit=False)
+        dt = time.perf_counter() - t0
+        first += spp_sample
+        if i >= warmup:
+            times.append(dt)
+    total = sum(times)
+    msamples = width * height * spp_sample * len(times) / total / 1e6
+    return msamples, 1e3 * total / len(times), threads
+
+
+def cpu_model():
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except Exception:
+        pass
+    return "unknown"
+
+
+def run_reference(args):
+    """`--impl reference`: the reference's tracing logic on the box's host cores.  The reference's own
+    implementation is HLSL via Vulkan (cannot run: no graphics stack) hosted by C# (no dotnet), so this
+    is the oracle port, OpenMP over rows (the Parallel.For analogue), all threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    wl = WORKLOADS[args.workload]
+    W, H, spp = wl["width"], wl["height"], wl["spp"]
+    jitter = args.workload != "frame"
+    spp_sample = 1 if not jitter else max(1, min(spp, args.cpu_spp))
+    ms, ms_step, threads = cpu_sample(W, H, spp_sample, args.steps, args.warmup, jitter)
+    sample = (f"{W}x{H}, {spp_sample} of {spp} spp per step ({'jittered accumulate + resolve' if jitter else 'csmain frame'}), "
+              f"{args.steps} steps; Msamples/s is spp-invariant")
+    line = {
+        "impl": "reference", "metric": "Msamples/s", "value": ms, "unit": "Msamples/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl["name"], "cpu_model": cpu_model()},
+        "cpu_baseline": {"value": ms, "unit": "Msamples/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": ms, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from pathtracing_b200 import NativeTracer
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the B200 arm has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    wl = WORKLOADS[args.workload]
+    W, H, spp = wl["width"], wl["height"], wl["spp"]
+    n_pix = W * H
+    strong = args.workload == "c5"
+    literal = args.workload == "frame"
+    spp_rank = spp // world if strong else spp         # samples per pixel per rank per step
+    K, Wm = args.steps, args.warmup
+
+    stream = torch.cuda.Stream(device=dev)
+    accum = torch.zeros((H, W, 4), dtype=torch.float32, device=dev)
+    host_img = torch.empty((H, W, 4), dtype=torch.uint8).pin_memory()
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    t = NativeTracer(W, H, device=local, seed=0, stream=stream.cuda_stream)
+    t.set_accum_buffer(accum.data_ptr())
+    peaks = load_peaks()
+
+    def first_sample(step):
+        # disjoint, absolute sample indices: step-major, rank-minor
+        return (step * world + rank) * spp_rank
+
+    def merge_and_resolve(total_spp):
+        """NCCL reduce of the per-rank accumulation buffers over NVLink, resolve on rank 0."""
+        if world > 1:
+            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+            if rank != 0:
+                accum.zero_()          # root keeps the running total, the others the delta since the last merge
+        if rank == 0:
+            t.set_accum_spp(total_spp)
+            t.resolve()
+
+    def step_device(step):
+        if literal:
+            t.compute_frame()
+            return
+        t.render_samples(first_sample(step), spp_rank, jitter=True)
+        if strong:
+            merge_and_resolve((step + 1) * spp)
+        elif world == 1:
+            t.resolve()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with torch.cuda.stream(stream):
+        # ---- device-timed value -----------------------------------------------------------------
+        for s in range(Wm):
+            step_device(s)
+        barrier()
+        clocks = ClockSampler(local)
+        if rank == 0:
+            clocks.start()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K + 1)]
+        kern_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        launches0 = t.launch_count
+        barrier()
+        for s in range(K):
+            flush.fill_(s & 0xFF)                      # L2 flush between timed iterations (untimed)
+            ev[s][0].record(stream)
+            kern_ev[s][0].record(stream)
+            if literal:
+                t.compute_frame()
+            else:
+                t.render_samples(first_sample(Wm + s), spp_rank, jitter=True)
+            kern_ev[s][1].record(stream)
+            if not literal:
+                if strong:
+                    merge_and_resolve((Wm + s + 1) * spp)
+                elif world == 1:
+                    t.resolve()
+            ev[s][1].record(stream)
+        # c2 at N>1: one merge + resolve for the whole progressive render, timed
+        ev[K][0].record(stream)
+        if not literal and not strong and world > 1:
+            merge_and_resolve((Wm + K) * spp * world)
+        ev[K][1].record(stream)
+        barrier()
+        launches = t.launch_count - launches0
+        step_ms = [a.elapsed_time(b) for a, b in ev[:K]]
+        merge_ms = ev[K][0].elapsed_time(ev[K][1])
+        kern_ms = [a.elapsed_time(b) for a, b in kern_ev]
+        total_ms = sum(step_ms) + merge_ms
+        clk = clocks.stop() if rank == 0 else None
+
+        # ---- e2e: C ABI with host buffers ---------------------------------------------------------
+        def step_e2e(step):
+            if literal:
+                t.compute_frame()
+            else:
+                t.render_samples(first_sample(step), spp_rank, jitter=True)
+                if world > 1:
+                    merge_and_resolve((step + 1) * spp * (1 if strong else world))
+                else:
+                    t.resolve()
+            if rank == 0:
+                t._ck(t._lib.ptb_read_rgba8(t.handle, host_img.data_ptr(), W * 4))   # D2H into pinned host memory
+            else:
+                t.wait()
+        e2e_steps = max(3, min(K, 50))
+        for s in range(Wm):
+            step_e2e(2 * (Wm + K) + s)
+        barrier()
+        t0 = time.perf_counter()
+        for s in range(e2e_steps):
+            step_e2e(3 * (Wm + K) + s)
+        barrier()
+        e2e_s = time.perf_counter() - t0
+
+    # ---- the literal reference frame (1 spp, RGBA8) as a secondary line: HBM-write / launch bound ----
+    literal_frame = None
+    if rank == 0 and world == 1 and not literal:
+        with NativeTracer(W, H, device=local, stream=stream.cuda_stream) as tf, torch.cuda.stream(stream):
+            for _ in range(5):
+                tf.compute_frame()
+            torch.cuda.synchronize()
+            n_bb = 200
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            for _ in range(n_bb):
+                tf.compute_frame()
+            b.record(stream)
+            torch.cuda.synchronize()
+            bb_ms = a.elapsed_time(b) / n_bb
+            iso = []
+            for i in range(20):
+                flush.fill_(i)
+                a.record(stream)
+                tf.compute_frame()
+                b.record(stream)
+                torch.cuda.synchronize()
+                iso.append(a.elapsed_time(b))
+            iso_ms = statistics.median(iso)
+            bytes_frame = RGBA8_BYTES_PER_PIXEL * n_pix
+            literal_frame = {
+                "workload": WORKLOADS["frame"]["name"], "ms_per_frame_back_to_back": bb_ms,
+                "ms_per_frame_l2_flushed": iso_ms, "msamples_per_s_back_to_back": n_pix / (bb_ms * 1e-3) / 1e6,
+                "roofline": {"kernel": "csmain_frame_vec4", "bound": "hbm", "unit": "GB/s",
+                             "achieved": bytes_frame / (iso_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"],
+                             "frac": bytes_frame / (iso_ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
+                             "algorithmic_bytes_per_launch": bytes_frame,
+                             "note": "8.3 MB write per launch: ~1.3 us at the HBM roof, i.e. launch-latency scale"}}
+
+    tot = torch.tensor([total_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tot, op=dist.ReduceOp.MAX)
+    total_ms, e2e_ms = float(tot[0]), float(tot[1])
+
+    samples_per_step = n_pix * spp_rank * world            # all ranks
+    value = samples_per_step * K / (total_ms * 1e-3) / 1e6
+    e2e_value = samples_per_step * e2e_steps / (e2e_ms * 1e-3) / 1e6
+
+    if rank == 0:
+        # ---- roofline of the dominant kernel, from the live per-launch event durations -------------
+        k_ms = statistics.mean(kern_ms)
+        if literal:
+            alg = RGBA8_BYTES_PER_PIXEL * n_pix
+            achieved = alg / (k_ms * 1e-3) / 1e9
+            roof = {"kernel": "csmain_frame_vec4", "bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"],
+                    "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None,
+                    "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peaks['source']})",
+                    "algorithmic_bytes_per_launch": alg, "launch_ms": k_ms}
+        else:
+            fp32_peak = 148 * 128 * 2 * peaks["sm_max_mhz"] * 1e6 / 1e12     # TFLOP/s at max SM clock
+            flops = FLOP_PER_SAMPLE * n_pix * spp_rank
+            achieved = flops / (k_ms * 1e-3) / 1e12
+            roof = {"kernel": "csmain_accumulate", "bound": "fp32", "achieved": achieved, "peak": fp32_peak,
+                    "unit": "TFLOP/s", "frac": achieved / fp32_peak, "traffic": None,
+                    "peak_source": f"148 SM x 128 lanes x 2 x sm_max_mhz from MEASURED_PEAKS.json ({peaks['source']}); "
+                                   "FP32 CUDA-core issue bound, no tensor/HBM roof applies (SURVEY.md §8d)",
+                    "algorithmic_flops_per_launch": flops, "launch_ms": k_ms,
+                    "hbm_bytes_per_launch": ACCUM_BYTES_PER_PIXEL * n_pix,
+                    "hbm_frac": ACCUM_BYTES_PER_PIXEL * n_pix / (k_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]}
+        tr = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tr):
+            try:
+                roof["traffic"] = json.load(open(tr)).get(roof["kernel"])
+            except Exception:
+                pass
+
+        # ---- CPU baseline on this box's host cores (bounded sample) ----------------------------------
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            spp_s = 1 if literal else max(1, min(spp, args.cpu_spp))
+            ms, _, threads = cpu_sample(W, H, spp_s, 5, 1, jitter=not literal)
+            cpu = {"value": ms, "unit": "Msamples/s", "cores": threads, "kind": "port",
+                   "sample": f"{W}x{H}, {spp_s} of {spp} spp per step x 5 steps, OpenMP over rows, {cpu_model()}"}
+
+        d2h = n_pix * 4
+        line = {
+            "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": K, "warmup": Wm,
+            "ms_per_step": total_ms / K, "ms_per_frame": total_ms / K, "higher_is_better": True,
+            "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl["name"], "width": W, "height": H, "spp_per_step_per_rank": spp_rank,
+                       "spp_per_step_total": spp_rank * world, "seed": 0, "jitter": not literal,
+                       "sharding": ("none" if world == 1 else ("sample ranges, NCCL reduce+resolve every step" if strong else
+                                    "sample ranges, one NCCL reduce+resolve inside the timed total")),
+                       "l2": "flushed between timed steps (256 MB fill, untimed)",
+                       "timing": "per-step CUDA events on the launching stream, summed; max over ranks"},
+            "roofline": roof,
+            "cpu_baseline": cpu,
+            "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": 64, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps,
+                    "note": "C-ABI calls with host buffers; the path's only input is the parameter block "
+                            "(Test.hlsl reads nothing), output = RGBA8 frame read into pinned host memory each step"},
+            "gpu_launches": int(launches),
+            "clocks": {"sm_mhz": clk["sm_mhz"], "sm_max_mhz": clk["sm_max_mhz"], "reasons": clk["reasons"],
+                       "samples": clk["samples"]},
+            "merge_ms": merge_ms,
+            "literal_frame": literal_frame,
+        }
+        print(json.dumps(line))
+    t.destroy()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--cpu-spp", type=int, default=16, help="spp per step of the bounded CPU sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "b200":
+        args.warmup = 3           # timing rule: W >= 3
+    if args.impl == "reference":
+        return run_reference(args)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.gpus > 1 and world == 1:
+        # convenience: re-launch under torchrun, one rank per GPU
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", "29513", os.path.abspath(__file__)] + sys.argv[1:]
+        return subprocess.call(cmd)
+    return run_b200(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

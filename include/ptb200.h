@@ -1,0 +1,149 @@
+/*
+ * ptb200.h — C ABI of libptb200.so, the B200 (sm_100a) CUDA backend that stands where the
+ * reference's Vulkan compute pipeline stood.
+ *
+ * The reference has no FFI of its own for this path: the seam is the compute-pipeline
+ * contract inside RayTracing/Graphics/Renderer.cs.  Each entry point below
+ * cites the Renderer member (file:line under /root/reference/RayTracing/) it replaces.
+ * The C# binding a maintainer would add is shown in INTEGRATION.md and shipped as source in
+ * pathtracing_b200/cs/NativeTracer.cs.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every struct is blittable (P/Invoke / ctypes friendly);
+ *   - every call returns an int status: 0 = PTB_OK, negative = ptb_status; nothing throws or
+ *     aborts across the ABI (the reference throws `new Exception(string)` on any non-Success
+ *     Vk result, e.g. Renderer.cs:115-118; the C# wrapper rethrows from ptb_last_error);
+ *   - a context is externally synchronised (one host thread at a time, like the Vulkan
+ *     objects it replaces); distinct contexts may be used from distinct threads;
+ *   - launches are asynchronous on the context's stream; ptb_wait / ptb_read_* synchronise;
+ *   - there is NO CPU fallback: without a CUDA device ptb_create fails with PTB_ERR_CUDA.
+ */
+#ifndef PTB200_H
+#define PTB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PTB_ABI_VERSION 1
+
+typedef enum ptb_status {
+    PTB_OK = 0,
+    PTB_ERR_INVALID = -1,     /* bad argument (NULL, zero size, bad flags, pitch too small) */
+    PTB_ERR_CUDA = -2,        /* CUDA runtime error; text in ptb_last_error */
+    PTB_ERR_NOMEM = -3,       /* device or host allocation failed */
+    PTB_ERR_STATE = -4,       /* call not valid in the current state (e.g. resolve with 0 spp) */
+    PTB_ERR_UNSUPPORTED = -5  /* feature not built / size beyond limits */
+} ptb_status;
+
+typedef struct ptb_context ptb_context;   /* opaque; owns all device memory and its stream */
+
+/* ptb_config.flags */
+#define PTB_CFG_KEEP_F32      0x1u  /* ptb_compute_frame also stores the float4 image (Test.hlsl:1 RWTexture2D<float4>) */
+#define PTB_CFG_KEEP_HIT_IDS  0x2u  /* ptb_compute_frame also stores int32 hit ids (0 = sphere, -1 = miss) */
+#define PTB_CFG_EXTERNAL_STREAM 0x4u /* use `stream` (a cudaStream_t) instead of creating one */
+
+/* Parameters that are literals in the reference (Test.hlsl:6,8,12,13; App.cs:27).
+ * ptb_default_config fills them so that width=1920,height=1080 reproduces the reference. */
+typedef struct ptb_config {
+    uint32_t struct_size;       /* = sizeof(ptb_config); checked */
+    int32_t  device;            /* CUDA ordinal */
+    uint32_t width, height;     /* image size (Renderer.cs:128-129 Window.FramebufferSize) */
+    float    uv_div_x, uv_div_y;/* Test.hlsl:6 `resolution`; default (height,height) */
+    float    cam[3];            /* Test.hlsl:8 */
+    float    centre[3];         /* Test.hlsl:12 */
+    float    radius;            /* Test.hlsl:13 */
+    uint32_t seed;              /* RNG seed for jittered samples (no reference counterpart) */
+    uint32_t max_depth;         /* bounce limit for scene rendering; reference = 0 */
+    uint32_t flags;             /* PTB_CFG_* */
+    void    *stream;            /* cudaStream_t when PTB_CFG_EXTERNAL_STREAM */
+} ptb_config;
+
+/* Fill *cfg with the reference literals for a width x height image on device 0. */
+int ptb_default_config(ptb_config *cfg, uint32_t width, uint32_t height);
+
+/* Library / ABI version (PTB_ABI_VERSION of the built library). */
+int ptb_abi_version(void);
+
+/* Number of CUDA devices visible, or a negative ptb_status. */
+int ptb_device_count(void);
+
+/* ---- lifecycle -------------------------------------------------------------------------
+ * ptb_create  replaces Renderer.CreateResources (Renderer.cs:105-196: the W x H RGBA8 storage
+ *             image, its memory/view, layout transition) + Renderer.CreateComputePipeline
+ *             (Renderer.cs:293-403: descriptor layout, SPIR-V module, pipeline, ComputeFence).
+ * ptb_destroy replaces the compute part of Renderer.Dispose (Renderer.cs:1192-1216), and —
+ *             unlike the reference, which leaks its compute objects — frees everything.
+ *             ptb_destroy(NULL) is a no-op returning PTB_OK. */
+int ptb_create(const ptb_config *cfg, ptb_context **out_ctx);
+int ptb_destroy(ptb_context *ctx);
+
+/* UTF-8 text of the last error on this context (ctx == NULL: last ptb_create /
+ * argument error on the calling thread).  Never NULL; "" when no error. */
+const char *ptb_last_error(const ptb_context *ctx);
+
+/* ---- the per-frame hot path ------------------------------------------------------------
+ * ptb_compute_frame replaces Renderer.ComputeFrame (Renderer.cs:1006-1040): one launch of the
+ *             CSMain-equivalent kernel (Test.hlsl:3-40) over the whole image with an explicit
+ *             bounds guard (the reference over-dispatches 1920x1088 and relies on the API
+ *             dropping OOB writes).  Output: the context's RGBA8 UNORM image (the effective
+ *             store format, Renderer.cs:124), plus float4 / hit ids when configured.
+ * ptb_wait    replaces WaitForFences(ComputeFence, inf) (Renderer.cs:972). */
+int ptb_compute_frame(ptb_context *ctx);
+int ptb_wait(ptb_context *ctx);
+
+/* Headless consumers of the image (replace the fragment-stage sampling of ComputeImage,
+ * Renderer.cs:1086-1089).  pitch_bytes = host row stride; 0 means tightly packed.
+ * These synchronise the context's stream. */
+int ptb_read_rgba8(ptb_context *ctx, void *host_dst, size_t pitch_bytes);
+int ptb_read_f32(ptb_context *ctx, float *host_dst, size_t pitch_bytes);      /* needs KEEP_F32 */
+int ptb_read_hit_ids(ptb_context *ctx, int32_t *host_dst, size_t pitch_bytes);/* needs KEEP_HIT_IDS */
+
+/* Zero-copy access for device-side consumers (CUDA device pointers, valid until destroy). */
+void *ptb_device_rgba8(ptb_context *ctx);
+void *ptb_device_f32(ptb_context *ctx);
+void *ptb_device_accum(ptb_context *ctx);
+
+/* ---- multi-sample accumulation (north_star stages n1/n2; no reference counterpart) ------
+ * ptb_render_samples: for each pixel, samples s in [first_sample, first_sample+n_samples)
+ *   are evaluated in-kernel with sub-pixel jitter from the counter-based RNG keyed
+ *   (pixel, s, seed), summed sequentially, and the partial is added to the float4
+ *   accumulation buffer.  jitter == 0 evaluates the literal CSMain ray n_samples times.
+ * ptb_resolve: image = UNORM8(accum / spp_total) (flags: PTB_RESOLVE_*), written to the
+ *   context's RGBA8 image. */
+#define PTB_RESOLVE_SRGB 0x1u   /* apply the sRGB OETF (what a B8G8R8A8Srgb target does, SwapChain.cs:158) */
+#define PTB_RESOLVE_BGRA 0x2u   /* B,G,R,A byte order */
+int ptb_accum_reset(ptb_context *ctx);
+int ptb_render_samples(ptb_context *ctx, uint32_t first_sample, uint32_t n_samples, int jitter);
+int ptb_resolve(ptb_context *ctx, uint32_t flags);
+uint32_t ptb_accum_spp(const ptb_context *ctx);
+/* Checkpoint / restore of the progressive state (float4 accumulation + spp). */
+int ptb_read_accum(ptb_context *ctx, float *host_dst, size_t pitch_bytes);
+int ptb_write_accum(ptb_context *ctx, const float *host_src, size_t pitch_bytes, uint32_t spp_total);
+/* Use caller-owned device memory (W*H*4 floats, 16 B aligned) as the accumulation buffer,
+ * e.g. a buffer registered with a collective library.  NULL restores the internal one. */
+int ptb_set_accum_buffer(ptb_context *ctx, void *device_ptr);
+/* Override the spp count used by ptb_resolve after an external merge of accum buffers. */
+int ptb_set_accum_spp(ptb_context *ctx, uint32_t spp_total);
+
+/* ---- present-equivalent -----------------------------------------------
+ * ptb_present replaces the full-screen-quad draw (Renderer.cs:1079-1091) + PSMain
+ *   (PixelShader.hlsl:8-19): nearest/repeat sampling of the RGBA8 image onto a dst_w x dst_h
+ *   BGRA8 target (SwapChain.cs:154-165), optional sRGB OETF (PTB_RESOLVE_SRGB).  Headless. */
+int ptb_present(ptb_context *ctx, uint32_t dst_w, uint32_t dst_h, uint32_t flags);
+int ptb_read_present(ptb_context *ctx, void *host_dst, size_t pitch_bytes);
+
+/* ---- measurement -----------------------------------------------------------------------
+ * CUDA-event timing on the context's own stream (torch.cuda.Event only sees torch's stream). */
+int ptb_timer_begin(ptb_context *ctx);
+int ptb_timer_end(ptb_context *ctx, float *elapsed_ms);     /* synchronises */
+/* Kernels launched by this context since creation (for bench.py's gpu_launches). */
+uint64_t ptb_launch_count(const ptb_context *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PTB200_H */

@@ -1,0 +1,377 @@
+// api.cu — the extern "C" boundary of libptb200.so (include/ptb200.h).
+// Each entry point names the reference member it replaces in the header; this file only does
+// argument checking, resource ownership and stream/event plumbing around the kernel launchers.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include "ptb_internal.h"
+
+namespace {
+
+thread_local std::string g_err;   // errors with no context to hang them on
+
+int fail(ptb_context *ctx, int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->err = buf;
+    else g_err = buf;
+    return code;
+}
+
+int cuda_fail(ptb_context *ctx, cudaError_t e, const char *what)
+{
+    return fail(ctx, e == cudaErrorMemoryAllocation ? PTB_ERR_NOMEM : PTB_ERR_CUDA, "%s: %s (%s)", what,
+                cudaGetErrorString(e), cudaGetErrorName(e));
+}
+
+#define PTB_CUDA(ctx, call)                                        \
+    do {                                                           \
+        cudaError_t e__ = (call);                                  \
+        if (e__ != cudaSuccess) return cuda_fail(ctx, e__, #call); \
+    } while (0)
+
+// Every entry point makes the context's device current (contexts on different devices may be
+// interleaved on one host thread).
+#define PTB_ENTER(ctx)                                                    \
+    do {                                                                  \
+        if (!(ctx)) return fail(nullptr, PTB_ERR_INVALID, "%s: ctx is NULL", __func__); \
+        PTB_CUDA(ctx, cudaSetDevice((ctx)->cfg.device));                  \
+    } while (0)
+
+size_t n_pixels(const ptb_context *c) { return (size_t)c->cfg.width * c->cfg.height; }
+
+void free_buffers(ptb_context *c)
+{
+    cudaFree(c->buf.rgba8);
+    cudaFree(c->buf.f32);
+    cudaFree(c->buf.hit);
+    cudaFree(c->buf.accum_owned);
+    cudaFree(c->buf.present);
+    c->buf = ptb::Buffers{};
+}
+
+int read_rows(ptb_context *ctx, void *host_dst, size_t pitch, const void *dev, size_t row_bytes, size_t rows)
+{
+    if (!host_dst) return fail(ctx, PTB_ERR_INVALID, "host destination is NULL");
+    if (pitch == 0) pitch = row_bytes;
+    if (pitch < row_bytes) return fail(ctx, PTB_ERR_INVALID, "pitch %zu < row size %zu", pitch, row_bytes);
+    PTB_CUDA(ctx, cudaMemcpy2DAsync(host_dst, pitch, dev, row_bytes, row_bytes, rows, cudaMemcpyDeviceToHost,
+                                    ctx->stream));
+    PTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return PTB_OK;
+}
+
+}  // namespace
+
+namespace ptb {
+void scene_destroy(ptb_context *ctx);   // scene.cu
+}
+
+extern "C" {
+
+int ptb_abi_version(void) { return PTB_ABI_VERSION; }
+
+int ptb_device_count(void)
+{
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) return cuda_fail(nullptr, e, "cudaGetDeviceCount");
+    return n;
+}
+
+int ptb_default_config(ptb_config *cfg, uint32_t width, uint32_t height)
+{
+    if (!cfg) return fail(nullptr, PTB_ERR_INVALID, "ptb_default_config: cfg is NULL");
+    std::memset(cfg, 0, sizeof *cfg);
+    cfg->struct_size = (uint32_t)sizeof *cfg;
+    cfg->device = 0;
+    cfg->width = width;
+    cfg->height = height;
+    cfg->uv_div_x = (float)height;   // Test.hlsl:6 uses 1080 on both axes of a 1920x1080 image
+    cfg->uv_div_y = (float)height;
+    cfg->cam[2] = 1.0f;              // Test.hlsl:8
+    cfg->radius = 0.5f;              // Test.hlsl:13 (centre (0,0,0), :12)
+    return PTB_OK;
+}
+
+int ptb_create(const ptb_config *cfg, ptb_context **out_ctx)
+{
+    if (out_ctx) *out_ctx = nullptr;
+    if (!cfg || !out_ctx) return fail(nullptr, PTB_ERR_INVALID, "ptb_create: NULL argument");
+    if (cfg->struct_size != sizeof(ptb_config))
+        return fail(nullptr, PTB_ERR_INVALID, "ptb_create: struct_size %u != %zu (ABI mismatch)", cfg->struct_size,
+                    sizeof(ptb_config));
+    if (cfg->width == 0 || cfg->height == 0)
+        return fail(nullptr, PTB_ERR_INVALID, "ptb_create: empty image %ux%u", cfg->width, cfg->height);
+    if ((uint64_t)cfg->width * cfg->height > (1ull << 30))
+        return fail(nullptr, PTB_ERR_UNSUPPORTED, "ptb_create: %ux%u exceeds 2^30 pixels", cfg->width, cfg->height);
+    if (!(cfg->uv_div_x != 0.0f) || !(cfg->uv_div_y != 0.0f))
+        return fail(nullptr, PTB_ERR_INVALID, "ptb_create: uv divisor must be non-zero");
+    if (cfg->flags & ~(PTB_CFG_KEEP_F32 | PTB_CFG_KEEP_HIT_IDS | PTB_CFG_EXTERNAL_STREAM))
+        return fail(nullptr, PTB_ERR_INVALID, "ptb_create: unknown flags 0x%x", cfg->flags);
+
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess) return cuda_fail(nullptr, e, "ptb_create: no usable CUDA driver/device (no CPU fallback)");
+    if (cfg->device < 0 || cfg->device >= ndev)
+        return fail(nullptr, PTB_ERR_INVALID, "ptb_create: device %d out of range [0,%d)", cfg->device, ndev);
+    e = cudaSetDevice(cfg->device);
+    if (e != cudaSuccess) return cuda_fail(nullptr, e, "cudaSetDevice");
+
+    ptb_context *c = new (std::nothrow) ptb_context();
+    if (!c) return fail(nullptr, PTB_ERR_NOMEM, "ptb_create: host allocation failed");
+    c->cfg = *cfg;
+    c->k.width = cfg->width;
+    c->k.height = cfg->height;
+    c->k.div_x = cfg->uv_div_x;
+    c->k.div_y = cfg->uv_div_y;
+    for (int i = 0; i < 3; ++i) {
+        c->k.cam[i] = cfg->cam[i];
+        c->k.centre[i] = cfg->centre[i];
+    }
+    c->k.radius = cfg->radius;
+
+    auto bail = [&](cudaError_t err, const char *what) {
+        int rc = cuda_fail(nullptr, err, what);
+        ptb_destroy(c);
+        return rc;
+    };
+    if (cfg->flags & PTB_CFG_EXTERNAL_STREAM) {
+        c->stream = (cudaStream_t)cfg->stream;
+    } else {
+        if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess)
+            return bail(e, "cudaStreamCreate");
+        c->own_stream = true;
+    }
+    if ((e = cudaEventCreate(&c->ev0)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    if ((e = cudaEventCreate(&c->ev1)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    if ((e = ptb::image_tables_init()) != cudaSuccess) return bail(e, "image_tables_init");
+
+    const size_t n = n_pixels(c);
+    // ≙ CreateResources (Renderer.cs:120-179): the W x H RGBA8 storage image.
+    if ((e = cudaMalloc(&c->buf.rgba8, n * 4)) != cudaSuccess) return bail(e, "cudaMalloc(rgba8)");
+    if (cfg->flags & PTB_CFG_KEEP_F32)
+        if ((e = cudaMalloc(&c->buf.f32, n * sizeof(float4))) != cudaSuccess) return bail(e, "cudaMalloc(f32)");
+    if (cfg->flags & PTB_CFG_KEEP_HIT_IDS)
+        if ((e = cudaMalloc(&c->buf.hit, n * sizeof(int32_t))) != cudaSuccess) return bail(e, "cudaMalloc(hit)");
+    *out_ctx = c;
+    return PTB_OK;
+}
+
+int ptb_destroy(ptb_context *ctx)
+{
+    if (!ctx) return PTB_OK;
+    cudaSetDevice(ctx->cfg.device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    ptb::scene_destroy(ctx);
+    free_buffers(ctx);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return PTB_OK;
+}
+
+const char *ptb_last_error(const ptb_context *ctx) { return ctx ? ctx->err.c_str() : g_err.c_str(); }
+
+int ptb_compute_frame(ptb_context *ctx)
+{
+    PTB_ENTER(ctx);
+    PTB_CUDA(ctx, ptb::launch_csmain_frame(ctx->k, ctx->buf, ctx->stream));
+    ctx->launches += 1;
+    return PTB_OK;
+}
+
+int ptb_wait(ptb_context *ctx)
+{
+    PTB_ENTER(ctx);
+    PTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return PTB_OK;
+}
+
+int ptb_read_rgba8(ptb_context *ctx, void *host_dst, size_t pitch_bytes)
+{
+    PTB_ENTER(ctx);
+    return read_rows(ctx, host_dst, pitch_bytes, ctx->buf.rgba8, (size_t)ctx->cfg.width * 4, ctx->cfg.height);
+}
+
+int ptb_read_f32(ptb_context *ctx, float *host_dst, size_t pitch_bytes)
+{
+    PTB_ENTER(ctx);
+    if (!ctx->buf.f32) return fail(ctx, PTB_ERR_STATE, "ptb_read_f32: context created without PTB_CFG_KEEP_F32");
+    return read_rows(ctx, host_dst, pitch_bytes, ctx->buf.f32, (size_t)ctx->cfg.width * 16, ctx->cfg.height);
+}
+
+int ptb_read_hit_ids(ptb_context *ctx, int32_t *host_dst, size_t pitch_bytes)
+{
+    PTB_ENTER(ctx);
+    if (!ctx->buf.hit) return fail(ctx, PTB_ERR_STATE, "ptb_read_hit_ids: context created without PTB_CFG_KEEP_HIT_IDS");
+    return read_rows(ctx, host_dst, pitch_bytes, ctx->buf.hit, (size_t)ctx->cfg.width * 4, ctx->cfg.height);
+}
+
+void *ptb_device_rgba8(ptb_context *ctx) { return ctx ? ctx->buf.rgba8 : nullptr; }
+void *ptb_device_f32(ptb_context *ctx) { return ctx ? ctx->buf.f32 : nullptr; }
+
+static int ensure_accum(ptb_context *ctx)
+{
+    if (ctx->buf.accum) return PTB_OK;
+    const size_t bytes = n_pixels(ctx) * sizeof(float4);
+    PTB_CUDA(ctx, cudaMalloc(&ctx->buf.accum_owned, bytes));
+    ctx->buf.accum = ctx->buf.accum_owned;
+    PTB_CUDA(ctx, cudaMemsetAsync(ctx->buf.accum, 0, bytes, ctx->stream));
+    ctx->accum_spp = 0;
+    return PTB_OK;
+}
+
+void *ptb_device_accum(ptb_context *ctx)
+{
+    if (!ctx) return nullptr;
+    if (cudaSetDevice(ctx->cfg.device) != cudaSuccess) return nullptr;
+    if (ensure_accum(ctx) != PTB_OK) return nullptr;
+    return ctx->buf.accum;
+}
+
+int ptb_accum_reset(ptb_context *ctx)
+{
+    PTB_ENTER(ctx);
+    int rc = ensure_accum(ctx);
+    if (rc != PTB_OK) return rc;
+    PTB_CUDA(ctx, cudaMemsetAsync(ctx->buf.accum, 0, n_pixels(ctx) * sizeof(float4), ctx->stream));
+    ctx->accum_spp = 0;
+    return PTB_OK;
+}
+
+int ptb_render_samples(ptb_context *ctx, uint32_t first_sample, uint32_t n_samples, int jitter)
+{
+    PTB_ENTER(ctx);
+    if (n_samples == 0) return PTB_OK;
+    if ((uint64_t)ctx->accum_spp + n_samples > 0xFFFFFFFFull)
+        return fail(ctx, PTB_ERR_INVALID, "ptb_render_samples: spp counter would overflow");
+    int rc = ensure_accum(ctx);
+    if (rc != PTB_OK) return rc;
+    PTB_CUDA(ctx, ptb::launch_csmain_accumulate(ctx->k, ctx->buf.accum, first_sample, n_samples, ctx->cfg.seed,
+                                                jitter != 0, ctx->stream));
+    ctx->launches += 1;
+    ctx->accum_spp += n_samples;
+    return PTB_OK;
+}
+
+int ptb_resolve(ptb_context *ctx, uint32_t flags)
+{
+    PTB_ENTER(ctx);
+    if (flags & ~(PTB_RESOLVE_SRGB | PTB_RESOLVE_BGRA)) return fail(ctx, PTB_ERR_INVALID, "ptb_resolve: unknown flags 0x%x", flags);
+    if (!ctx->buf.accum || ctx->accum_spp == 0)
+        return fail(ctx, PTB_ERR_STATE, "ptb_resolve: nothing accumulated (0 spp)");
+    PTB_CUDA(ctx, ptb::launch_resolve(ctx->buf.accum, ctx->buf.rgba8, (uint32_t)n_pixels(ctx), ctx->accum_spp, flags,
+                                      ctx->stream));
+    ctx->launches += 1;
+    return PTB_OK;
+}
+
+uint32_t ptb_accum_spp(const ptb_context *ctx) { return ctx ? ctx->accum_spp : 0; }
+
+int ptb_read_accum(ptb_context *ctx, float *host_dst, size_t pitch_bytes)
+{
+    PTB_ENTER(ctx);
+    if (!ctx->buf.accum) return fail(ctx, PTB_ERR_STATE, "ptb_read_accum: no accumulation buffer yet");
+    return read_rows(ctx, host_dst, pitch_bytes, ctx->buf.accum, (size_t)ctx->cfg.width * 16, ctx->cfg.height);
+}
+
+int ptb_write_accum(ptb_context *ctx, const float *host_src, size_t pitch_bytes, uint32_t spp_total)
+{
+    PTB_ENTER(ctx);
+    if (!host_src) return fail(ctx, PTB_ERR_INVALID, "ptb_write_accum: host_src is NULL");
+    const size_t row = (size_t)ctx->cfg.width * 16;
+    if (pitch_bytes == 0) pitch_bytes = row;
+    if (pitch_bytes < row) return fail(ctx, PTB_ERR_INVALID, "ptb_write_accum: pitch %zu < row size %zu", pitch_bytes, row);
+    int rc = ensure_accum(ctx);
+    if (rc != PTB_OK) return rc;
+    PTB_CUDA(ctx, cudaMemcpy2DAsync(ctx->buf.accum, row, host_src, pitch_bytes, row, ctx->cfg.height,
+                                    cudaMemcpyHostToDevice, ctx->stream));
+    PTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->accum_spp = spp_total;
+    return PTB_OK;
+}
+
+int ptb_set_accum_buffer(ptb_context *ctx, void *device_ptr)
+{
+    PTB_ENTER(ctx);
+    if (device_ptr) {
+        if ((uintptr_t)device_ptr & 15u) return fail(ctx, PTB_ERR_INVALID, "ptb_set_accum_buffer: pointer not 16 B aligned");
+        cudaPointerAttributes attr{};
+        PTB_CUDA(ctx, cudaPointerGetAttributes(&attr, device_ptr));
+        if (attr.type != cudaMemoryTypeDevice && attr.type != cudaMemoryTypeManaged)
+            return fail(ctx, PTB_ERR_INVALID, "ptb_set_accum_buffer: not a device pointer");
+        ctx->buf.accum = static_cast<float4 *>(device_ptr);
+    } else {
+        ctx->buf.accum = ctx->buf.accum_owned;   // may be NULL: allocated lazily again
+    }
+    ctx->accum_spp = 0;
+    return PTB_OK;
+}
+
+int ptb_set_accum_spp(ptb_context *ctx, uint32_t spp_total)
+{
+    PTB_ENTER(ctx);
+    ctx->accum_spp = spp_total;
+    return PTB_OK;
+}
+
+int ptb_present(ptb_context *ctx, uint32_t dst_w, uint32_t dst_h, uint32_t flags)
+{
+    PTB_ENTER(ctx);
+    if (dst_w == 0 || dst_h == 0) return fail(ctx, PTB_ERR_INVALID, "ptb_present: empty target");
+    if (flags & ~PTB_RESOLVE_SRGB) return fail(ctx, PTB_ERR_INVALID, "ptb_present: unknown flags 0x%x", flags);
+    if ((uint64_t)dst_w * dst_h > (1ull << 30)) return fail(ctx, PTB_ERR_UNSUPPORTED, "ptb_present: target too large");
+    const size_t need = (size_t)dst_w * dst_h * 4;
+    if (need > ctx->buf.present_cap) {
+        cudaFree(ctx->buf.present);
+        ctx->buf.present = nullptr;
+        ctx->buf.present_cap = 0;
+        PTB_CUDA(ctx, cudaMalloc(&ctx->buf.present, need));
+        ctx->buf.present_cap = need;
+    }
+    ctx->buf.present_w = dst_w;
+    ctx->buf.present_h = dst_h;
+    PTB_CUDA(ctx, ptb::launch_present(ctx->buf.rgba8, ctx->cfg.width, ctx->cfg.height, ctx->buf.present, dst_w, dst_h,
+                                      flags, ctx->stream));
+    ctx->launches += 1;
+    return PTB_OK;
+}
+
+int ptb_read_present(ptb_context *ctx, void *host_dst, size_t pitch_bytes)
+{
+    PTB_ENTER(ctx);
+    if (!ctx->buf.present || ctx->buf.present_w == 0) return fail(ctx, PTB_ERR_STATE, "ptb_read_present: ptb_present not called");
+    return read_rows(ctx, host_dst, pitch_bytes, ctx->buf.present, (size_t)ctx->buf.present_w * 4, ctx->buf.present_h);
+}
+
+int ptb_timer_begin(ptb_context *ctx)
+{
+    PTB_ENTER(ctx);
+    PTB_CUDA(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    ctx->timer_open = true;
+    return PTB_OK;
+}
+
+int ptb_timer_end(ptb_context *ctx, float *elapsed_ms)
+{
+    PTB_ENTER(ctx);
+    if (!elapsed_ms) return fail(ctx, PTB_ERR_INVALID, "ptb_timer_end: elapsed_ms is NULL");
+    if (!ctx->timer_open) return fail(ctx, PTB_ERR_STATE, "ptb_timer_end without ptb_timer_begin");
+    PTB_CUDA(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    PTB_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
+    PTB_CUDA(ctx, cudaEventElapsedTime(elapsed_ms, ctx->ev0, ctx->ev1));
+    ctx->timer_open = false;
+    return PTB_OK;
+}
+
+uint64_t ptb_launch_count(const ptb_context *ctx) { return ctx ? ctx->launches : 0; }
+
+}  // extern "C"

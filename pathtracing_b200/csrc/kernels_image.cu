@@ -1,0 +1,142 @@
+// kernels_image.cu — resolve ("tonemap") and present-equivalent kernels (HBM-bound byte work).
+//
+//   resolve : accum float4 / spp -> UNORM8 (optional sRGB OETF, optional BGRA order).
+//             The UNORM8 clamp is what the reference's R8G8B8A8Unorm storage image implies
+//             (RayTracing/Graphics/Renderer.cs:124); the OETF is what its preferred
+//             B8G8R8A8Srgb swapchain format applies on write (Graphics/SwapChain.cs:154-165).
+//   present : the arithmetic of the full-screen quad + PSMain
+//             (Assets/Shaders/Source/Basic/PixelShader.hlsl:8-19; sampler nearest/repeat,
+//             Renderer.cs:181-191; quad uv without flip, Renderer.cs:45-56) as a headless copy.
+#include <cmath>
+#include <mutex>
+
+#include "ptb_internal.h"
+#include "ptb_math.cuh"
+
+namespace ptb {
+
+// c_srgb_thresh[k] (k = 1..255) = smallest float whose sRGB-encoded UNORM8 value is >= k;
+// encode(v) = #{k : v >= thresh[k]}.  c_srgb_lut8[i] = encode(i/255) for 8-bit sources.
+__constant__ float c_srgb_thresh[256];
+__constant__ uint8_t c_srgb_lut8[256];
+
+static double srgb_eotf(double e) { return e <= 0.04045 ? e / 12.92 : std::pow((e + 0.055) / 1.055, 2.4); }
+
+cudaError_t image_tables_init()
+{
+    float thresh[256];
+    uint8_t lut[256];
+    thresh[0] = 0.0f;
+    for (int k = 1; k < 256; ++k) {
+        const double b = srgb_eotf((k - 0.5) / 255.0);   // linear value where the code flips to k
+        float f = (float)b;
+        if ((double)f < b) f = std::nextafterf(f, 2.0f);
+        thresh[k] = f;
+    }
+    for (int i = 0; i < 256; ++i) {
+        const float v = (float)i / 255.0f;
+        int code = 0;
+        for (int k = 1; k < 256; ++k) code += (v >= thresh[k]);
+        lut[i] = (uint8_t)code;
+    }
+    cudaError_t e = cudaMemcpyToSymbol(c_srgb_thresh, thresh, sizeof thresh);
+    if (e != cudaSuccess) return e;
+    return cudaMemcpyToSymbol(c_srgb_lut8, lut, sizeof lut);
+}
+
+// Branch-free 8-step binary search over the (shared-memory copy of the) threshold table.
+__device__ __forceinline__ uint32_t srgb8_from_linear(const float *__restrict__ th, float v)
+{
+    if (!(v > 0.0f)) return 0u;   // NaN and negatives
+    uint32_t lo = 0;              // invariant: v >= th[lo] (th[0] = 0)
+#pragma unroll
+    for (uint32_t step = 128; step > 0; step >>= 1) {
+        const uint32_t mid = lo + step;   // <= 255
+        lo = (v >= th[mid]) ? mid : lo;
+    }
+    return lo;
+}
+
+template <bool SRGB, bool BGRA>
+__global__ void __launch_bounds__(256) resolve_kernel(const float4 *__restrict__ accum,
+                                                      uint32_t *__restrict__ out8, uint32_t n_pixels,
+                                                      float spp)
+{
+    __shared__ float th[256];
+    if (SRGB) {
+        th[threadIdx.x] = c_srgb_thresh[threadIdx.x];
+        __syncthreads();
+    }
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_pixels; i += stride) {
+        const float4 a = __ldcs(accum + i);   // streamed once: evict-first
+        const float r = fdiv(a.x, spp), g = fdiv(a.y, spp), b = fdiv(a.z, spp), al = fdiv(a.w, spp);
+        uint32_t r8, g8, b8;
+        if (SRGB) {
+            r8 = srgb8_from_linear(th, r);
+            g8 = srgb8_from_linear(th, g);
+            b8 = srgb8_from_linear(th, b);
+        } else {
+            r8 = unorm8(r);
+            g8 = unorm8(g);
+            b8 = unorm8(b);
+        }
+        const uint32_t a8 = unorm8(al);
+        out8[i] = BGRA ? (b8 | (g8 << 8) | (r8 << 16) | (a8 << 24)) : (r8 | (g8 << 8) | (b8 << 16) | (a8 << 24));
+    }
+}
+
+cudaError_t launch_resolve(const float4 *accum, uint32_t *out8, uint32_t n_pixels, uint32_t spp_total,
+                           uint32_t flags, cudaStream_t s)
+{
+    const int block = 256;
+    int grid = (int)((n_pixels + block - 1) / block);
+    const int cap = 148 * 8 * 4;   // a few waves of resident CTAs; grid-stride beyond that
+    if (grid > cap) grid = cap;
+    const float spp = (float)spp_total;
+    const bool srgb = flags & PTB_RESOLVE_SRGB, bgra = flags & PTB_RESOLVE_BGRA;
+    if (srgb && bgra) resolve_kernel<true, true><<<grid, block, 0, s>>>(accum, out8, n_pixels, spp);
+    else if (srgb) resolve_kernel<true, false><<<grid, block, 0, s>>>(accum, out8, n_pixels, spp);
+    else if (bgra) resolve_kernel<false, true><<<grid, block, 0, s>>>(accum, out8, n_pixels, spp);
+    else resolve_kernel<false, false><<<grid, block, 0, s>>>(accum, out8, n_pixels, spp);
+    return cudaGetLastError();
+}
+
+template <bool SRGB>
+__global__ void __launch_bounds__(256) present_kernel(const uint32_t *__restrict__ src, uint32_t sw, uint32_t sh,
+                                                      uint32_t *__restrict__ dst, uint32_t dw, uint32_t dh)
+{
+    __shared__ uint8_t lut[256];
+    if (SRGB) {
+        lut[threadIdx.y * blockDim.x + threadIdx.x] = c_srgb_lut8[threadIdx.y * blockDim.x + threadIdx.x];
+        __syncthreads();
+    }
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t j = blockIdx.y * blockDim.y + threadIdx.y;
+    if (i >= dw || j >= dh) return;
+    // nearest texel of the pixel-centre uv: floor(((i+0.5)/dw)*sw) in exact integer form,
+    // repeat addressing.
+    const uint32_t sx = (uint32_t)(((2ull * i + 1ull) * sw) / (2ull * dw)) % sw;
+    const uint32_t sy = (uint32_t)(((2ull * j + 1ull) * sh) / (2ull * dh)) % sh;
+    const uint32_t p = __ldg(src + (size_t)sy * sw + sx);
+    uint32_t r = p & 0xFFu, g = (p >> 8) & 0xFFu, b = (p >> 16) & 0xFFu;
+    const uint32_t a = p >> 24;
+    if (SRGB) {
+        r = lut[r];
+        g = lut[g];
+        b = lut[b];
+    }
+    dst[(size_t)j * dw + i] = b | (g << 8) | (r << 16) | (a << 24);
+}
+
+cudaError_t launch_present(const uint32_t *src, uint32_t sw, uint32_t sh, uint32_t *dst, uint32_t dw,
+                           uint32_t dh, uint32_t flags, cudaStream_t s)
+{
+    const dim3 block(32, 8);
+    const dim3 grid((dw + 31) / 32, (dh + 7) / 8);
+    if (flags & PTB_RESOLVE_SRGB) present_kernel<true><<<grid, block, 0, s>>>(src, sw, sh, dst, dw, dh);
+    else present_kernel<false><<<grid, block, 0, s>>>(src, sw, sh, dst, dw, dh);
+    return cudaGetLastError();
+}
+
+}  // namespace ptb

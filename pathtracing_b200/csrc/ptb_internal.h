@@ -1,0 +1,58 @@
+// ptb_internal.h — context layout and kernel-launcher declarations shared by the
+// translation units of libptb200.so.  Not part of the public ABI (include/ptb200.h).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <cuda_runtime.h>
+
+#include "../../include/ptb200.h"
+
+namespace ptb {
+
+// Launch-uniform parameters of the CSMain-equivalent kernels (passed by value as a kernel
+// argument -> constant bank).  Literals of Test.hlsl:6,8,12,13 made runtime parameters.
+struct FrameK {
+    uint32_t width, height;
+    float div_x, div_y;
+    float cam[3];
+    float centre[3];
+    float radius;
+};
+
+struct Buffers {
+    uint32_t *rgba8 = nullptr;   // W*H packed R8G8B8A8 (Renderer.cs:124)
+    float4 *f32 = nullptr;       // W*H float4 (Test.hlsl:1), optional
+    int32_t *hit = nullptr;      // W*H hit ids, optional
+    float4 *accum = nullptr;     // W*H float4 accumulation (n2)
+    float4 *accum_owned = nullptr;
+    uint32_t *present = nullptr; // dst_w*dst_h packed B8G8R8A8
+    uint32_t present_w = 0, present_h = 0;
+    size_t present_cap = 0;
+};
+
+// kernels_csmain.cu
+cudaError_t launch_csmain_frame(const FrameK &k, const Buffers &b, cudaStream_t s);
+cudaError_t launch_csmain_accumulate(const FrameK &k, float4 *accum, uint32_t first_sample,
+                                     uint32_t n_samples, uint32_t seed, bool jitter, cudaStream_t s);
+// kernels_image.cu
+cudaError_t image_tables_init();   // sRGB tables -> __constant__ (once per device)
+cudaError_t launch_resolve(const float4 *accum, uint32_t *out8, uint32_t n_pixels, uint32_t spp_total,
+                           uint32_t flags, cudaStream_t s);
+cudaError_t launch_present(const uint32_t *src, uint32_t sw, uint32_t sh, uint32_t *dst, uint32_t dw,
+                           uint32_t dh, uint32_t flags, cudaStream_t s);
+
+}  // namespace ptb
+
+struct ptb_context {
+    ptb_config cfg{};
+    ptb::FrameK k{};
+    ptb::Buffers buf{};
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timer_open = false;
+    uint32_t accum_spp = 0;
+    uint64_t launches = 0;
+    std::string err;
+    void *scene = nullptr;       // ptb::SceneState*, owned (scene.cu)
+};

@@ -1,0 +1,172 @@
+"""NativeTracer — thin, typed wrapper over the C ABI (include/ptb200.h).
+
+This is the executable stand-in for the C# P/Invoke wrapper shipped as source in
+pathtracing_b200/cs/NativeTracer.cs: same calls, same order, same error convention.
+All buffers handed across the boundary are HOST numpy arrays (or raw device pointers for the
+zero-copy accessors); nothing here computes pixels.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import _lib
+from ._lib import (CFG_EXTERNAL_STREAM, CFG_KEEP_F32, CFG_KEEP_HIT_IDS, RESOLVE_BGRA, RESOLVE_SRGB,
+                   Config, PtbError, check)
+
+
+class NativeTracer:
+    """One context == the compute half of the reference's `Renderer` (image + pipeline + fence)."""
+
+    def __init__(self, width: int, height: int, *, device: int = 0,
+                 uv_div: Optional[Sequence[float]] = None,
+                 cam: Optional[Sequence[float]] = None,
+                 centre: Optional[Sequence[float]] = None,
+                 radius: Optional[float] = None,
+                 seed: int = 0, max_depth: int = 0,
+                 keep_f32: bool = False, keep_hit_ids: bool = False,
+                 stream: Optional[int] = None):
+        self._lib = _lib.load()
+        self._ctx = C.c_void_p()
+        cfg = Config()
+        check(None, self._lib.ptb_default_config(C.byref(cfg), width, height))
+        cfg.device = device
+        if uv_div is not None:
+            cfg.uv_div_x, cfg.uv_div_y = float(uv_div[0]), float(uv_div[1])
+        if cam is not None:
+            cfg.cam[:] = [float(v) for v in cam]
+        if centre is not None:
+            cfg.centre[:] = [float(v) for v in centre]
+        if radius is not None:
+            cfg.radius = float(radius)
+        cfg.seed = seed
+        cfg.max_depth = max_depth
+        cfg.flags = (CFG_KEEP_F32 if keep_f32 else 0) | (CFG_KEEP_HIT_IDS if keep_hit_ids else 0)
+        if stream is not None:
+            cfg.flags |= CFG_EXTERNAL_STREAM
+            cfg.stream = stream
+        self.config = cfg
+        self.width, self.height = width, height
+        check(None, self._lib.ptb_create(C.byref(cfg), C.byref(self._ctx)))
+
+    # -- lifecycle -----------------------------------------------------------------------
+    def destroy(self) -> None:
+        if getattr(self, "_ctx", None) is not None and self._ctx.value:
+            self._lib.ptb_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    close = destroy
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.destroy()
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass
+
+    def _ck(self, status: int) -> None:
+        check(self._ctx, status)
+
+    @property
+    def handle(self) -> C.c_void_p:
+        return self._ctx
+
+    # -- the per-frame hot path ----------------------------------------------------------
+    def compute_frame(self) -> None:
+        self._ck(self._lib.ptb_compute_frame(self._ctx))
+
+    def wait(self) -> None:
+        self._ck(self._lib.ptb_wait(self._ctx))
+
+    def read_rgba8(self, out: Optional[np.ndarray] = None) -> np.ndarray:
+        if out is None:
+            out = np.empty((self.height, self.width, 4), np.uint8)
+        self._ck(self._lib.ptb_read_rgba8(self._ctx, out.ctypes.data, out.strides[0]))
+        return out
+
+    def read_f32(self, out: Optional[np.ndarray] = None) -> np.ndarray:
+        if out is None:
+            out = np.empty((self.height, self.width, 4), np.float32)
+        self._ck(self._lib.ptb_read_f32(self._ctx, out.ctypes.data, out.strides[0]))
+        return out
+
+    def read_hit_ids(self, out: Optional[np.ndarray] = None) -> np.ndarray:
+        if out is None:
+            out = np.empty((self.height, self.width), np.int32)
+        self._ck(self._lib.ptb_read_hit_ids(self._ctx, out.ctypes.data, out.strides[0]))
+        return out
+
+    # -- accumulation / resolve ----------------------------------------------------------
+    def accum_reset(self) -> None:
+        self._ck(self._lib.ptb_accum_reset(self._ctx))
+
+    def render_samples(self, first_sample: int, n_samples: int, jitter: bool = True) -> None:
+        self._ck(self._lib.ptb_render_samples(self._ctx, first_sample, n_samples, int(jitter)))
+
+    def resolve(self, srgb: bool = False, bgra: bool = False) -> None:
+        self._ck(self._lib.ptb_resolve(self._ctx, (RESOLVE_SRGB if srgb else 0) | (RESOLVE_BGRA if bgra else 0)))
+
+    @property
+    def accum_spp(self) -> int:
+        return int(self._lib.ptb_accum_spp(self._ctx))
+
+    def set_accum_spp(self, spp: int) -> None:
+        self._ck(self._lib.ptb_set_accum_spp(self._ctx, spp))
+
+    def read_accum(self, out: Optional[np.ndarray] = None) -> np.ndarray:
+        if out is None:
+            out = np.empty((self.height, self.width, 4), np.float32)
+        self._ck(self._lib.ptb_read_accum(self._ctx, out.ctypes.data, out.strides[0]))
+        return out
+
+    def write_accum(self, accum: np.ndarray, spp_total: int) -> None:
+        a = np.ascontiguousarray(accum, np.float32)
+        assert a.shape == (self.height, self.width, 4)
+        self._ck(self._lib.ptb_write_accum(self._ctx, a.ctypes.data, a.strides[0], spp_total))
+
+    def set_accum_buffer(self, device_ptr: Optional[int]) -> None:
+        self._ck(self._lib.ptb_set_accum_buffer(self._ctx, device_ptr))
+
+    # -- present-equivalent ----------------------------------------------------------------
+    def present(self, dst_w: Optional[int] = None, dst_h: Optional[int] = None, srgb: bool = True) -> None:
+        self._ck(self._lib.ptb_present(self._ctx, dst_w or self.width, dst_h or self.height,
+                                       RESOLVE_SRGB if srgb else 0))
+        self._present_shape = (dst_h or self.height, dst_w or self.width)
+
+    def read_present(self) -> np.ndarray:
+        h, w = self._present_shape
+        out = np.empty((h, w, 4), np.uint8)
+        self._ck(self._lib.ptb_read_present(self._ctx, out.ctypes.data, out.strides[0]))
+        return out
+
+    # -- zero-copy + measurement -----------------------------------------------------------
+    def device_rgba8(self) -> int:
+        return int(self._lib.ptb_device_rgba8(self._ctx) or 0)
+
+    def device_f32(self) -> int:
+        return int(self._lib.ptb_device_f32(self._ctx) or 0)
+
+    def device_accum(self) -> int:
+        return int(self._lib.ptb_device_accum(self._ctx) or 0)
+
+    def timer_begin(self) -> None:
+        self._ck(self._lib.ptb_timer_begin(self._ctx))
+
+    def timer_end(self) -> float:
+        ms = C.c_float()
+        self._ck(self._lib.ptb_timer_end(self._ctx, C.byref(ms)))
+        return float(ms.value)
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._lib.ptb_launch_count(self._ctx))
+
+
+__all__ = ["NativeTracer", "PtbError"]

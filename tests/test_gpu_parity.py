@@ -1,0 +1,286 @@
+"""GPU parity tests (run with -m gpu on the B200 box): the CUDA path, called through the C ABI,
+against the CPU oracle on the same inputs — bit-exact — and against the committed goldens."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+from pathtracing_b200 import NativeTracer, PtbError, Renderer, Window, _lib
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLD = os.path.join(HERE, "golden")
+with open(os.path.join(GOLD, "oracle_digests.json")) as f:
+    DIG = json.load(f)
+with open(os.path.join(GOLD, "appendix_b.json")) as f:
+    APPB = json.load(f)
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def eq_bits(a, b):
+    return np.array_equal(np.ascontiguousarray(a).view(np.uint32), np.ascontiguousarray(b).view(np.uint32))
+
+
+def gpu_frame(w, h, **kw):
+    with NativeTracer(w, h, keep_f32=True, keep_hit_ids=True, **kw) as t:
+        t.compute_frame()
+        t.wait()
+        return {"f32": t.read_f32(), "rgba8": t.read_rgba8(), "hit": t.read_hit_ids()}
+
+
+# ---- a1-a5: the literal CSMain frame -----------------------------------------------------------
+@pytest.mark.parametrize("name", sorted(DIG["frames"]))
+def test_frame_matches_golden_digests(name):
+    c = DIG["frames"][name]
+    kw = dict(c["params"])
+    if c["uv_div"]:
+        kw["uv_div"] = c["uv_div"]
+    g = gpu_frame(c["width"], c["height"], **kw)
+    assert int((g["hit"] == 0).sum()) == c["hits"]
+    assert sha(g["hit"]) == c["hit"]          # hit-primitive ids: bit-exact
+    assert sha(g["f32"]) == c["f32"]          # radiance: bit-exact (bar is 1e-4 rel)
+    assert sha(g["rgba8"]) == c["rgba8"]
+
+
+@pytest.mark.parametrize("w,h,div", [(320, 180, None), (1920, 1080, None), (3840, 2160, None),
+                                     (320, 180, (1080, 1080)), (333, 77, None), (1, 1, None), (7, 1, None),
+                                     (4, 5, None), (1921, 3, (1080, 1080))])
+def test_frame_matches_oracle_bit_exact(oracle, w, h, div):
+    p = oracle.frame_params(w, h, uv_div=div)
+    ref = oracle.csmain_frame(p)
+    g = gpu_frame(w, h, uv_div=div)
+    assert np.array_equal(g["hit"], ref["hit"])
+    assert eq_bits(g["f32"], ref["f32"])
+    assert np.array_equal(g["rgba8"], ref["rgba8"])
+    # north_star tolerance form of the same statement (1e-4 relative at 1 spp)
+    np.testing.assert_allclose(g["f32"], ref["f32"], rtol=1e-4, atol=0)
+
+
+def test_frame_appendix_b_known_answers():
+    g = gpu_frame(1920, 1080)
+    assert int((g["hit"] == 0).sum()) == 305317
+    ys, xs = np.nonzero(g["hit"] == 0)
+    assert (xs.min(), xs.max(), ys.min(), ys.max()) == (229, 851, 229, 851)
+    for px in APPB["pixels"]:
+        if px["div"] != 1080:
+            continue
+        col = g["f32"][px["y"], px["x"]]
+        assert [int(v) for v in col[:3].view(np.uint32)] == [int(v, 16) for v in px["rgb"]]
+        assert (g["hit"][px["y"], px["x"]] == 0) == bool(px["hit"])
+    assert g["f32"][540, 540].tolist() == [0.5, 0.5, 1.0, 1.0]
+
+
+def test_frame_small_fixture_without_oracle():
+    z = np.load(os.path.join(GOLD, "c1_small.npz"))
+    g = gpu_frame(64, 36)
+    assert eq_bits(g["f32"], z["f32"]) and np.array_equal(g["rgba8"], z["rgba8"]) and np.array_equal(g["hit"], z["hit"])
+
+
+def test_frame_moved_camera_and_sphere(oracle):
+    kw = dict(cam=(0.25, -0.5, 2.0), centre=(-0.3, 0.2, -0.4), radius=0.9)
+    ref = oracle.csmain_frame(oracle.frame_params(640, 360, **kw))
+    g = gpu_frame(640, 360, **kw)
+    assert np.array_equal(g["hit"], ref["hit"]) and eq_bits(g["f32"], ref["f32"])
+
+
+def test_frame_is_idempotent_and_rgba8_only_path():
+    with NativeTracer(1920, 1080) as t:     # no f32 / hit planes: the reference configuration
+        t.compute_frame()
+        a = t.read_rgba8()
+        t.compute_frame()
+        t.compute_frame()
+        b = t.read_rgba8()
+        assert t.launch_count == 3
+    assert np.array_equal(a, b)
+    assert sha(a) == DIG["frames"]["c2_1920x1080"]["rgba8"]
+
+
+def test_read_with_pitch():
+    with NativeTracer(100, 7) as t:
+        t.compute_frame()
+        tight = t.read_rgba8()
+        padded = np.zeros((7, 128, 4), np.uint8)
+        view = padded[:, :100, :]
+        t.read_rgba8(view)
+        assert np.array_equal(view, tight) and not padded[:, 100:, :].any()
+
+
+# ---- n1/n2: jittered accumulation + resolve -----------------------------------------------------
+@pytest.mark.parametrize("name", sorted(DIG["accum"]))
+def test_accumulate_matches_golden_digests(name):
+    c = DIG["accum"][name]
+    with NativeTracer(c["width"], c["height"], seed=c["seed"]) as t:
+        t.render_samples(c["first"], c["n"], jitter=c["jitter"])
+        acc = t.read_accum()
+        assert sha(acc) == c["accum"]
+        t.resolve()
+        assert sha(t.read_rgba8()) == c["resolve"]
+        t.resolve(srgb=True, bgra=True)
+        assert sha(t.read_rgba8()) == c["resolve_srgb_bgra"]
+
+
+@pytest.mark.parametrize("w,h,first,n,seed", [(320, 180, 0, 8, 0), (333, 77, 5, 3, 99), (1920, 1080, 0, 2, 1)])
+def test_accumulate_matches_oracle_bit_exact(oracle, w, h, first, n, seed):
+    p = oracle.frame_params(w, h)
+    ref = oracle.accumulate(p, first, n, seed, True)
+    with NativeTracer(w, h, seed=seed) as t:
+        t.render_samples(first, n, jitter=True)
+        acc = t.read_accum()
+        assert eq_bits(acc, ref)
+        t.resolve()
+        assert np.array_equal(t.read_rgba8(), oracle.resolve(ref, n))
+        t.resolve(srgb=True)
+        assert np.array_equal(t.read_rgba8(), oracle.resolve(ref, n, srgb=True))
+
+
+def test_accumulate_no_jitter_reduces_to_csmain():
+    with NativeTracer(320, 180, keep_f32=True) as t:
+        t.compute_frame()
+        frame, frame8 = t.read_f32(), t.read_rgba8()
+        t.render_samples(0, 1, jitter=False)
+        assert eq_bits(t.read_accum(), frame)
+        t.resolve()
+        assert np.array_equal(t.read_rgba8(), frame8)
+
+
+def test_progressive_launches_and_checkpoint(oracle):
+    p = oracle.frame_params(320, 180)
+    ref = oracle.accumulate(p, 0, 4, 3, True)
+    ref = oracle.accumulate(p, 4, 4, 3, True, accum=ref)
+    with NativeTracer(320, 180, seed=3) as t:
+        t.render_samples(0, 4)
+        ckpt, spp = t.read_accum(), t.accum_spp
+        assert spp == 4
+        t.render_samples(4, 4)
+        full = t.read_accum()
+        assert t.accum_spp == 8 and eq_bits(full, ref)
+    with NativeTracer(320, 180, seed=3) as t2:      # resume from the checkpoint
+        t2.write_accum(ckpt, spp)
+        t2.render_samples(4, 4)
+        assert eq_bits(t2.read_accum(), ref) and t2.accum_spp == 8
+        t2.accum_reset()
+        assert t2.accum_spp == 0 and not t2.read_accum().any()
+
+
+def test_full_size_properties_c2_64spp():
+    """BASELINE configs[1] at full size through size-independent properties."""
+    with NativeTracer(1920, 1080, seed=0, keep_f32=True) as t:
+        t.render_samples(0, 64)
+        acc = t.read_accum()
+        t.compute_frame()
+        frame = t.read_f32()
+    assert np.all(acc[..., 3] == 64.0)                     # alpha is exactly 1 per sample
+    mean = acc / np.float32(64)
+    assert np.isfinite(mean).all()
+    # interior of the sphere and far background are smooth: jittered mean ~ centre sample
+    assert np.abs(mean[540, 540] - frame[540, 540]).max() < 2e-3
+    assert np.abs(mean[10, 1900] - frame[10, 1900]).max() < 2e-3
+    # mirror symmetry of the scene about the sphere centre row is preserved statistically
+    assert abs(float(mean[300:781, 300:781, 2].mean()) - float(mean[300:781, 300:781, 2][::-1].mean())) < 1e-3
+
+
+# ---- f1: present-equivalent ---------------------------------------------------------------------
+@pytest.mark.parametrize("dw,dh,srgb", [(320, 180, True), (320, 180, False), (500, 333, True), (97, 41, False),
+                                        (1, 1, True)])
+def test_present_matches_oracle(oracle, dw, dh, srgb):
+    with NativeTracer(320, 180) as t:
+        t.compute_frame()
+        img = t.read_rgba8()
+        t.present(dw, dh, srgb=srgb)
+        out = t.read_present()
+    assert np.array_equal(out, oracle.present(img, dw, dh, srgb=srgb))
+
+
+def test_present_golden_digests():
+    g = DIG["present"]
+    with NativeTracer(320, 180) as t:
+        t.compute_frame()
+        t.present(320, 180, srgb=True)
+        assert sha(t.read_present()) == g["same_size_srgb"]
+        t.present(500, 333, srgb=True)
+        assert sha(t.read_present()) == g["up_500x333_srgb"]
+        t.present(97, 41, srgb=False)
+        assert sha(t.read_present()) == g["down_97x41_linear"]
+
+
+def test_srgb_encode_exhaustive_on_a_ramp(oracle):
+    """resolve(sRGB) against the oracle's double-precision OETF on a dense float ramp incl. edge values."""
+    w, h = 4096, 64
+    rng = np.random.default_rng(5)
+    acc = np.zeros((h, w, 4), np.float32)
+    acc[..., 0] = np.linspace(0, 1, w * h, dtype=np.float32).reshape(h, w)
+    acc[..., 1] = rng.random((h, w), dtype=np.float32) * np.float32(1.2) - np.float32(0.1)
+    acc[..., 2] = rng.random((h, w), dtype=np.float32) ** 4
+    acc[..., 3] = 1.0
+    acc[0, :8, 1] = [np.nan, np.inf, -np.inf, 0.0, -0.0, 1.0, 0.0031308, 1e-30]
+    with NativeTracer(w, h) as t:
+        t.write_accum(acc, 1)
+        t.resolve(srgb=True)
+        out = t.read_rgba8()
+        t.write_accum(acc * np.float32(3), 3)
+        t.resolve(srgb=False, bgra=True)
+        out_lin = t.read_rgba8()
+    assert np.array_equal(out, oracle.resolve(acc, 1, srgb=True))
+    assert np.array_equal(out_lin, oracle.resolve(acc * np.float32(3), 3, bgra=True))
+
+
+# ---- the Renderer mirror and the error contract ------------------------------------------------------
+def test_renderer_mirror_call_sequence(oracle):
+    r = Renderer(Window(FramebufferSize=(1920, 1080)))
+    r.Init()
+    r.Render(1.0 / 60.0)
+    img, shown = r.ReadImage(), r.ReadPresented()
+    r.Dispose()
+    r.Dispose()                                            # idempotent
+    ref = oracle.csmain_frame(oracle.frame_params(1920, 1080))["rgba8"]
+    assert np.array_equal(img, ref)
+    assert np.array_equal(shown, oracle.present(ref, 1920, 1080, srgb=True))
+
+
+def test_renderer_requires_pipeline():
+    r = Renderer(Window((64, 36)))
+    with pytest.raises(Exception):
+        r.CreateComputePipeline()
+    r.CreateResources()
+    with pytest.raises(Exception):
+        r.ComputeFrame(0.0)
+    r.Dispose()
+
+
+def test_error_contract():
+    with NativeTracer(64, 36) as t:
+        with pytest.raises(PtbError) as e:
+            t.read_f32()                                   # created without KEEP_F32
+        assert e.value.status == _lib.PTB_ERR_STATE
+        with pytest.raises(PtbError) as e:
+            t.resolve()                                    # 0 spp
+        assert e.value.status == _lib.PTB_ERR_STATE
+        with pytest.raises(PtbError) as e:
+            t.read_present()
+        assert e.value.status == _lib.PTB_ERR_STATE
+        bad = np.zeros((36, 8, 4), np.uint8)               # pitch too small
+        with pytest.raises(PtbError) as e:
+            t._ck(t._lib.ptb_read_rgba8(t.handle, bad.ctypes.data, 32))
+        assert e.value.status == _lib.PTB_ERR_INVALID
+        with pytest.raises(PtbError):
+            t._ck(t._lib.ptb_read_rgba8(t.handle, None, 0))
+        t.compute_frame()                                  # context still usable after errors
+        t.wait()
+    with pytest.raises(PtbError) as e:
+        NativeTracer(64, 36, device=999)
+    assert e.value.status == _lib.PTB_ERR_INVALID
+
+
+def test_timer_and_launch_count():
+    with NativeTracer(1920, 1080) as t:
+        t.timer_begin()
+        for _ in range(10):
+            t.compute_frame()
+        ms = t.timer_end()
+        assert 0 < ms < 1000 and t.launch_count == 10
