@@ -398,6 +398,7 @@ def run_b200(args):
                     "note": "C-ABI calls with host buffers; the path's only input is the parameter block "
                             "(Test.hlsl reads nothing), output = RGBA8 frame read into pinned host memory each step"},
             "gpu_launches": int(launches),
+            "kernel_mode": t.kernel_mode,
             "clocks": {"sm_mhz": clk["sm_mhz"], "sm_max_mhz": clk["sm_max_mhz"], "reasons": clk["reasons"],
                        "samples": clk["samples"]},
             "merge_ms": merge_ms,

@@ -45,6 +45,8 @@ typedef struct ptb_context ptb_context;   /* opaque; owns all device memory and 
 #define PTB_CFG_KEEP_F32      0x1u  /* ptb_compute_frame also stores the float4 image (Test.hlsl:1 RWTexture2D<float4>) */
 #define PTB_CFG_KEEP_HIT_IDS  0x2u  /* ptb_compute_frame also stores int32 hit ids (0 = sphere, -1 = miss) */
 #define PTB_CFG_EXTERNAL_STREAM 0x4u /* use `stream` (a cudaStream_t) instead of creating one */
+#define PTB_CFG_FORCE_IEEE    0x8u  /* always run the literal IEEE-intrinsic kernels (never the shortened, proven-equal
+                                       FMA sequences); results are bit-identical either way — for tests / A-B timing */
 
 /* Parameters that are literals in the reference (Test.hlsl:6,8,12,13; App.cs:27).
  * ptb_default_config fills them so that width=1920,height=1080 reproduces the reference. */
@@ -142,6 +144,14 @@ int ptb_timer_begin(ptb_context *ctx);
 int ptb_timer_end(ptb_context *ctx, float *elapsed_ms);     /* synchronises */
 /* Kernels launched by this context since creation (for bench.py's gpu_launches). */
 uint64_t ptb_launch_count(const ptb_context *ctx);
+/* Which CSMain kernel variant this context runs: 0 = literal IEEE intrinsics, 1 = shortened exact
+ * sequences, 2 = shortened + camera-on-axis specialisation.  All three produce identical bits. */
+int ptb_kernel_mode(const ptb_context *ctx);
+/* Proof by exhaustion, on the device, that a shortened sequence equals the IEEE intrinsic on its
+ * whole domain: which = 0 sqrt over [2^-20,2^24), 1 reciprocal over [2^-12,2^12), 2 division of
+ * every float in [2^-24,2^17) by `divisor`.  Writes the number of disagreeing inputs (must be 0
+ * for the fast kernels to be selected) and the number of inputs tested. */
+int ptb_selftest_exact_math(ptb_context *ctx, int which, float divisor, uint64_t *mismatches, uint64_t *tested);
 
 #ifdef __cplusplus
 }

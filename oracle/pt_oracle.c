@@ -153,29 +153,20 @@ int64_t pto_csmain_frame(const pto_frame_params *p, float *out_f32, uint8_t *out
 }
 
 /* ---- RNG (no reference counterpart: Test.hlsl is deterministic; spec frozen here) ---- */
-uint32_t pto_pcg_hash(uint32_t v)
+void pto_pcg3d(uint32_t v[3])
 {
-    uint32_t state = v * 747796405u + 2891336453u;
-    uint32_t word = ((state >> ((state >> 28) + 4u)) ^ state) * 277803737u;
-    return (word >> 22) ^ word;
+    uint32_t x = v[0] * 1664525u + 1013904223u;
+    uint32_t y = v[1] * 1664525u + 1013904223u;
+    uint32_t z = v[2] * 1664525u + 1013904223u;
+    x += y * z; y += z * x; z += x * y;
+    x ^= x >> 16; y ^= y >> 16; z ^= z >> 16;
+    x += y * z; y += z * x; z += x * y;
+    v[0] = x; v[1] = y; v[2] = z;
 }
 
-uint32_t pto_rng_init(uint32_t pixel_index, uint32_t sample_index, uint32_t seed)
+float pto_bits_to_unit(uint32_t w)
 {
-    return pto_pcg_hash(pixel_index + pto_pcg_hash(sample_index + pto_pcg_hash(seed)));
-}
-
-uint32_t pto_rng_next(uint32_t *state)
-{
-    uint32_t s = *state * 747796405u + 2891336453u;
-    *state = s;
-    uint32_t word = ((s >> ((s >> 28) + 4u)) ^ s) * 277803737u;
-    return (word >> 22) ^ word;
-}
-
-float pto_rng_float(uint32_t *state)
-{
-    return (float)(pto_rng_next(state) >> 8) * 5.9604644775390625e-8f; /* 2^-24, exact */
+    return (float)(w >> 9) * 1.1920928955078125e-7f;   /* 2^-23, exact */
 }
 
 void pto_accumulate(const pto_frame_params *p, uint32_t first_sample, uint32_t n_samples,
@@ -193,9 +184,10 @@ void pto_accumulate(const pto_frame_params *p, uint32_t first_sample, uint32_t n
             for (uint32_t k = 0; k < n_samples; ++k) {
                 float jx = 0.0f, jy = 0.0f;
                 if (jitter) {
-                    uint32_t st = pto_rng_init(pix, first_sample + k, seed);
-                    jx = pto_rng_float(&st);
-                    jy = pto_rng_float(&st);
+                    uint32_t v[3] = { pix, first_sample + k, seed };
+                    pto_pcg3d(v);
+                    jx = pto_bits_to_unit(v[0]);
+                    jy = pto_bits_to_unit(v[1]);
                 }
                 float col[4];
                 pto_csmain_sample(p, (float)x + jx, (float)y + jy, col, NULL, NULL);

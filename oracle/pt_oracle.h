@@ -63,15 +63,15 @@ uint8_t pto_unorm8(float v);
 /* sRGB OETF then UNORM8 (what a B8G8R8A8Srgb attachment does on write). */
 uint8_t pto_srgb8(float v);
 
-/* ---- n1: counter-based RNG (frozen spec, shared by CPU oracle and CUDA path) ---- */
-uint32_t pto_pcg_hash(uint32_t v);
-uint32_t pto_rng_init(uint32_t pixel_index, uint32_t sample_index, uint32_t seed);
-uint32_t pto_rng_next(uint32_t *state);          /* PCG-RXS-M-XS 32 */
-float    pto_rng_float(uint32_t *state);         /* (next >> 8) * 2^-24, in [0,1) */
+/* ---- n1: counter-based RNG (frozen spec, restated independently by the CUDA path) ----
+ * pcg3d (Jarzynski & Olano, JCGT 2020) keyed (pixel index, sample index, seed); a random
+ * 32-bit word w maps to the unit interval as (w >> 9) * 2^-23 (exact, 23 bits). */
+void  pto_pcg3d(uint32_t v[3]);
+float pto_bits_to_unit(uint32_t w);
 
 /* ---- n1/n2: jittered multi-sample accumulation of the CSMain path ----
- * For s in [first_sample, first_sample+n_samples): state = rng_init(y*W+x, s, seed);
- * jx = rng_float, jy = rng_float; colour = csmain((float)x + jx, (float)y + jy).
+ * For s in [first_sample, first_sample+n_samples): v = pcg3d(y*W+x, s, seed);
+ * jx = unit(v.x), jy = unit(v.y); colour = csmain((float)x + jx, (float)y + jy).
  * Samples are summed sequentially in s into a float4 partial starting from 0, and
  * the partial is then added to accum[pixel] (one add per launch).
  * jitter == 0 -> jx = jy = 0 (reduces to a1-a5 exactly). */

@@ -56,14 +56,10 @@ def lib() -> C.CDLL:
         L.pto_unorm8.restype = C.c_uint8
         L.pto_srgb8.argtypes = [C.c_float]
         L.pto_srgb8.restype = C.c_uint8
-        L.pto_pcg_hash.argtypes = [C.c_uint32]
-        L.pto_pcg_hash.restype = C.c_uint32
-        L.pto_rng_init.argtypes = [C.c_uint32] * 3
-        L.pto_rng_init.restype = C.c_uint32
-        L.pto_rng_next.argtypes = [P(C.c_uint32)]
-        L.pto_rng_next.restype = C.c_uint32
-        L.pto_rng_float.argtypes = [P(C.c_uint32)]
-        L.pto_rng_float.restype = C.c_float
+        L.pto_pcg3d.argtypes = [P(C.c_uint32)]
+        L.pto_pcg3d.restype = None
+        L.pto_bits_to_unit.argtypes = [C.c_uint32]
+        L.pto_bits_to_unit.restype = C.c_float
         L.pto_accumulate.argtypes = [P(FrameParams), C.c_uint32, C.c_uint32, C.c_uint32, C.c_int,
                                      C.c_void_p, C.c_int]
         L.pto_accumulate.restype = None
@@ -139,13 +135,14 @@ def present(src_rgba8: np.ndarray, dw: int, dh: int, srgb=True) -> np.ndarray:
     return out
 
 
-def rng_stream(pixel: int, sample: int, seed: int, n: int):
-    """-> (uint32[n] raw outputs, float32[n]) of two independent passes over the same stream."""
-    st = C.c_uint32(lib().pto_rng_init(pixel, sample, seed))
-    raw = [lib().pto_rng_next(C.byref(st)) for _ in range(n)]
-    st = C.c_uint32(lib().pto_rng_init(pixel, sample, seed))
-    flt = [lib().pto_rng_float(C.byref(st)) for _ in range(n)]
-    return np.array(raw, np.uint32), np.array(flt, np.float32)
+def pcg3d(x: int, y: int, z: int):
+    v = (C.c_uint32 * 3)(x & 0xFFFFFFFF, y & 0xFFFFFFFF, z & 0xFFFFFFFF)
+    lib().pto_pcg3d(v)
+    return int(v[0]), int(v[1]), int(v[2])
+
+
+def bits_to_unit(w: int) -> np.float32:
+    return np.float32(lib().pto_bits_to_unit(w & 0xFFFFFFFF))
 
 
 def max_threads() -> int:

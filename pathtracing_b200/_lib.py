@@ -24,6 +24,7 @@ PTB_ERR_UNSUPPORTED = -5
 CFG_KEEP_F32 = 0x1
 CFG_KEEP_HIT_IDS = 0x2
 CFG_EXTERNAL_STREAM = 0x4
+CFG_FORCE_IEEE = 0x8
 RESOLVE_SRGB = 0x1
 RESOLVE_BGRA = 0x2
 
@@ -103,6 +104,8 @@ SIGNATURES = {
     "ptb_timer_begin": (C.c_int, [_CTX]),
     "ptb_timer_end": (C.c_int, [_CTX, _P(C.c_float)]),
     "ptb_launch_count": (C.c_uint64, [_CTX]),
+    "ptb_kernel_mode": (C.c_int, [_CTX]),
+    "ptb_selftest_exact_math": (C.c_int, [_CTX, C.c_int, C.c_float, _P(C.c_uint64), _P(C.c_uint64)]),
 }
 
 _lib = None

@@ -1,6 +1,7 @@
 // api.cu — the extern "C" boundary of libptb200.so (include/ptb200.h).
 // Each entry point names the reference member it replaces in the header; this file only does
 // argument checking, resource ownership and stream/event plumbing around the kernel launchers.
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -67,6 +68,32 @@ int read_rows(ptb_context *ctx, void *host_dst, size_t pitch, const void *dev, s
     return PTB_OK;
 }
 
+// Launch-uniform validity of the shortened exact sequences (kernels_csmain.cu MODE_FAST*):
+//  - both screen divisors pass the exhaustive one-correction division check for v in [2^-24, 2^17);
+//  - pixel coordinates (plus jitter) stay below 2^17;
+//  - |uv| is bounded so that dot(v,v) of Test.hlsl:10 stays inside [1, 2^23) (sqrt / rcp domains);
+//  - every derived term is finite.
+void derive_fast_flags(ptb_context *c)
+{
+    ptb::FrameK &k = c->k;
+    k.fast = 0;
+    k.on_axis = 0;
+    if (c->cfg.flags & PTB_CFG_FORCE_IEEE) return;
+    const float vals[] = {k.cam[0], k.cam[1], k.cam[2], k.centre[0], k.centre[1], k.centre[2], k.radius,
+                          k.oc[0], k.oc[1], k.oc[2], k.c, k.c4, k.inv_div_x, k.inv_div_y};
+    for (float v : vals)
+        if (!std::isfinite(v)) return;
+    if (k.width > 65536u || k.height > 65536u) return;
+    const double ux = 2.0 * (k.width + 1.0) / std::fabs((double)k.div_x) + 1.0;
+    const double uy = 2.0 * (k.height + 1.0) / std::fabs((double)k.div_y) + 1.0;
+    if (!(ux * ux + uy * uy + 1.0 < 8388608.0)) return;
+    if (!ptb::uniform_divisor_verified(k.div_x, c->stream)) return;
+    if (!ptb::uniform_divisor_verified(k.div_y, c->stream)) return;
+    k.fast = 1;
+    const float az = std::fabs(k.oc[2]);
+    k.on_axis = (k.oc[0] == 0.0f && k.oc[1] == 0.0f && az >= 8.67e-19f /*~2^-60*/ && az <= 1.15e18f /*~2^60*/) ? 1u : 0u;
+}
+
 }  // namespace
 
 namespace ptb {
@@ -113,7 +140,7 @@ int ptb_create(const ptb_config *cfg, ptb_context **out_ctx)
         return fail(nullptr, PTB_ERR_UNSUPPORTED, "ptb_create: %ux%u exceeds 2^30 pixels", cfg->width, cfg->height);
     if (!(cfg->uv_div_x != 0.0f) || !(cfg->uv_div_y != 0.0f))
         return fail(nullptr, PTB_ERR_INVALID, "ptb_create: uv divisor must be non-zero");
-    if (cfg->flags & ~(PTB_CFG_KEEP_F32 | PTB_CFG_KEEP_HIT_IDS | PTB_CFG_EXTERNAL_STREAM))
+    if (cfg->flags & ~(PTB_CFG_KEEP_F32 | PTB_CFG_KEEP_HIT_IDS | PTB_CFG_EXTERNAL_STREAM | PTB_CFG_FORCE_IEEE))
         return fail(nullptr, PTB_ERR_INVALID, "ptb_create: unknown flags 0x%x", cfg->flags);
 
     int ndev = 0;
@@ -152,6 +179,8 @@ int ptb_create(const ptb_config *cfg, ptb_context **out_ctx)
     if ((e = cudaEventCreate(&c->ev0)) != cudaSuccess) return bail(e, "cudaEventCreate");
     if ((e = cudaEventCreate(&c->ev1)) != cudaSuccess) return bail(e, "cudaEventCreate");
     if ((e = ptb::image_tables_init()) != cudaSuccess) return bail(e, "image_tables_init");
+    if ((e = ptb::prepare_terms(&c->k, c->stream)) != cudaSuccess) return bail(e, "prepare_terms");
+    derive_fast_flags(c);
 
     const size_t n = n_pixels(c);
     // ≙ CreateResources (Renderer.cs:120-179): the W x H RGBA8 storage image.
@@ -373,5 +402,26 @@ int ptb_timer_end(ptb_context *ctx, float *elapsed_ms)
 }
 
 uint64_t ptb_launch_count(const ptb_context *ctx) { return ctx ? ctx->launches : 0; }
+
+int ptb_kernel_mode(const ptb_context *ctx)
+{
+    if (!ctx) return fail(nullptr, PTB_ERR_INVALID, "ptb_kernel_mode: ctx is NULL");
+    return ctx->k.fast ? (ctx->k.on_axis ? 2 : 1) : 0;
+}
+
+int ptb_selftest_exact_math(ptb_context *ctx, int which, float divisor, uint64_t *mismatches, uint64_t *tested)
+{
+    PTB_ENTER(ctx);
+    if (which < 0 || which > 2 || !mismatches || !tested)
+        return fail(ctx, PTB_ERR_INVALID, "ptb_selftest_exact_math: bad argument");
+    if (which == 2 && !(std::fabs(divisor) > 0.0f && std::isfinite(divisor)))
+        return fail(ctx, PTB_ERR_INVALID, "ptb_selftest_exact_math: divisor must be finite and non-zero");
+    unsigned long long bad = 0, n = 0;
+    PTB_CUDA(ctx, ptb::selftest_exact(which, divisor, &bad, &n, ctx->stream));
+    ctx->launches += 1;
+    *mismatches = bad;
+    *tested = n;
+    return PTB_OK;
+}
 
 }  // extern "C"

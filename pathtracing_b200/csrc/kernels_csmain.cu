@@ -8,59 +8,112 @@
 //   csmain_accumulate   : north_star stage n1/n2 — spp jittered samples per pixel summed
 //                         in-kernel into a float4 accumulation buffer.
 //
-// Arithmetic is the frozen "one rounding per op" evaluation of Test.hlsl (ptb_math.cuh), so
-// results are bit-identical to the CPU oracle's.  These kernels are FP32-issue bound (multi-spp)
-// or HBM-write / launch bound (1 spp); there is no dense contraction, so no tensor cores.
+// Arithmetic is the frozen "one rounding per op" evaluation of Test.hlsl, so results are
+// bit-identical to the CPU oracle's.  Both kernels are FP32-issue bound (the IEEE divisions and
+// square roots dominate), so the work here is cutting instructions WITHOUT changing a single
+// result bit: MODE_FAST replaces each IEEE division / sqrt by a short FMA sequence that is
+// proven (exhaustively, selftest.cu) or provable (Markstein) to round identically on the domain
+// the launch-uniform checks in api.cu guarantee; MODE_GENERIC is the literal intrinsic form and
+// is used whenever those checks fail.  No dense contraction anywhere => no tensor cores.
 #include "ptb_internal.h"
 #include "ptb_math.cuh"
 
 namespace ptb {
 
-// Launch-uniform terms of Test.hlsl:16,19 (oc, c) evaluated once per thread.
-struct SphereTerms {
-    V3 cam, centre, oc;
-    float c;
-};
+enum Mode { MODE_GENERIC = 0, MODE_FAST = 1, MODE_FAST_ON_AXIS = 2 };
 
-__device__ __forceinline__ SphereTerms sphere_terms(const FrameK &k)
+// Launch-uniform subexpressions, evaluated once on the device with the same intrinsics.
+__global__ void prepare_terms_kernel(FrameK *k)
 {
-    SphereTerms s;
-    s.cam = V3{k.cam[0], k.cam[1], k.cam[2]};
-    s.centre = V3{k.centre[0], k.centre[1], k.centre[2]};
-    s.oc = V3{fsub(s.cam.x, s.centre.x), fsub(s.cam.y, s.centre.y), fsub(s.cam.z, s.centre.z)};  // :16
-    s.c = fsub(dot3(s.oc, s.oc), fmul(k.radius, k.radius));                                       // :19
-    return s;
+    k->inv_div_x = __frcp_rn(k->div_x);
+    k->inv_div_y = __frcp_rn(k->div_y);
+    const V3 oc{fsub(k->cam[0], k->centre[0]), fsub(k->cam[1], k->centre[1]), fsub(k->cam[2], k->centre[2])};  // :16
+    k->oc[0] = oc.x;
+    k->oc[1] = oc.y;
+    k->oc[2] = oc.z;
+    k->c = fsub(dot3(oc, oc), fmul(k->radius, k->radius));   // :19
+    k->c4 = fmul(4.0f, k->c);
+    k->neg2ocz = -fmul(2.0f, oc.z);
+}
+
+cudaError_t prepare_terms(FrameK *k_host, cudaStream_t s)
+{
+    FrameK *d = nullptr;
+    cudaError_t e = cudaMalloc(&d, sizeof(FrameK));
+    if (e != cudaSuccess) return e;
+    e = cudaMemcpyAsync(d, k_host, sizeof(FrameK), cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess) {
+        prepare_terms_kernel<<<1, 1, 0, s>>>(d);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(k_host, d, sizeof(FrameK), cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaFree(d);
+    return e;
 }
 
 // Test.hlsl:7 for one axis: uv = (id / resolution) * 2 - 1.
-__device__ __forceinline__ float screen_uv(float p, float div)
+template <int MODE>
+__device__ __forceinline__ float screen_uv(float p, float div, float inv_div)
 {
-    return fsub(fmul(fdiv(p, div), 2.0f), 1.0f);
+    if (MODE == MODE_GENERIC) return fsub(fmul(fdiv(p, div), 2.0f), 1.0f);
+    // q*2 is exact, so one FMA rounds exactly like (q*2) - 1.
+    return ffma(div_rn_uniform(p, div, inv_div), 2.0f, -1.0f);
 }
 
-// Test.hlsl:10-37 given uv.  Returns true on hit (disc > 0, strict).
-__device__ __forceinline__ bool csmain_shade(const SphereTerms &s, float uvx, float uvy, float4 &col)
+// Test.hlsl:10-37 given uv.  Returns true on hit (disc > 0, strict); rgb = colour.xyz (alpha is 1).
+template <int MODE>
+__device__ __forceinline__ bool csmain_shade(const FrameK &k, float uvx, float uvy, float &r, float &g, float &bl)
 {
-    const V3 d = normalize3(V3{uvx, uvy, -1.0f});                 // :10
-    const float a = dot3(d, d);                                   // :17
-    const float b = fmul(2.0f, dot3(s.oc, d));                    // :18
-    const float disc = fsub(fmul(b, b), fmul(fmul(4.0f, a), s.c)); // :21
-    if (disc > 0.0f) {                                            // :24
-        const float t = fdiv(fsub(-b, fsqrt(disc)), fmul(2.0f, a));  // :27
-        const V3 P{fadd(s.cam.x, fmul(t, d.x)), fadd(s.cam.y, fmul(t, d.y)), fadd(s.cam.z, fmul(t, d.z))};  // :28
-        const V3 n = normalize3(V3{fsub(P.x, s.centre.x), fsub(P.y, s.centre.y), fsub(P.z, s.centre.z)});   // :29
-        col = make_float4(fadd(fmul(n.x, 0.5f), 0.5f), fadd(fmul(n.y, 0.5f), 0.5f),
-                          fadd(fmul(n.z, 0.5f), 0.5f), 1.0f);      // :31
+    V3 d;
+    float a, b, disc;
+    if (MODE == MODE_GENERIC) {
+        d = normalize3(V3{uvx, uvy, -1.0f});                                   // :10
+        a = dot3(d, d);                                                        // :17
+        b = fmul(2.0f, dot3(V3{k.oc[0], k.oc[1], k.oc[2]}, d));                // :18
+        disc = fsub(fmul(b, b), fmul(fmul(4.0f, a), k.c));                     // :21
+    } else {
+        // :10 — dot(v,v) with v.z = -1: (-1)*(-1) == 1 exactly; len in [1, 2^12) by the launch check.
+        const float len = sqrt_rn_fast(fadd(fadd(fmul(uvx, uvx), fmul(uvy, uvy)), 1.0f));
+        const float yh = rcp_rn_fast(len);                                     // RN(1/len)
+        d = V3{div_rn_by_rcp(uvx, len, yh), div_rn_by_rcp(uvy, len, yh), -yh};  // -1/len == -RN(1/len)
+        a = fadd(fadd(fmul(d.x, d.x), fmul(d.y, d.y)), fmul(yh, yh));          // :17
+        if (MODE == MODE_FAST_ON_AXIS)
+            b = fmul(k.neg2ocz, yh);   // :18 with oc = (0,0,z): 2*(z*d.z) == RN((-2z)*yh), scalings exact
+        else
+            b = fmul(2.0f, dot3(V3{k.oc[0], k.oc[1], k.oc[2]}, d));
+        disc = fsub(fmul(b, b), fmul(a, k.c4));                                // :21, (4a)c == a(4c) exactly scaled
+    }
+    if (disc > 0.0f) {                                                         // :24
+        const float t = fdiv(fsub(-b, fsqrt(disc)), fmul(2.0f, a));            // :27
+        const V3 pc{fsub(fadd(k.cam[0], fmul(t, d.x)), k.centre[0]),           // :28-29
+                    fsub(fadd(k.cam[1], fmul(t, d.y)), k.centre[1]),
+                    fsub(fadd(k.cam[2], fmul(t, d.z)), k.centre[2])};
+        V3 n;
+        const float dot2 = dot3(pc, pc);
+        if (MODE != MODE_GENERIC && in_fast_range(dot2)) {
+            const float len2 = sqrt_rn_fast(dot2);
+            const float yh2 = rcp_rn_fast(len2);
+            n = V3{div_rn_by_rcp(pc.x, len2, yh2), div_rn_by_rcp(pc.y, len2, yh2), div_rn_by_rcp(pc.z, len2, yh2)};
+        } else {
+            const float len2 = fsqrt(dot2);
+            n = V3{fdiv(pc.x, len2), fdiv(pc.y, len2), fdiv(pc.z, len2)};
+        }
+        r = ffma(n.x, 0.5f, 0.5f);   // :31 — n*0.5 is exact, so the FMA rounds like (n*0.5)+0.5
+        g = ffma(n.y, 0.5f, 0.5f);
+        bl = ffma(n.z, 0.5f, 0.5f);
         return true;
     }
-    col = make_float4(uvx, uvy, 0.0f, 1.0f);                      // :36
+    r = uvx;                                                                   // :36
+    g = uvy;
+    bl = 0.0f;
     return false;
 }
 
 // ---- 1 spp frame, 4 pixels per thread, one STG.128 of packed RGBA8 per thread -------------
 // Requires width % 4 == 0 (16 B aligned rows).  Block (32,8): a warp covers 128 consecutive
 // pixels of one row = 512 contiguous bytes of RGBA8.
-template <bool KEEP_F32, bool KEEP_HIT>
+template <int MODE>
 __global__ void __launch_bounds__(256) csmain_frame_vec4(const FrameK k, uint4 *__restrict__ rgba8,
                                                          float4 *__restrict__ f32, int4 *__restrict__ hit)
 {
@@ -69,64 +122,64 @@ __global__ void __launch_bounds__(256) csmain_frame_vec4(const FrameK k, uint4 *
     const uint32_t wq = k.width >> 2;
     if (xq >= wq || y >= k.height) return;                       // the guard Test.hlsl:39 lacks
 
-    const SphereTerms s = sphere_terms(k);
-    const float uvy = screen_uv(__uint2float_rn(y), k.div_y);
+    const float uvy = screen_uv<MODE>(__uint2float_rn(y), k.div_y, k.inv_div_y);
     uint32_t px8[4];
     int32_t hid[4];
     const size_t q = (size_t)y * wq + xq;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        const float uvx = screen_uv(__uint2float_rn(xq * 4u + i), k.div_x);
-        float4 col;
-        const bool h = csmain_shade(s, uvx, uvy, col);
-        px8[i] = pack_rgba8(col.x, col.y, col.z, col.w);
+        const float uvx = screen_uv<MODE>(__uint2float_rn(xq * 4u + i), k.div_x, k.inv_div_x);
+        float r, g, b;
+        const bool h = csmain_shade<MODE>(k, uvx, uvy, r, g, b);
+        px8[i] = pack_rgba8(r, g, b, 1.0f);
         hid[i] = h ? 0 : -1;
-        if (KEEP_F32) f32[q * 4 + i] = col;
+        if (f32) f32[q * 4 + i] = make_float4(r, g, b, 1.0f);
     }
     rgba8[q] = make_uint4(px8[0], px8[1], px8[2], px8[3]);
-    if (KEEP_HIT) hit[q] = make_int4(hid[0], hid[1], hid[2], hid[3]);
+    if (hit) hit[q] = make_int4(hid[0], hid[1], hid[2], hid[3]);
 }
 
 // ---- 1 spp frame, 1 pixel per thread (any width) ------------------------------------------
-template <bool KEEP_F32, bool KEEP_HIT>
+template <int MODE>
 __global__ void __launch_bounds__(256) csmain_frame_scalar(const FrameK k, uint32_t *__restrict__ rgba8,
                                                            float4 *__restrict__ f32, int32_t *__restrict__ hit)
 {
     const uint32_t x = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t y = blockIdx.y * blockDim.y + threadIdx.y;
     if (x >= k.width || y >= k.height) return;
-    const SphereTerms s = sphere_terms(k);
-    float4 col;
-    const bool h = csmain_shade(s, screen_uv(__uint2float_rn(x), k.div_x),
-                                screen_uv(__uint2float_rn(y), k.div_y), col);
+    float r, g, b;
+    const bool h = csmain_shade<MODE>(k, screen_uv<MODE>(__uint2float_rn(x), k.div_x, k.inv_div_x),
+                                      screen_uv<MODE>(__uint2float_rn(y), k.div_y, k.inv_div_y), r, g, b);
     const size_t i = (size_t)y * k.width + x;
-    rgba8[i] = pack_rgba8(col.x, col.y, col.z, col.w);
-    if (KEEP_F32) f32[i] = col;
-    if (KEEP_HIT) hit[i] = h ? 0 : -1;
+    rgba8[i] = pack_rgba8(r, g, b, 1.0f);
+    if (f32) f32[i] = make_float4(r, g, b, 1.0f);
+    if (hit) hit[i] = h ? 0 : -1;
 }
 
-template <bool F, bool H>
+static int pick_mode(const FrameK &k) { return k.fast ? (k.on_axis ? MODE_FAST_ON_AXIS : MODE_FAST) : MODE_GENERIC; }
+
+template <int MODE>
 static cudaError_t launch_frame_t(const FrameK &k, const Buffers &b, cudaStream_t s)
 {
     const dim3 block(32, 8);
     if ((k.width & 3u) == 0) {
         const dim3 grid(((k.width >> 2) + 31) / 32, (k.height + 7) / 8);
-        csmain_frame_vec4<F, H><<<grid, block, 0, s>>>(k, reinterpret_cast<uint4 *>(b.rgba8), b.f32,
+        csmain_frame_vec4<MODE><<<grid, block, 0, s>>>(k, reinterpret_cast<uint4 *>(b.rgba8), b.f32,
                                                        reinterpret_cast<int4 *>(b.hit));
     } else {
         const dim3 grid((k.width + 31) / 32, (k.height + 7) / 8);
-        csmain_frame_scalar<F, H><<<grid, block, 0, s>>>(k, b.rgba8, b.f32, b.hit);
+        csmain_frame_scalar<MODE><<<grid, block, 0, s>>>(k, b.rgba8, b.f32, b.hit);
     }
     return cudaGetLastError();
 }
 
 cudaError_t launch_csmain_frame(const FrameK &k, const Buffers &b, cudaStream_t s)
 {
-    const bool f = b.f32 != nullptr, h = b.hit != nullptr;
-    if (f && h) return launch_frame_t<true, true>(k, b, s);
-    if (f) return launch_frame_t<true, false>(k, b, s);
-    if (h) return launch_frame_t<false, true>(k, b, s);
-    return launch_frame_t<false, false>(k, b, s);
+    switch (pick_mode(k)) {
+    case MODE_FAST_ON_AXIS: return launch_frame_t<MODE_FAST_ON_AXIS>(k, b, s);
+    case MODE_FAST: return launch_frame_t<MODE_FAST>(k, b, s);
+    default: return launch_frame_t<MODE_GENERIC>(k, b, s);
+    }
 }
 
 // ---- multi-sample accumulation -------------------------------------------------------------
@@ -134,52 +187,81 @@ cudaError_t launch_csmain_frame(const FrameK &k, const Buffers &b, cudaStream_t 
 // accumulation buffer (32 B/pixel/launch) is amortised over n_samples, leaving the kernel
 // FP32-issue bound.  Block (32,8) keeps a warp on one row (coalesced 512 B accum access) and a
 // block on a 32x8 tile (hit/miss is spatially coherent, so few warps diverge).
-template <bool JITTER>
+// RNG: pcg3d keyed (pixel, sample, seed); the pixel and seed lanes of its first LCG step are
+// loop-invariant and hoisted.
+template <int MODE, bool JITTER>
 __global__ void __launch_bounds__(256) csmain_accumulate(const FrameK k, float4 *__restrict__ accum,
-                                                         uint32_t first_sample, uint32_t n_samples,
-                                                         uint32_t seed_hash)
+                                                         uint32_t first_sample, uint32_t n_samples, uint32_t seed)
 {
     const uint32_t x = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t y = blockIdx.y * blockDim.y + threadIdx.y;
     if (x >= k.width || y >= k.height) return;
-    const SphereTerms s = sphere_terms(k);
     const uint32_t pix = y * k.width + x;
     const float fx = __uint2float_rn(x), fy = __uint2float_rn(y);
+    // (x - 1) + m with m in [1,2) is the same real sum as x + (m - 1): one exact-rounded add.
+    const float fxm1 = fsub(fx, 1.0f), fym1 = fsub(fy, 1.0f);
+    const uint32_t vx0 = pix * 1664525u + 1013904223u;
+    const uint32_t vz0 = seed * 1664525u + 1013904223u;
+    const float uvx0 = screen_uv<MODE>(fx, k.div_x, k.inv_div_x), uvy0 = screen_uv<MODE>(fy, k.div_y, k.inv_div_y);
 
-    float4 sum = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    float sr = 0.0f, sg = 0.0f, sb = 0.0f, sa = 0.0f;
     for (uint32_t i = 0; i < n_samples; ++i) {
-        float px = fx, py = fy;
+        float uvx = uvx0, uvy = uvy0;
         if (JITTER) {
-            uint32_t st = rng_init(pix, first_sample + i, seed_hash);
-            px = fadd(fx, rng_float(st));
-            py = fadd(fy, rng_float(st));
+            uint32_t vx = vx0, vy = (first_sample + i) * 1664525u + 1013904223u, vz = vz0;
+            vx += vy * vz;
+            vy += vz * vx;
+            vz += vx * vy;
+            vx ^= vx >> 16;
+            vy ^= vy >> 16;
+            vz ^= vz >> 16;
+            vx += vy * vz;
+            vy += vz * vx;
+            uvx = screen_uv<MODE>(fadd(fxm1, bits_to_unit_plus_one(vx)), k.div_x, k.inv_div_x);
+            uvy = screen_uv<MODE>(fadd(fym1, bits_to_unit_plus_one(vy)), k.div_y, k.inv_div_y);
         }
-        float4 col;
-        csmain_shade(s, screen_uv(px, k.div_x), screen_uv(py, k.div_y), col);
-        sum.x = fadd(sum.x, col.x);
-        sum.y = fadd(sum.y, col.y);
-        sum.z = fadd(sum.z, col.z);
-        sum.w = fadd(sum.w, col.w);
+        float r, g, b;
+        const bool h = csmain_shade<MODE>(k, uvx, uvy, r, g, b);
+        sr = fadd(sr, r);
+        sg = fadd(sg, g);
+        if (MODE == MODE_GENERIC) {
+            sb = fadd(sb, b);
+            sa = fadd(sa, 1.0f);
+        } else if (h) {
+            sb = fadd(sb, b);   // a miss adds +0.0 to a sum that is never -0.0: identity
+        }
     }
+    // alpha: n_samples sequential additions of 1.0 are exact up to 2^24 (checked by the launcher)
+    if (MODE != MODE_GENERIC) sa = __uint2float_rn(n_samples);
     float4 acc = accum[pix];
-    acc.x = fadd(acc.x, sum.x);
-    acc.y = fadd(acc.y, sum.y);
-    acc.z = fadd(acc.z, sum.z);
-    acc.w = fadd(acc.w, sum.w);
+    acc.x = fadd(acc.x, sr);
+    acc.y = fadd(acc.y, sg);
+    acc.z = fadd(acc.z, sb);
+    acc.w = fadd(acc.w, sa);
     accum[pix] = acc;
+}
+
+template <int MODE>
+static cudaError_t launch_acc_t(const FrameK &k, float4 *accum, uint32_t first, uint32_t n, uint32_t seed,
+                                bool jitter, cudaStream_t s)
+{
+    const dim3 block(32, 8);
+    const dim3 grid((k.width + 31) / 32, (k.height + 7) / 8);
+    if (jitter) csmain_accumulate<MODE, true><<<grid, block, 0, s>>>(k, accum, first, n, seed);
+    else csmain_accumulate<MODE, false><<<grid, block, 0, s>>>(k, accum, first, n, seed);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_csmain_accumulate(const FrameK &k, float4 *accum, uint32_t first_sample,
                                      uint32_t n_samples, uint32_t seed, bool jitter, cudaStream_t s)
 {
-    const dim3 block(32, 8);
-    const dim3 grid((k.width + 31) / 32, (k.height + 7) / 8);
-    const uint32_t seed_hash = pcg_hash(seed);
-    if (jitter)
-        csmain_accumulate<true><<<grid, block, 0, s>>>(k, accum, first_sample, n_samples, seed_hash);
-    else
-        csmain_accumulate<false><<<grid, block, 0, s>>>(k, accum, first_sample, n_samples, seed_hash);
-    return cudaGetLastError();
+    int mode = pick_mode(k);
+    if (n_samples > (1u << 24)) mode = MODE_GENERIC;
+    switch (mode) {
+    case MODE_FAST_ON_AXIS: return launch_acc_t<MODE_FAST_ON_AXIS>(k, accum, first_sample, n_samples, seed, jitter, s);
+    case MODE_FAST: return launch_acc_t<MODE_FAST>(k, accum, first_sample, n_samples, seed, jitter, s);
+    default: return launch_acc_t<MODE_GENERIC>(k, accum, first_sample, n_samples, seed, jitter, s);
+    }
 }
 
 }  // namespace ptb

@@ -10,13 +10,24 @@
 namespace ptb {
 
 // Launch-uniform parameters of the CSMain-equivalent kernels (passed by value as a kernel
-// argument -> constant bank).  Literals of Test.hlsl:6,8,12,13 made runtime parameters.
+// argument -> constant bank).  Literals of Test.hlsl:6,8,12,13 made runtime parameters, plus
+// the launch-uniform subexpressions of Test.hlsl:16,19, which are evaluated ONCE ON THE DEVICE
+// (prepare_terms kernel, same *_rn intrinsics as the per-pixel code) when the context is created.
 struct FrameK {
     uint32_t width, height;
     float div_x, div_y;
     float cam[3];
     float centre[3];
     float radius;
+    // derived on the device:
+    float inv_div_x, inv_div_y;   // RN(1/div)
+    float oc[3];                  // :16 cam - centre
+    float c;                      // :19 dot(oc,oc) - r*r
+    float c4;                     // 4*c (exact scaling)
+    float neg2ocz;                // -(2*oc.z) (exact), used when on_axis
+    // launch-uniform validity of the short exact sequences (api.cu: derive_fast_flags)
+    uint32_t fast;                // 1: uv division / sqrt / rcp domains verified for these parameters
+    uint32_t on_axis;             // 1: oc.x == oc.y == 0 and oc.z is a moderate normal number
 };
 
 struct Buffers {
@@ -31,9 +42,17 @@ struct Buffers {
 };
 
 // kernels_csmain.cu
+cudaError_t prepare_terms(FrameK *k_host, cudaStream_t s);   // fills the derived fields (device-evaluated)
 cudaError_t launch_csmain_frame(const FrameK &k, const Buffers &b, cudaStream_t s);
 cudaError_t launch_csmain_accumulate(const FrameK &k, float4 *accum, uint32_t first_sample,
                                      uint32_t n_samples, uint32_t seed, bool jitter, cudaStream_t s);
+// selftest.cu — exhaustive proofs of the short exact sequences in ptb_math.cuh
+//   which: 0 = sqrt_rn_fast over [2^-20,2^24), 1 = rcp_rn_fast over [2^-12,2^12),
+//          2 = div_rn_uniform(v, D) for v in {0} U [2^-24, 2^17)
+cudaError_t selftest_exact(int which, float D, unsigned long long *mismatches, unsigned long long *tested,
+                           cudaStream_t s);
+bool uniform_divisor_verified(float D, cudaStream_t s);      // cached per (device, D)
+
 // kernels_image.cu
 cudaError_t image_tables_init();   // sRGB tables -> __constant__ (once per device)
 cudaError_t launch_resolve(const float4 *accum, uint32_t *out8, uint32_t n_pixels, uint32_t spp_total,

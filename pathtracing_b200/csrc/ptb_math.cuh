@@ -47,31 +47,89 @@ __device__ __forceinline__ uint32_t pack_rgba8(float r, float g, float b, float 
     return unorm8(r) | (unorm8(g) << 8) | (unorm8(b) << 16) | (unorm8(a) << 24);
 }
 
-// ---- RNG: PCG hash keyed on (pixel, sample, seed), PCG-RXS-M-XS-32 stream ----------------
-__host__ __device__ __forceinline__ uint32_t pcg_hash(uint32_t v)
+// ---- short exactly-rounded sequences ---------------------------------------------------------
+// Each is bit-identical to the IEEE intrinsic it replaces on the stated domain; the domains are
+// proven by exhaustion on the GPU (selftest.cu / experiments/exactmath.cu) and the callers
+// guarantee them (launch-uniform checks in api.cu, per-sample exponent guards in the kernels).
+
+__device__ __forceinline__ float mufu_rsq(float x)
 {
-    const uint32_t state = v * 747796405u + 2891336453u;
-    const uint32_t word = ((state >> ((state >> 28) + 4u)) ^ state) * 277803737u;
-    return (word >> 22) ^ word;
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float mufu_rcp(float x)
+{
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
 }
 
-__host__ __device__ __forceinline__ uint32_t rng_init(uint32_t pixel, uint32_t sample, uint32_t seed_hash)
+// == __fsqrt_rn(x) for every float x in [2^-20, 2^24) (exhaustive).
+__device__ __forceinline__ float sqrt_rn_fast(float x)
 {
-    // seed_hash = pcg_hash(seed) is launch-uniform and hoisted by the callers.
-    return pcg_hash(pixel + pcg_hash(sample + seed_hash));
+    const float r = mufu_rsq(x);
+    const float s = fmul(x, r), h = fmul(r, 0.5f);
+    return ffma(ffma(-s, s, x), h, s);
 }
 
-__device__ __forceinline__ uint32_t rng_next(uint32_t &state)
+// == __frcp_rn(y) for every float y in [2^-12, 2^12) (exhaustive).
+__device__ __forceinline__ float rcp_rn_fast(float y)
 {
-    state = state * 747796405u + 2891336453u;
-    const uint32_t word = ((state >> ((state >> 28) + 4u)) ^ state) * 277803737u;
-    return (word >> 22) ^ word;
+    const float q = mufu_rcp(y);
+    return ffma(ffma(-y, q, 1.0f), q, q);
 }
 
-// uniform in [0,1): 24 random bits scaled by 2^-24 (exact).
-__device__ __forceinline__ float rng_float(uint32_t &state)
+// v / y given yh = RN(1/y).  Two Markstein corrections: after the first the quotient is
+// faithful, so the second is correctly rounded for every v (no under/overflow) — provable.
+__device__ __forceinline__ float div_rn_by_rcp(float v, float y, float yh)
 {
-    return fmul(__uint2float_rn(rng_next(state) >> 8), 5.9604644775390625e-8f);
+    const float q0 = fmul(v, yh);
+    const float q1 = ffma(ffma(-q0, y, v), yh, q0);
+    return ffma(ffma(-q1, y, v), yh, q1);
 }
+
+// v / D for a launch-uniform D with Dh = RN(1/D): one correction.  Correct for every v in the
+// range that was verified exhaustively for this D when the context was created (selftest.cu).
+__device__ __forceinline__ float div_rn_uniform(float v, float D, float Dh)
+{
+    const float q0 = fmul(v, Dh);
+    return ffma(ffma(-q0, D, v), Dh, q0);
+}
+
+// true iff 2^-20 <= x < 2^24 (x a non-negative finite float): one IADD + one ISETP.
+__device__ __forceinline__ bool in_fast_range(float x)
+{
+    return (__float_as_uint(x) - 0x35800000u) < (0x4B800000u - 0x35800000u);
+}
+
+// ---- RNG: counter-based pcg3d (Jarzynski & Olano, "Hash Functions for GPU Rendering", JCGT 2020)
+// keyed (pixel index, sample index, seed).  No reference counterpart (Test.hlsl is deterministic);
+// this is the frozen spec shared with the CPU oracle.
+struct U3 {
+    uint32_t x, y, z;
+};
+
+__host__ __device__ __forceinline__ U3 pcg3d(uint32_t x, uint32_t y, uint32_t z)
+{
+    x = x * 1664525u + 1013904223u;
+    y = y * 1664525u + 1013904223u;
+    z = z * 1664525u + 1013904223u;
+    x += y * z;
+    y += z * x;
+    z += x * y;
+    x ^= x >> 16;
+    y ^= y >> 16;
+    z ^= z >> 16;
+    x += y * z;
+    y += z * x;
+    z += x * y;
+    return U3{x, y, z};
+}
+
+// 23 random bits -> float in [1,2) (exact); the callers subtract 1 or fold it into an add.
+__device__ __forceinline__ float bits_to_unit_plus_one(uint32_t v) { return __uint_as_float((v >> 9) | 0x3F800000u); }
+// uniform in [0,1): (v >> 9) * 2^-23 (exact).
+__device__ __forceinline__ float bits_to_unit(uint32_t v) { return fsub(bits_to_unit_plus_one(v), 1.0f); }
 
 }  // namespace ptb

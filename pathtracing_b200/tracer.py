@@ -13,7 +13,7 @@ from typing import Optional, Sequence
 import numpy as np
 
 from . import _lib
-from ._lib import (CFG_EXTERNAL_STREAM, CFG_KEEP_F32, CFG_KEEP_HIT_IDS, RESOLVE_BGRA, RESOLVE_SRGB,
+from ._lib import (CFG_EXTERNAL_STREAM, CFG_FORCE_IEEE, CFG_KEEP_F32, CFG_KEEP_HIT_IDS, RESOLVE_BGRA, RESOLVE_SRGB,
                    Config, PtbError, check)
 
 
@@ -27,7 +27,7 @@ class NativeTracer:
                  radius: Optional[float] = None,
                  seed: int = 0, max_depth: int = 0,
                  keep_f32: bool = False, keep_hit_ids: bool = False,
-                 stream: Optional[int] = None):
+                 stream: Optional[int] = None, force_ieee: bool = False):
         self._lib = _lib.load()
         self._ctx = C.c_void_p()
         cfg = Config()
@@ -44,11 +44,14 @@ class NativeTracer:
         cfg.seed = seed
         cfg.max_depth = max_depth
         cfg.flags = (CFG_KEEP_F32 if keep_f32 else 0) | (CFG_KEEP_HIT_IDS if keep_hit_ids else 0)
+        if force_ieee:
+            cfg.flags |= CFG_FORCE_IEEE
         if stream is not None:
             cfg.flags |= CFG_EXTERNAL_STREAM
             cfg.stream = stream
         self.config = cfg
         self.width, self.height = width, height
+        self._present_shape = None
         check(None, self._lib.ptb_create(C.byref(cfg), C.byref(self._ctx)))
 
     # -- lifecycle -----------------------------------------------------------------------
@@ -141,7 +144,7 @@ class NativeTracer:
         self._present_shape = (dst_h or self.height, dst_w or self.width)
 
     def read_present(self) -> np.ndarray:
-        h, w = self._present_shape
+        h, w = self._present_shape or (1, 1)     # no present yet: the native call reports PTB_ERR_STATE
         out = np.empty((h, w, 4), np.uint8)
         self._ck(self._lib.ptb_read_present(self._ctx, out.ctypes.data, out.strides[0]))
         return out
@@ -163,6 +166,17 @@ class NativeTracer:
         ms = C.c_float()
         self._ck(self._lib.ptb_timer_end(self._ctx, C.byref(ms)))
         return float(ms.value)
+
+    @property
+    def kernel_mode(self) -> int:
+        """0 = literal IEEE intrinsics, 1 = shortened exact sequences, 2 = + on-axis camera."""
+        return int(self._lib.ptb_kernel_mode(self._ctx))
+
+    def selftest_exact_math(self, which: int, divisor: float = 1.0):
+        """-> (mismatches, tested) of the on-device proof by exhaustion (see include/ptb200.h)."""
+        bad, n = C.c_uint64(), C.c_uint64()
+        self._ck(self._lib.ptb_selftest_exact_math(self._ctx, which, divisor, C.byref(bad), C.byref(n)))
+        return int(bad.value), int(n.value)
 
     @property
     def launch_count(self) -> int:

@@ -66,9 +66,9 @@ def main():
             "resolve": sha(O.resolve(acc, n)),
             "resolve_srgb_bgra": sha(O.resolve(acc, n, srgb=True, bgra=True)),
         }
-    raw, flt = O.rng_stream(12345, 6, 42, 8)
-    out["rng"] = {"pixel": 12345, "sample": 6, "seed": 42, "raw": [int(v) for v in raw],
-                  "float_bits": [int(np.float32(v).view(np.uint32)) for v in flt]}
+    keys = [(0, 0, 0), (1, 2, 3), (12345, 6, 42), (2073599, 63, 0), (0xFFFFFFFF, 0xFFFFFFFF, 0xFFFFFFFF)]
+    out["rng"] = {"pcg3d": [{"key": list(k), "out": list(O.pcg3d(*k)),
+                             "unit_bits": [int(O.bits_to_unit(w).view(np.uint32)) for w in O.pcg3d(*k)]} for k in keys]}
     p = O.frame_params(320, 180)
     img = O.csmain_frame(p)["rgba8"]
     out["present"] = {

@@ -284,3 +284,60 @@ def test_timer_and_launch_count():
             t.compute_frame()
         ms = t.timer_end()
         assert 0 < ms < 1000 and t.launch_count == 10
+
+
+# ---- the shortened exact sequences: proofs by exhaustion and A/B against the literal IEEE kernels ------
+def test_exact_math_proofs_by_exhaustion():
+    with NativeTracer(64, 36) as t:
+        bad, n = t.selftest_exact_math(0)                  # sqrt over [2^-20, 2^24)
+        assert bad == 0 and n == 44 * 2 ** 23
+        bad, n = t.selftest_exact_math(1)                  # reciprocal over [2^-12, 2^12)
+        assert bad == 0 and n == 24 * 2 ** 23
+        for d in (1080.0, 2160.0, 180.0, 36.0, 77.0, 3.0, 1234.567, -1080.0):
+            bad, n = t.selftest_exact_math(2, d)           # v / d for every float v in [2^-24, 2^17)
+            assert n == 41 * 2 ** 23
+            assert bad == 0, f"one-correction division by {d} disagrees with IEEE for {bad} inputs"
+
+
+def test_kernel_mode_selection():
+    with NativeTracer(1920, 1080) as t:
+        assert t.kernel_mode == 2                          # reference literals: fast + on-axis camera
+    with NativeTracer(1920, 1080, force_ieee=True) as t:
+        assert t.kernel_mode == 0
+    with NativeTracer(640, 360, cam=(0.25, -0.5, 2.0)) as t:
+        assert t.kernel_mode == 1                          # off-axis camera
+    with NativeTracer(64, 36, uv_div=(1e-9, 36)) as t:
+        assert t.kernel_mode == 0                          # |uv| unbounded for the sqrt/rcp domains
+    with NativeTracer(64, 36, cam=(0, 0, float("inf"))) as t:
+        assert t.kernel_mode == 0
+
+
+@pytest.mark.parametrize("kw", [dict(), dict(cam=(0.25, -0.5, 2.0), centre=(-0.3, 0.2, -0.4), radius=0.9),
+                                dict(uv_div=(777.0, 1234.567)), dict(cam=(0, 0, 40.0), radius=30.0),
+                                dict(cam=(0, 0, 1.0), radius=1.0), dict(cam=(0, 0, 0.25)), dict(radius=1e-3)],
+                         ids=["default", "moved", "odd_div", "huge_sphere", "camera_on_surface", "camera_inside", "tiny"])
+def test_fast_and_ieee_kernels_agree_bitwise(oracle, kw):
+    w, h = 1280, 720
+    ref = oracle.csmain_frame(oracle.frame_params(w, h, **kw))
+    ref_acc = oracle.accumulate(oracle.frame_params(w, h, **kw), 3, 5, 11, True)
+    outs = []
+    for force in (False, True):
+        with NativeTracer(w, h, keep_f32=True, keep_hit_ids=True, seed=11, force_ieee=force, **kw) as t:
+            t.compute_frame()
+            t.render_samples(3, 5)
+            outs.append((t.kernel_mode, t.read_f32(), t.read_hit_ids(), t.read_accum()))
+    assert outs[0][0] in (1, 2) and outs[1][0] == 0
+    for mode, f32, hit, acc in outs:
+        assert np.array_equal(hit, ref["hit"]), mode
+        assert eq_bits(f32, ref["f32"]), mode
+        assert eq_bits(acc, ref_acc), mode
+
+
+def test_generic_kernel_handles_degenerate_parameters(oracle):
+    """Parameters outside the proven domains run the literal kernels and still match the oracle (NaN-aware)."""
+    kw = dict(uv_div=(1e-3, 36.0), cam=(0.0, 0.0, 1e20))
+    ref = oracle.csmain_frame(oracle.frame_params(64, 36, **kw))
+    g = gpu_frame(64, 36, **kw)
+    assert np.array_equal(g["hit"], ref["hit"])
+    assert eq_bits(np.nan_to_num(g["f32"], nan=-7.0), np.nan_to_num(ref["f32"], nan=-7.0))
+    assert np.array_equal(g["rgba8"], ref["rgba8"])

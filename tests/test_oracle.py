@@ -107,36 +107,41 @@ def test_srgb8_monotone_and_endpoints(oracle):
     assert L.pto_srgb8(0.0031308) == round(12.92 * 0.0031308 * 255)
 
 
+def np_pcg3d(x, y, z):
+    """Independent numpy restatement of pcg3d (Jarzynski & Olano, JCGT 2020, listing 'pcg3d')."""
+    M = 0xFFFFFFFF
+    x = (x * 1664525 + 1013904223) & M
+    y = (y * 1664525 + 1013904223) & M
+    z = (z * 1664525 + 1013904223) & M
+    x = (x + y * z) & M; y = (y + z * x) & M; z = (z + x * y) & M
+    x ^= x >> 16; y ^= y >> 16; z ^= z >> 16
+    x = (x + y * z) & M; y = (y + z * x) & M; z = (z + x * y) & M
+    return x, y, z
+
+
 def test_rng_known_answers(oracle):
-    g = DIG["rng"]
-    raw, flt = oracle.rng_stream(g["pixel"], g["sample"], g["seed"], len(g["raw"]))
-    assert [int(v) for v in raw] == g["raw"]
-    assert [bits(v) for v in flt] == g["float_bits"]
-    assert np.all((flt >= 0) & (flt < 1))
-    # the float is exactly the top 24 bits * 2^-24
-    assert np.array_equal(flt, (raw >> 8).astype(np.float32) * np.float32(2.0 ** -24))
-    # independent numpy restatement of the PCG hash
-    def pcg(v):
-        v = np.uint64(v)
-        s = (v * np.uint64(747796405) + np.uint64(2891336453)) & np.uint64(0xFFFFFFFF)
-        w = (((s >> ((s >> np.uint64(28)) + np.uint64(4))) ^ s) * np.uint64(277803737)) & np.uint64(0xFFFFFFFF)
-        return int((w >> np.uint64(22)) ^ w)
-    for v in (0, 1, 12345, 0xFFFFFFFF):
-        assert oracle.lib().pto_pcg_hash(v) == pcg(v)
+    for g in DIG["rng"]["pcg3d"]:
+        out = oracle.pcg3d(*g["key"])
+        assert list(out) == g["out"] == list(np_pcg3d(*g["key"]))
+        assert [bits(oracle.bits_to_unit(w)) for w in out] == g["unit_bits"]
+    # unit mapping: exactly the top 23 bits * 2^-23, in [0,1)
+    for w in (0, 1, 511, 512, 0x80000000, 0xFFFFFFFF):
+        u = oracle.bits_to_unit(w)
+        assert u == np.float32(w >> 9) * np.float32(2.0 ** -23) and 0.0 <= u < 1.0
 
 
 def test_rng_uniformity(oracle):
-    # crude: jitter means over many pixels ~ 0.5, streams of neighbouring pixels decorrelated
-    L = oracle.lib()
-    import ctypes as C
-    vals = []
-    for pix in range(2000):
-        st = C.c_uint32(L.pto_rng_init(pix, 0, 0))
-        vals.append((L.pto_rng_float(C.byref(st)), L.pto_rng_float(C.byref(st))))
-    v = np.array(vals)
-    assert abs(v[:, 0].mean() - 0.5) < 0.03 and abs(v[:, 1].mean() - 0.5) < 0.03
-    assert abs(np.corrcoef(v[:-1, 0], v[1:, 0])[0, 1]) < 0.08
-    assert abs(np.corrcoef(v[:, 0], v[:, 1])[0, 1]) < 0.08
+    # crude: jitter means over many pixels ~ 0.5; neighbouring pixels / samples / axes decorrelated
+    v = np.array([[float(oracle.bits_to_unit(w)) for w in oracle.pcg3d(pix, 0, 0)[:2]] for pix in range(4000)])
+    assert abs(v[:, 0].mean() - 0.5) < 0.02 and abs(v[:, 1].mean() - 0.5) < 0.02
+    assert abs(np.corrcoef(v[:-1, 0], v[1:, 0])[0, 1]) < 0.06
+    assert abs(np.corrcoef(v[:, 0], v[:, 1])[0, 1]) < 0.06
+    s = np.array([[float(oracle.bits_to_unit(w)) for w in oracle.pcg3d(777, k, 5)[:2]] for k in range(4000)])
+    assert abs(s[:, 0].mean() - 0.5) < 0.02 and abs(np.corrcoef(s[:-1, 0], s[1:, 0])[0, 1]) < 0.06
+    # 8x8 stratification counts of one pixel's 4096 jitters are roughly flat
+    j = np.array([[float(oracle.bits_to_unit(w)) for w in oracle.pcg3d(31337, k, 1)[:2]] for k in range(4096)])
+    hist, _, _ = np.histogram2d(j[:, 0], j[:, 1], bins=8, range=[[0, 1], [0, 1]])
+    assert hist.min() > 30 and hist.max() < 100          # expectation 64
 
 
 @pytest.mark.parametrize("name", sorted(DIG["accum"]))
