@@ -57,56 +57,60 @@ def load_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
-         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons DURING the timed region, polled through NVML (the same counters
+    `nvidia-smi --query-gpu=clocks.sm,clocks.max.sm,clocks_event_reasons.*` prints) every 10 ms."""
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
     def __init__(self, index: int):
         self.index = index
-        self.proc = None
-        self.path = None
+        self.sm, self.bits, self.power = [], 0, []
+        self.mx = None
+        self._stop = None
+        self._thr = None
 
     def start(self):
         try:
-            fd, self.path = tempfile.mkstemp(suffix=".csv")
-            os.close(fd)
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.index)],
-                stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+            import threading
+            import pynvml
+            pynvml.nvmlInit()
+            # CUDA_VISIBLE_DEVICES-safe: resolve by the CUDA device's UUID/PCI bus id when possible
+            h = None
+            try:
+                import torch
+                bus = torch.cuda.get_device_properties(self.index).pci_bus_id
+                dom = torch.cuda.get_device_properties(self.index).pci_domain_id
+                dev = torch.cuda.get_device_properties(self.index).pci_device_id
+                h = pynvml.nvmlDeviceGetHandleByPciBusId(f"{dom:08x}:{bus:02x}:{dev:02x}.0")
+            except Exception:
+                h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            self._stop = threading.Event()
+
+            def loop():
+                while not self._stop.is_set():
+                    try:
+                        self.sm.append(float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)))
+                        self.bits |= int(pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                        self.power.append(pynvml.nvmlDeviceGetPowerUsage(h) / 1000.0)
+                    except Exception:
+                        pass
+                    self._stop.wait(0.01)
+            self._thr = threading.Thread(target=loop, daemon=True)
+            self._thr.start()
         except Exception:
-            self.proc = None
+            self._thr = None
 
     def stop(self):
-        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        if self.proc is None:
+        out = {"sm_mhz": None, "sm_max_mhz": self.mx, "reasons": [], "samples": 0, "power_w_max": None}
+        if self._thr is None:
             return out
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        try:
-            for line in open(self.path):
-                f = [x.strip() for x in line.split(",")]
-                if len(f) < 9:
-                    continue
-                try:
-                    sm.append(float(f[1]))
-                    mx.append(float(f[2]))
-                except ValueError:
-                    continue
-                for n, v in zip(names, f[5:9]):
-                    if v.lower().startswith("active"):
-                        reasons.add(n)
-            os.unlink(self.path)
-        except Exception:
-            pass
-        if sm:
-            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), samples=len(sm))
-        out["reasons"] = sorted(reasons)
+        self._stop.set()
+        self._thr.join(timeout=2)
+        if self.sm:
+            out.update(sm_mhz=statistics.median(self.sm), samples=len(self.sm))
+        if self.power:
+            out["power_w_max"] = max(self.power)
+        out["reasons"] = sorted(n for b, n in self.REASONS.items() if self.bits & b)
         return out
 
 
@@ -400,7 +404,7 @@ def run_b200(args):
             "gpu_launches": int(launches),
             "kernel_mode": t.kernel_mode,
             "clocks": {"sm_mhz": clk["sm_mhz"], "sm_max_mhz": clk["sm_max_mhz"], "reasons": clk["reasons"],
-                       "samples": clk["samples"]},
+                       "samples": clk["samples"], "power_w_max": clk["power_w_max"]},
             "merge_ms": merge_ms,
             "literal_frame": literal_frame,
         }
@@ -415,7 +419,7 @@ def run_b200(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))

@@ -34,6 +34,7 @@ __global__ void prepare_terms_kernel(FrameK *k)
     k->c = fsub(dot3(oc, oc), fmul(k->radius, k->radius));   // :19
     k->c4 = fmul(4.0f, k->c);
     k->neg2ocz = -fmul(2.0f, oc.z);
+    k->nzero = -0.0f;
 }
 
 cudaError_t prepare_terms(FrameK *k_host, cudaStream_t s)
@@ -110,6 +111,70 @@ __device__ __forceinline__ bool csmain_shade(const FrameK &k, float uvx, float u
     return false;
 }
 
+// Two samples per instruction (FFMA2/FMUL2/FADD2), fast modes only.  Lane i of every F2 is exactly
+// the scalar csmain_shade<MODE> evaluation of sample i: same ops, same order, one rounding each.
+// Negated lengths are carried (xn, lenN, denN) so the Markstein residuals fma(q, -y, v) need no
+// separate negation.  h0/h1 = per-lane hit.
+template <int MODE>
+__device__ __forceinline__ void csmain_shade2(const FrameK &k, F2 uvx, F2 uvy, F2 &r, F2 &g, F2 &bl, bool &h0, bool &h1)
+{
+    const F2 z = splat(k.nzero);   // run-time -0.0: keeps ptxas from fusing mul+add (see fmul2a)
+    // :10 — -(dot(v,v)) = RN(-(uvx^2 + uvy^2) - 1)
+    const F2 xn = ffma2(fadd2(fmul2a(uvx, uvx, z), fmul2a(uvy, uvy, z)), splat(-1.0f), splat(-1.0f));
+    const F2 lenN = neg_sqrt_rn_fast2(xn);
+    const F2 yh = rcp_rn_fast2_neg(lenN);                        // RN(1/len); d.z = -yh
+    const F2 dx = div_rn_by_rcp2(uvx, lenN, yh), dy = div_rn_by_rcp2(uvy, lenN, yh);
+    const F2 a = fadd2(fadd2(fmul2a(dx, dx, z), fmul2a(dy, dy, z)), fmul2a(yh, yh, z));   // :17
+    F2 b;                                                        // :18
+    if (MODE == MODE_FAST_ON_AXIS)
+        b = fmul2(splat(k.neg2ocz), yh);
+    else
+        b = fmul2(splat(2.0f), fadd2(fadd2(fmul2a(splat(k.oc[0]), dx, z), fmul2a(splat(k.oc[1]), dy, z)),
+                                     fmul2a(splat(-k.oc[2]), yh, z)));
+    const F2 disc = fadd2(fmul2a(b, b, z), fmul2a(a, splat(-k.c4), z));  // :21
+    h0 = disc.x > 0.0f;                                          // :24
+    h1 = disc.y > 0.0f;
+    r = uvx;                                                     // :36
+    g = uvy;
+    bl = splat(0.0f);
+    if (h0 || h1) {
+        // :27 — IEEE sqrt per lane (disc may be arbitrarily small); a missing lane gets a dummy argument
+        const F2 num = make_float2(fsub(-b.x, fsqrt(h0 ? disc.x : 1.0f)), fsub(-b.y, fsqrt(h1 ? disc.y : 1.0f)));
+        const F2 denN = fmul2(splat(-2.0f), a);                  // -(2a), 2a in (1,4)
+        const F2 t = div_rn_by_rcp2(num, denN, rcp_rn_fast2_neg(denN));
+        // :28-29 — pc = (cam + t*d) - centre, with t*d.z = RN(t*(-yh))
+        const F2 pcx = fadd2(fadd2(splat(k.cam[0]), fmul2a(t, dx, z)), splat(-k.centre[0]));
+        const F2 pcy = fadd2(fadd2(splat(k.cam[1]), fmul2a(t, dy, z)), splat(-k.centre[1]));
+        const F2 pcz = fadd2(fadd2(splat(k.cam[2]), fmul2a(t, neg2(yh), z)), splat(-k.centre[2]));
+        const F2 dot2 = fadd2(fadd2(fmul2a(pcx, pcx, z), fmul2a(pcy, pcy, z)), fmul2a(pcz, pcz, z));
+        F2 nx, ny, nz;
+        if (in_fast_range(dot2.x) && in_fast_range(dot2.y)) {
+            const F2 len2N = neg_sqrt_rn_fast2(neg2(dot2));
+            const F2 yh2 = rcp_rn_fast2_neg(len2N);
+            nx = div_rn_by_rcp2(pcx, len2N, yh2);
+            ny = div_rn_by_rcp2(pcy, len2N, yh2);
+            nz = div_rn_by_rcp2(pcz, len2N, yh2);
+        } else {   // outside the proven domain (or a dummy lane): literal IEEE per lane
+            const float l0 = fsqrt(dot2.x), l1 = fsqrt(dot2.y);
+            nx = make_float2(fdiv(pcx.x, l0), fdiv(pcx.y, l1));
+            ny = make_float2(fdiv(pcy.x, l0), fdiv(pcy.y, l1));
+            nz = make_float2(fdiv(pcz.x, l0), fdiv(pcz.y, l1));
+        }
+        const F2 rh = ffma2(nx, splat(0.5f), splat(0.5f));       // :31
+        const F2 gh = ffma2(ny, splat(0.5f), splat(0.5f));
+        const F2 bh = ffma2(nz, splat(0.5f), splat(0.5f));
+        r = make_float2(h0 ? rh.x : r.x, h1 ? rh.y : r.y);
+        g = make_float2(h0 ? gh.x : g.x, h1 ? gh.y : g.y);
+        bl = make_float2(h0 ? bh.x : 0.0f, h1 ? bh.y : 0.0f);
+    }
+}
+
+// Test.hlsl:7 for two samples of one axis.
+__device__ __forceinline__ F2 screen_uv2(F2 p, float div, float inv_div)
+{
+    return ffma2(div_rn_uniform2(p, splat(-div), splat(inv_div)), splat(2.0f), splat(-1.0f));
+}
+
 // ---- 1 spp frame, 4 pixels per thread, one STG.128 of packed RGBA8 per thread -------------
 // Requires width % 4 == 0 (16 B aligned rows).  Block (32,8): a warp covers 128 consecutive
 // pixels of one row = 512 contiguous bytes of RGBA8.
@@ -126,14 +191,32 @@ __global__ void __launch_bounds__(256) csmain_frame_vec4(const FrameK k, uint4 *
     uint32_t px8[4];
     int32_t hid[4];
     const size_t q = (size_t)y * wq + xq;
+    if (MODE == MODE_GENERIC) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const float uvx = screen_uv<MODE>(__uint2float_rn(xq * 4u + i), k.div_x, k.inv_div_x);
-        float r, g, b;
-        const bool h = csmain_shade<MODE>(k, uvx, uvy, r, g, b);
-        px8[i] = pack_rgba8(r, g, b, 1.0f);
-        hid[i] = h ? 0 : -1;
-        if (f32) f32[q * 4 + i] = make_float4(r, g, b, 1.0f);
+        for (int i = 0; i < 4; ++i) {
+            const float uvx = screen_uv<MODE>(__uint2float_rn(xq * 4u + i), k.div_x, k.inv_div_x);
+            float r, g, b;
+            const bool h = csmain_shade<MODE>(k, uvx, uvy, r, g, b);
+            px8[i] = pack_rgba8(r, g, b, 1.0f);
+            hid[i] = h ? 0 : -1;
+            if (f32) f32[q * 4 + i] = make_float4(r, g, b, 1.0f);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 4; i += 2) {   // two pixels per FP32x2 instruction
+            const F2 px = make_float2(__uint2float_rn(xq * 4u + i), __uint2float_rn(xq * 4u + i + 1));
+            F2 r, g, b;
+            bool h0, h1;
+            csmain_shade2<MODE>(k, screen_uv2(px, k.div_x, k.inv_div_x), splat(uvy), r, g, b, h0, h1);
+            px8[i] = pack_rgba8(r.x, g.x, b.x, 1.0f);
+            px8[i + 1] = pack_rgba8(r.y, g.y, b.y, 1.0f);
+            hid[i] = h0 ? 0 : -1;
+            hid[i + 1] = h1 ? 0 : -1;
+            if (f32) {
+                f32[q * 4 + i] = make_float4(r.x, g.x, b.x, 1.0f);
+                f32[q * 4 + i + 1] = make_float4(r.y, g.y, b.y, 1.0f);
+            }
+        }
     }
     rgba8[q] = make_uint4(px8[0], px8[1], px8[2], px8[3]);
     if (hit) hit[q] = make_int4(hid[0], hid[1], hid[2], hid[3]);
@@ -205,7 +288,40 @@ __global__ void __launch_bounds__(256) csmain_accumulate(const FrameK k, float4 
     const float uvx0 = screen_uv<MODE>(fx, k.div_x, k.inv_div_x), uvy0 = screen_uv<MODE>(fy, k.div_y, k.inv_div_y);
 
     float sr = 0.0f, sg = 0.0f, sb = 0.0f, sa = 0.0f;
-    for (uint32_t i = 0; i < n_samples; ++i) {
+    uint32_t i = 0;
+    if (MODE != MODE_GENERIC && JITTER) {
+        // two samples per iteration in FP32x2 lanes; the sums stay sequential in sample order
+        for (; i + 2 <= n_samples; i += 2) {
+            uint32_t ax = vx0, ay = (first_sample + i) * 1664525u + 1013904223u, az = vz0;
+            uint32_t bx = vx0, by = ay + 1664525u, bz = vz0;
+            ax += ay * az;
+            bx += by * bz;
+            ay += az * ax;
+            by += bz * bx;
+            az += ax * ay;
+            bz += bx * by;
+            ax ^= ax >> 16;
+            bx ^= bx >> 16;
+            ay ^= ay >> 16;
+            by ^= by >> 16;
+            az ^= az >> 16;
+            bz ^= bz >> 16;
+            ax += ay * az;
+            bx += by * bz;
+            ay += az * ax;
+            by += bz * bx;
+            const F2 px = fadd2(splat(fxm1), make_float2(bits_to_unit_plus_one(ax), bits_to_unit_plus_one(bx)));
+            const F2 py = fadd2(splat(fym1), make_float2(bits_to_unit_plus_one(ay), bits_to_unit_plus_one(by)));
+            F2 r, g, b;
+            bool h0, h1;
+            csmain_shade2<MODE>(k, screen_uv2(px, k.div_x, k.inv_div_x), screen_uv2(py, k.div_y, k.inv_div_y), r, g, b,
+                                h0, h1);
+            sr = fadd(fadd(sr, r.x), r.y);
+            sg = fadd(fadd(sg, g.x), g.y);
+            sb = fadd(fadd(sb, b.x), b.y);   // a miss adds +0.0 to a sum that is never -0.0: identity
+        }
+    }
+    for (; i < n_samples; ++i) {
         float uvx = uvx0, uvy = uvy0;
         if (JITTER) {
             uint32_t vx = vx0, vy = (first_sample + i) * 1664525u + 1013904223u, vz = vz0;
@@ -228,7 +344,7 @@ __global__ void __launch_bounds__(256) csmain_accumulate(const FrameK k, float4 
             sb = fadd(sb, b);
             sa = fadd(sa, 1.0f);
         } else if (h) {
-            sb = fadd(sb, b);   // a miss adds +0.0 to a sum that is never -0.0: identity
+            sb = fadd(sb, b);
         }
     }
     // alpha: n_samples sequential additions of 1.0 are exact up to 2^24 (checked by the launcher)

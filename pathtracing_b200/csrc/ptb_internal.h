@@ -25,6 +25,7 @@ struct FrameK {
     float c;                      // :19 dot(oc,oc) - r*r
     float c4;                     // 4*c (exact scaling)
     float neg2ocz;                // -(2*oc.z) (exact), used when on_axis
+    float nzero;                  // -0.0f at run time: the addend of the un-contractable packed multiply (ptb_math.cuh)
     // launch-uniform validity of the short exact sequences (api.cu: derive_fast_flags)
     uint32_t fast;                // 1: uv division / sqrt / rcp domains verified for these parameters
     uint32_t on_axis;             // 1: oc.x == oc.y == 0 and oc.z is a moderate normal number

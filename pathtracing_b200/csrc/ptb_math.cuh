@@ -80,17 +80,19 @@ __device__ __forceinline__ float rcp_rn_fast(float y)
     return ffma(ffma(-y, q, 1.0f), q, q);
 }
 
-// v / y given yh = RN(1/y).  Two Markstein corrections: after the first the quotient is
-// faithful, so the second is correctly rounded for every v (no under/overflow) — provable.
+// v / y given yh = RN(1/y): q0 = RN(v*yh) (always within 1 ulp), then ONE Markstein correction.
+// Correctly rounded for EVERY pair of binary32 significands — proven by exhaustion over all 2^46
+// pairs on a B200 (experiments/div3_exhaustive.cu, 57.5 s; profiles/r01_div3_exhaustive.txt), and
+// exact scaling by powers of two extends that to all normal operands whose residual v - q0*y does
+// not underflow (|v| >= 2^-100 or v == 0; the callers' operands are screen/unit-sphere sized).
 __device__ __forceinline__ float div_rn_by_rcp(float v, float y, float yh)
 {
     const float q0 = fmul(v, yh);
-    const float q1 = ffma(ffma(-q0, y, v), yh, q0);
-    return ffma(ffma(-q1, y, v), yh, q1);
+    return ffma(ffma(-q0, y, v), yh, q0);
 }
 
-// v / D for a launch-uniform D with Dh = RN(1/D): one correction.  Correct for every v in the
-// range that was verified exhaustively for this D when the context was created (selftest.cu).
+// v / D for a launch-uniform D with Dh = RN(1/D): the same one-correction division; additionally
+// re-verified for this D over every float v in [2^-24, 2^17) when the context is created (selftest.cu).
 __device__ __forceinline__ float div_rn_uniform(float v, float D, float Dh)
 {
     const float q0 = fmul(v, Dh);
@@ -131,5 +133,57 @@ __host__ __device__ __forceinline__ U3 pcg3d(uint32_t x, uint32_t y, uint32_t z)
 __device__ __forceinline__ float bits_to_unit_plus_one(uint32_t v) { return __uint_as_float((v >> 9) | 0x3F800000u); }
 // uniform in [0,1): (v >> 9) * 2^-23 (exact).
 __device__ __forceinline__ float bits_to_unit(uint32_t v) { return fsub(bits_to_unit_plus_one(v), 1.0f); }
+
+}  // namespace ptb
+
+// ---- packed FP32x2 forms (Blackwell FFMA2 / FMUL2 / FADD2: two IEEE-rounded lanes per issue slot)
+// The CSMain kernels are issue-bound, so evaluating two samples per instruction halves the FP
+// issue pressure without changing any lane's rounding (each lane is an independent *_rn op).
+namespace ptb {
+
+typedef float2 F2;
+
+__device__ __forceinline__ F2 splat(float s) { return make_float2(s, s); }
+__device__ __forceinline__ F2 fmul2(F2 a, F2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ F2 fadd2(F2 a, F2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ F2 ffma2(F2 a, F2 b, F2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ F2 neg2(F2 a) { return make_float2(-a.x, -a.y); }
+// A multiply whose result feeds an ADD.  ptxas (12.9) contracts mul.rn.f32x2 + add.rn.f32x2 into one
+// FFMA2 — unlike the scalar *_rn forms it does not honour .rn as "do not fuse", even with -fmad=false,
+// and it also folds fma(a,b,-0.0) back to a multiply first.  An FMA whose addend is a RUN-TIME -0.0
+// (FrameK::nzero) is opaque to it and rounds exactly like the multiply: RN(a*b + (-0)) == RN(a*b),
+// signed zeros included.  Same issue cost as FMUL2.
+__device__ __forceinline__ F2 fmul2a(F2 a, F2 b, F2 nzero) { return __ffma2_rn(a, b, nzero); }
+
+// Returns -sqrt(x) given xn = -x (x in [2^-20, 2^24)): the negated length is what every later
+// correction step consumes (fma(q, -len, v)), so no separate negations are issued.
+//   s = x*r, e = x - s*s, sqrt = s + e*(r/2)   ==>   -sqrt = fma(sn*sn - x, r/2, sn), sn = -s
+__device__ __forceinline__ F2 neg_sqrt_rn_fast2(F2 xn)
+{
+    const F2 r = make_float2(mufu_rsq(-xn.x), mufu_rsq(-xn.y));
+    const F2 sn = fmul2(xn, r), h = fmul2(r, splat(0.5f));
+    return ffma2(ffma2(sn, sn, xn), h, sn);
+}
+
+// RN(1/y) given yn = -y (y in [2^-12, 2^12)).
+__device__ __forceinline__ F2 rcp_rn_fast2_neg(F2 yn)
+{
+    const F2 q = make_float2(mufu_rcp(-yn.x), mufu_rcp(-yn.y));
+    return ffma2(ffma2(yn, q, splat(1.0f)), q, q);
+}
+
+// v / y given yn = -y and yh = RN(1/y): one Markstein correction (see div_rn_by_rcp).
+__device__ __forceinline__ F2 div_rn_by_rcp2(F2 v, F2 yn, F2 yh)
+{
+    const F2 q0 = fmul2(v, yh);
+    return ffma2(ffma2(q0, yn, v), yh, q0);
+}
+
+// v / D for the launch-uniform D given Dn = -D and Dh = RN(1/D): one correction (see div_rn_uniform).
+__device__ __forceinline__ F2 div_rn_uniform2(F2 v, F2 Dn, F2 Dh)
+{
+    const F2 q0 = fmul2(v, Dh);
+    return ffma2(ffma2(q0, Dn, v), Dh, q0);
+}
 
 }  // namespace ptb
