@@ -101,6 +101,12 @@ int ptb_wait(ptb_context *ctx);
  * Renderer.cs:1086-1089).  pitch_bytes = host row stride; 0 means tightly packed.
  * These synchronise the context's stream. */
 int ptb_read_rgba8(ptb_context *ctx, void *host_dst, size_t pitch_bytes);
+/* Non-blocking variant: the copy is queued behind the work submitted so far on a separate copy
+ * stream, so the next frame's kernels overlap the PCIe transfer (the reference overlaps compute
+ * with presentation the same way: the graphics queue consumes frame k while the compute queue may
+ * start k+1).  host_dst should be page-locked; it is valid after the next ptb_wait.  The next
+ * writer of the image (ptb_compute_frame / ptb_resolve) is ordered after the copy. */
+int ptb_read_rgba8_async(ptb_context *ctx, void *host_dst, size_t pitch_bytes);
 int ptb_read_f32(ptb_context *ctx, float *host_dst, size_t pitch_bytes);      /* needs KEEP_F32 */
 int ptb_read_hit_ids(ptb_context *ctx, int32_t *host_dst, size_t pitch_bytes);/* needs KEEP_HIT_IDS */
 

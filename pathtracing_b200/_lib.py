@@ -86,6 +86,7 @@ SIGNATURES = {
     "ptb_compute_frame": (C.c_int, [_CTX]),
     "ptb_wait": (C.c_int, [_CTX]),
     "ptb_read_rgba8": (C.c_int, [_CTX, C.c_void_p, C.c_size_t]),
+    "ptb_read_rgba8_async": (C.c_int, [_CTX, C.c_void_p, C.c_size_t]),
     "ptb_read_f32": (C.c_int, [_CTX, C.c_void_p, C.c_size_t]),
     "ptb_read_hit_ids": (C.c_int, [_CTX, C.c_void_p, C.c_size_t]),
     "ptb_device_rgba8": (C.c_void_p, [_CTX]),

@@ -178,6 +178,9 @@ int ptb_create(const ptb_config *cfg, ptb_context **out_ctx)
     }
     if ((e = cudaEventCreate(&c->ev0)) != cudaSuccess) return bail(e, "cudaEventCreate");
     if ((e = cudaEventCreate(&c->ev1)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    if ((e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate(copy)");
+    if ((e = cudaEventCreateWithFlags(&c->ev_img_ready, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    if ((e = cudaEventCreateWithFlags(&c->ev_copy_done, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
     if ((e = ptb::image_tables_init()) != cudaSuccess) return bail(e, "image_tables_init");
     if ((e = ptb::prepare_terms(&c->k, c->stream)) != cudaSuccess) return bail(e, "prepare_terms");
     derive_fast_flags(c);
@@ -202,6 +205,12 @@ int ptb_destroy(ptb_context *ctx)
     free_buffers(ctx);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->copy_stream) {
+        cudaStreamSynchronize(ctx->copy_stream);
+        cudaStreamDestroy(ctx->copy_stream);
+    }
+    if (ctx->ev_img_ready) cudaEventDestroy(ctx->ev_img_ready);
+    if (ctx->ev_copy_done) cudaEventDestroy(ctx->ev_copy_done);
     if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
     return PTB_OK;
@@ -212,6 +221,7 @@ const char *ptb_last_error(const ptb_context *ctx) { return ctx ? ctx->err.c_str
 int ptb_compute_frame(ptb_context *ctx)
 {
     PTB_ENTER(ctx);
+    if (ctx->copy_pending) PTB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_copy_done, 0));
     PTB_CUDA(ctx, ptb::launch_csmain_frame(ctx->k, ctx->buf, ctx->stream));
     ctx->launches += 1;
     return PTB_OK;
@@ -221,6 +231,26 @@ int ptb_wait(ptb_context *ctx)
 {
     PTB_ENTER(ctx);
     PTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->copy_pending) {
+        PTB_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
+        ctx->copy_pending = false;
+    }
+    return PTB_OK;
+}
+
+int ptb_read_rgba8_async(ptb_context *ctx, void *host_dst, size_t pitch_bytes)
+{
+    PTB_ENTER(ctx);
+    if (!host_dst) return fail(ctx, PTB_ERR_INVALID, "ptb_read_rgba8_async: host destination is NULL");
+    const size_t row = (size_t)ctx->cfg.width * 4;
+    if (pitch_bytes == 0) pitch_bytes = row;
+    if (pitch_bytes < row) return fail(ctx, PTB_ERR_INVALID, "ptb_read_rgba8_async: pitch %zu < row size %zu", pitch_bytes, row);
+    PTB_CUDA(ctx, cudaEventRecord(ctx->ev_img_ready, ctx->stream));
+    PTB_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_img_ready, 0));
+    PTB_CUDA(ctx, cudaMemcpy2DAsync(host_dst, pitch_bytes, ctx->buf.rgba8, row, row, ctx->cfg.height,
+                                    cudaMemcpyDeviceToHost, ctx->copy_stream));
+    PTB_CUDA(ctx, cudaEventRecord(ctx->ev_copy_done, ctx->copy_stream));
+    ctx->copy_pending = true;
     return PTB_OK;
 }
 
@@ -297,6 +327,7 @@ int ptb_resolve(ptb_context *ctx, uint32_t flags)
     if (flags & ~(PTB_RESOLVE_SRGB | PTB_RESOLVE_BGRA)) return fail(ctx, PTB_ERR_INVALID, "ptb_resolve: unknown flags 0x%x", flags);
     if (!ctx->buf.accum || ctx->accum_spp == 0)
         return fail(ctx, PTB_ERR_STATE, "ptb_resolve: nothing accumulated (0 spp)");
+    if (ctx->copy_pending) PTB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_copy_done, 0));
     PTB_CUDA(ctx, ptb::launch_resolve(ctx->buf.accum, ctx->buf.rgba8, (uint32_t)n_pixels(ctx), ctx->accum_spp, flags,
                                       ctx->stream));
     ctx->launches += 1;

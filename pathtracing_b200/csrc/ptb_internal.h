@@ -70,6 +70,11 @@ struct ptb_context {
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // asynchronous image read-back (ptb_read_rgba8_async): a copy stream ordered after the producer
+    // by ev_img_ready; the next writer of the image waits on ev_copy_done.
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_img_ready = nullptr, ev_copy_done = nullptr;
+    bool copy_pending = false;
     bool timer_open = false;
     uint32_t accum_spp = 0;
     uint64_t launches = 0;

@@ -94,6 +94,10 @@ class NativeTracer:
         self._ck(self._lib.ptb_read_rgba8(self._ctx, out.ctypes.data, out.strides[0]))
         return out
 
+    def read_rgba8_async(self, host_ptr: int, pitch_bytes: int = 0) -> None:
+        """Queue a device->host copy of the image into (page-locked) host memory; valid after wait()."""
+        self._ck(self._lib.ptb_read_rgba8_async(self._ctx, host_ptr, pitch_bytes))
+
     def read_f32(self, out: Optional[np.ndarray] = None) -> np.ndarray:
         if out is None:
             out = np.empty((self.height, self.width, 4), np.float32)

@@ -341,3 +341,27 @@ def test_generic_kernel_handles_degenerate_parameters(oracle):
     assert np.array_equal(g["hit"], ref["hit"])
     assert eq_bits(np.nan_to_num(g["f32"], nan=-7.0), np.nan_to_num(ref["f32"], nan=-7.0))
     assert np.array_equal(g["rgba8"], ref["rgba8"])
+
+
+def test_async_readback_is_ordered_and_matches_sync(oracle):
+    import ctypes
+    w, h = 640, 360
+    bufs = [np.zeros((h, w, 4), np.uint8) for _ in range(3)]
+    with NativeTracer(w, h, seed=2) as t:
+        t.compute_frame()
+        t.read_rgba8_async(bufs[0].ctypes.data)            # frame 0: the literal CSMain image
+        t.render_samples(0, 4)
+        t.resolve()                                        # must not overwrite the image before copy 0 finished
+        t.read_rgba8_async(bufs[1].ctypes.data)
+        t.render_samples(4, 4)
+        t.resolve(srgb=True)
+        t.read_rgba8_async(bufs[2].ctypes.data)
+        t.wait()
+        sync = t.read_rgba8()
+    p = oracle.frame_params(w, h)
+    assert np.array_equal(bufs[0], oracle.csmain_frame(p)["rgba8"])
+    acc = oracle.accumulate(p, 0, 4, 2, True)
+    assert np.array_equal(bufs[1], oracle.resolve(acc, 4))
+    acc = oracle.accumulate(p, 4, 4, 2, True, accum=acc)
+    assert np.array_equal(bufs[2], oracle.resolve(acc, 8, srgb=True))
+    assert np.array_equal(sync, bufs[2])
