@@ -183,6 +183,7 @@ def run_b200(args):
     import torch
     import torch.distributed as dist
     from pathtracing_b200 import NativeTracer
+    from pathtracing_b200.dist import GpuEngine, ShardedRenderer
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -200,49 +201,35 @@ def run_b200(args):
     n_pix = W * H
     strong = args.workload == "c5"
     literal = args.workload == "frame"
-    spp_rank = spp // world if strong else spp         # samples per pixel per rank per step
+    # samples per pixel per STEP over all ranks: c2 scales with the world (weak), c5 is fixed (strong)
+    spp_step = spp if (strong or literal) else spp * world
     K, Wm = args.steps, args.warmup
-
-    stream = torch.cuda.Stream(device=dev)
-    accum = torch.zeros((H, W, 4), dtype=torch.float32, device=dev)
-    host_img = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(2)]   # double-buffered
-    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)   # > 126 MB L2
-
-    t = NativeTracer(W, H, device=local, seed=0, stream=stream.cuda_stream)
-    t.set_accum_buffer(accum.data_ptr())
     peaks = load_peaks()
 
-    def first_sample(step):
-        # disjoint, absolute sample indices: step-major, rank-minor
-        return (step * world + rank) * spp_rank
-
-    def merge_and_resolve(total_spp):
-        """NCCL reduce of the per-rank accumulation buffers over NVLink, resolve on rank 0."""
-        if world > 1:
-            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
-            if rank != 0:
-                accum.zero_()          # root keeps the running total, the others the delta since the last merge
-        if rank == 0:
-            t.set_accum_spp(total_spp)
-            t.resolve()
-
-    def step_device(step):
-        if literal:
-            t.compute_frame()
-            return
-        t.render_samples(first_sample(step), spp_rank, jitter=True)
-        if strong:
-            merge_and_resolve((step + 1) * spp)
-        elif world == 1:
-            t.resolve()
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+    stream = torch.cuda.Stream(device=dev)
+    host_img = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(2)]   # double-buffered
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)                   # > 126 MB L2
 
     with torch.cuda.stream(stream):
-        # ---- device-timed value -----------------------------------------------------------------
+        eng = GpuEngine(W, H, local, seed=0, stream=stream)
+        t = eng.tracer
+        sr = ShardedRenderer(eng, mode=args.shard)
+        merge_every_step = strong or world == 1        # c2 at N>1: one merge for the whole progressive render
+
+        def barrier():
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+
+        def step_device(step):
+            if literal:
+                t.compute_frame()
+                return
+            sr.render(step * spp_step, spp_step)
+            if merge_every_step:
+                sr.merge(0)
+
+        # ---- device-timed value ---------------------------------------------------------------------
         for s in range(Wm):
             step_device(s)
         barrier()
@@ -260,18 +247,14 @@ def run_b200(args):
             if literal:
                 t.compute_frame()
             else:
-                t.render_samples(first_sample(Wm + s), spp_rank, jitter=True)
+                sr.render((Wm + s) * spp_step, spp_step)
             kern_ev[s][1].record(stream)
-            if not literal:
-                if strong:
-                    merge_and_resolve((Wm + s + 1) * spp)
-                elif world == 1:
-                    t.resolve()
+            if not literal and merge_every_step:
+                sr.merge(0)
             ev[s][1].record(stream)
-        # c2 at N>1: one merge + resolve for the whole progressive render, timed
         ev[K][0].record(stream)
-        if not literal and not strong and world > 1:
-            merge_and_resolve((Wm + K) * spp * world)
+        if not literal and not merge_every_step:
+            sr.merge(0)                                # timed: NCCL reduce over NVLink + resolve on rank 0
         ev[K][1].record(stream)
         barrier()
         launches = t.launch_count - launches0
@@ -281,76 +264,78 @@ def run_b200(args):
         total_ms = sum(step_ms) + merge_ms
         clk = clocks.stop() if rank == 0 else None
 
-        # ---- e2e: C ABI with host buffers ---------------------------------------------------------
+        # ---- e2e: C ABI with host buffers, image delivered to pinned host memory EVERY step -------------
         def step_e2e(step):
             if literal:
                 t.compute_frame()
             else:
-                t.render_samples(first_sample(step), spp_rank, jitter=True)
-                if world > 1:
-                    merge_and_resolve((step + 1) * spp * (1 if strong else world))
-                else:
-                    t.resolve()
+                sr.render(step * spp_step, spp_step)
+                sr.merge(0)
             if rank == 0:
-                # D2H of this step's frame into pinned host memory, queued on the library's copy stream so
-                # the PCIe transfer overlaps the next step's kernels; every copy completes inside the timed region
+                # queued on the library's copy stream: the PCIe transfer overlaps the next step's kernels,
+                # and every copy completes inside the timed region
                 t.read_rgba8_async(host_img[step & 1].data_ptr(), W * 4)
         e2e_steps = max(3, min(K, 50))
+        base = Wm + K
         for s in range(Wm):
-            step_e2e(2 * (Wm + K) + s)
+            step_e2e(base + s)
+        t.wait()
         barrier()
         t0 = time.perf_counter()
         for s in range(e2e_steps):
-            step_e2e(3 * (Wm + K) + s)
-        t.wait()                      # last frame has landed in host memory
+            step_e2e(base + Wm + s)
+        t.wait()                                       # last frame has landed in host memory
         barrier()
         e2e_s = time.perf_counter() - t0
 
-    # ---- the literal reference frame (1 spp, RGBA8) as a secondary line: HBM-write / launch bound ----
-    literal_frame = None
-    if rank == 0 and world == 1 and not literal:
-        with NativeTracer(W, H, device=local, stream=stream.cuda_stream) as tf, torch.cuda.stream(stream):
-            for _ in range(5):
-                tf.compute_frame()
-            torch.cuda.synchronize()
-            n_bb = 200
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record(stream)
-            for _ in range(n_bb):
-                tf.compute_frame()
-            b.record(stream)
-            torch.cuda.synchronize()
-            bb_ms = a.elapsed_time(b) / n_bb
-            iso = []
-            for i in range(20):
-                flush.fill_(i)
+        # ---- the literal reference frame (1 spp, RGBA8) as a secondary line ------------------------------
+        literal_frame = None
+        if rank == 0 and world == 1 and not literal:
+            with NativeTracer(W, H, device=local, stream=stream.cuda_stream) as tf:
+                for _ in range(5):
+                    tf.compute_frame()
+                torch.cuda.synchronize()
+                n_bb = 200
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 a.record(stream)
-                tf.compute_frame()
+                for _ in range(n_bb):
+                    tf.compute_frame()
                 b.record(stream)
                 torch.cuda.synchronize()
-                iso.append(a.elapsed_time(b))
-            iso_ms = statistics.median(iso)
-            bytes_frame = RGBA8_BYTES_PER_PIXEL * n_pix
-            literal_frame = {
-                "workload": WORKLOADS["frame"]["name"], "ms_per_frame_back_to_back": bb_ms,
-                "ms_per_frame_l2_flushed": iso_ms, "msamples_per_s_back_to_back": n_pix / (bb_ms * 1e-3) / 1e6,
-                "roofline": {"kernel": "csmain_frame_vec4", "bound": "hbm", "unit": "GB/s",
-                             "achieved": bytes_frame / (iso_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"],
-                             "frac": bytes_frame / (iso_ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
-                             "algorithmic_bytes_per_launch": bytes_frame,
-                             "note": "8.3 MB write per launch: ~1.3 us at the HBM roof, i.e. launch-latency scale"}}
+                bb_ms = a.elapsed_time(b) / n_bb
+                iso = []
+                for i in range(20):
+                    flush.fill_(i)
+                    a.record(stream)
+                    tf.compute_frame()
+                    b.record(stream)
+                    torch.cuda.synchronize()
+                    iso.append(a.elapsed_time(b))
+                iso_ms = statistics.median(iso)
+                bytes_frame = RGBA8_BYTES_PER_PIXEL * n_pix
+                literal_frame = {
+                    "workload": WORKLOADS["frame"]["name"], "ms_per_frame_back_to_back": bb_ms,
+                    "ms_per_frame_l2_flushed": iso_ms, "msamples_per_s_back_to_back": n_pix / (bb_ms * 1e-3) / 1e6,
+                    "roofline": {"kernel": "csmain_frame_vec4", "bound": "fp32 (HBM figure for reference)", "unit": "GB/s",
+                                 "achieved": bytes_frame / (iso_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"],
+                                 "frac": bytes_frame / (iso_ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
+                                 "algorithmic_bytes_per_launch": bytes_frame,
+                                 "note": "8.3 MB written per launch = 1.3 us at the HBM roof; ~40 exact-rounded FP32 "
+                                         "instructions per pixel make even the 1-spp frame FP32-issue bound"}}
 
     tot = torch.tensor([total_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tot, op=dist.ReduceOp.MAX)
     total_ms, e2e_ms = float(tot[0]), float(tot[1])
 
-    samples_per_step = n_pix * spp_rank * world            # all ranks
+    samples_per_step = n_pix * spp_step                  # all ranks together
     value = samples_per_step * K / (total_ms * 1e-3) / 1e6
     e2e_value = samples_per_step * e2e_steps / (e2e_ms * 1e-3) / 1e6
+    spp_rank = spp_step / world if args.shard == "samples" else spp_step   # per-pixel samples one launch evaluates
+    pix_rank = n_pix if args.shard == "samples" else n_pix / world
 
     if rank == 0:
-        # ---- roofline of the dominant kernel, from the live per-launch event durations -------------
+        # ---- roofline of the dominant kernel, from the live per-launch event durations -------------------
         k_ms = statistics.mean(kern_ms)
         if literal:
             alg = RGBA8_BYTES_PER_PIXEL * n_pix
@@ -361,23 +346,23 @@ def run_b200(args):
                     "algorithmic_bytes_per_launch": alg, "launch_ms": k_ms}
         else:
             fp32_peak = 148 * 128 * 2 * peaks["sm_max_mhz"] * 1e6 / 1e12     # TFLOP/s at max SM clock
-            flops = FLOP_PER_SAMPLE * n_pix * spp_rank
+            flops = FLOP_PER_SAMPLE * pix_rank * spp_rank
             achieved = flops / (k_ms * 1e-3) / 1e12
             roof = {"kernel": "csmain_accumulate", "bound": "fp32", "achieved": achieved, "peak": fp32_peak,
                     "unit": "TFLOP/s", "frac": achieved / fp32_peak, "traffic": None,
                     "peak_source": f"148 SM x 128 lanes x 2 x sm_max_mhz from MEASURED_PEAKS.json ({peaks['source']}); "
-                                   "FP32 CUDA-core issue bound, no tensor/HBM roof applies (SURVEY.md §8d)",
+                                   "FP32 CUDA-core (FMA port) bound: no tensor or HBM roof applies (SURVEY.md 8d, DESIGN.md 4)",
                     "algorithmic_flops_per_launch": flops, "launch_ms": k_ms,
-                    "hbm_bytes_per_launch": ACCUM_BYTES_PER_PIXEL * n_pix,
-                    "hbm_frac": ACCUM_BYTES_PER_PIXEL * n_pix / (k_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]}
+                    "hbm_bytes_per_launch": ACCUM_BYTES_PER_PIXEL * pix_rank,
+                    "hbm_frac": ACCUM_BYTES_PER_PIXEL * pix_rank / (k_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]}
         tr = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tr):
+        if os.path.exists(tr) and world == 1 and args.workload == "c2":
             try:
                 roof["traffic"] = json.load(open(tr)).get(roof["kernel"])
             except Exception:
                 pass
 
-        # ---- CPU baseline on this box's host cores (bounded sample) ----------------------------------
+        # ---- CPU baseline on this box's host cores (bounded sample) ------------------------------------------
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             spp_s = 1 if literal else max(1, min(spp, args.cpu_spp))
@@ -385,23 +370,28 @@ def run_b200(args):
             cpu = {"value": ms, "unit": "Msamples/s", "cores": threads, "kind": "port",
                    "sample": f"{W}x{H}, {spp_s} of {spp} spp per step x 5 steps, OpenMP over rows, {cpu_model()}"}
 
-        d2h = n_pix * 4
+        if world == 1:
+            sharding = "none"
+        elif args.shard == "tiles":
+            sharding = "interleaved image rows per rank; merge = NCCL reduce of disjoint RGBA8 rows"
+        else:
+            sharding = "disjoint sample ranges per rank; merge = NCCL reduce(sum) of float4 accumulation buffers + resolve on rank 0"
+        sharding += "" if world == 1 else (", every step" if merge_every_step else ", once, inside the timed total")
         line = {
             "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": K, "warmup": Wm,
             "ms_per_step": total_ms / K, "ms_per_frame": total_ms / K, "higher_is_better": True,
             "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": wl["name"], "width": W, "height": H, "spp_per_step_per_rank": spp_rank,
-                       "spp_per_step_total": spp_rank * world, "seed": 0, "jitter": not literal,
-                       "sharding": ("none" if world == 1 else ("sample ranges, NCCL reduce+resolve every step" if strong else
-                                    "sample ranges, one NCCL reduce+resolve inside the timed total")),
+            "config": {"workload": wl["name"], "width": W, "height": H, "spp_per_step_total": spp_step,
+                       "spp_per_step_per_rank": spp_rank, "seed": 0, "jitter": not literal, "sharding": sharding,
                        "l2": "flushed between timed steps (256 MB fill, untimed)",
                        "timing": "per-step CUDA events on the launching stream, summed; max over ranks"},
             "roofline": roof,
             "cpu_baseline": cpu,
-            "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": 64, "d2h_bytes_per_step": d2h,
+            "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": 128, "d2h_bytes_per_step": n_pix * 4,
                     "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps,
-                    "note": "C-ABI calls with host buffers (ptb_render_samples, ptb_resolve, ptb_read_rgba8_async, double-buffered); the path's only input is the parameter block "
-                            "(Test.hlsl reads nothing), output = RGBA8 frame read into pinned host memory each step"},
+                    "note": "C-ABI calls with host buffers (ptb_render_samples, ptb_resolve, ptb_read_rgba8_async into "
+                            "double-buffered pinned memory; merge over NCCL every step when N>1). The path's only input is "
+                            "the parameter block (Test.hlsl reads nothing); output = the RGBA8 frame, every step"},
             "gpu_launches": int(launches),
             "kernel_mode": t.kernel_mode,
             "clocks": {"sm_mhz": clk["sm_mhz"], "sm_max_mhz": clk["sm_max_mhz"], "reasons": clk["reasons"],
@@ -410,7 +400,7 @@ def run_b200(args):
             "literal_frame": literal_frame,
         }
         print(json.dumps(line))
-    t.destroy()
+    eng.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -426,6 +416,8 @@ def main():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-spp", type=int, default=16, help="spp per step of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--shard", default="samples", choices=["samples", "tiles"],
+                    help="multi-GPU partitioning: disjoint sample ranges (default) or interleaved image rows")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3           # timing rule: W >= 3

@@ -134,6 +134,12 @@ int ptb_write_accum(ptb_context *ctx, const float *host_src, size_t pitch_bytes,
 /* Use caller-owned device memory (W*H*4 floats, 16 B aligned) as the accumulation buffer,
  * e.g. a buffer registered with a collective library.  NULL restores the internal one. */
 int ptb_set_accum_buffer(ptb_context *ctx, void *device_ptr);
+/* Multi-GPU image-tile sharding (north_star stage n8, partitioning A): this context renders only
+ * rows  row_offset + i*row_stride  (interleaved for load balance: hits cluster in the image).
+ * Untouched rows of the image / accumulation buffer keep their contents (zero after create /
+ * ptb_accum_reset), so the per-device results merge by a sum == gather of disjoint rows and the
+ * merged image is bit-identical to a single-device render.  Default (0,1) = every row. */
+int ptb_set_row_shard(ptb_context *ctx, uint32_t row_offset, uint32_t row_stride);
 /* Override the spp count used by ptb_resolve after an external merge of accum buffers. */
 int ptb_set_accum_spp(ptb_context *ctx, uint32_t spp_total);
 

@@ -61,10 +61,12 @@ def build(force: bool = False, verbose: bool = False) -> str:
     """Compile libptb200.so in-tree with nvcc for sm_100a (pathtracing_b200/csrc/Makefile)."""
     srcs = [os.path.join(_CSRC, f) for f in os.listdir(_CSRC) if f.endswith((".cu", ".cuh", ".h"))]
     srcs.append(HEADER_PATH)
-    stale = (not os.path.exists(LIB_PATH)) or any(
+    host = os.path.join(_PKG, "host")
+    srcs += [os.path.join(host, f) for f in os.listdir(host) if f.endswith((".cpp", ".hpp"))]
+    stale = (not os.path.exists(LIB_PATH)) or (not os.path.exists(os.path.join(host, "pt_render"))) or any(
         os.path.getmtime(s) > os.path.getmtime(LIB_PATH) for s in srcs)
     if force or stale:
-        cmd = ["make", "-C", _CSRC] + (["-B"] if force else [])
+        cmd = ["make", "-C", _CSRC, "all"] + (["-B"] if force else [])
         r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         if verbose or r.returncode != 0:
             print(r.stdout)
@@ -100,6 +102,7 @@ SIGNATURES = {
     "ptb_write_accum": (C.c_int, [_CTX, C.c_void_p, C.c_size_t, C.c_uint32]),
     "ptb_set_accum_buffer": (C.c_int, [_CTX, C.c_void_p]),
     "ptb_set_accum_spp": (C.c_int, [_CTX, C.c_uint32]),
+    "ptb_set_row_shard": (C.c_int, [_CTX, C.c_uint32, C.c_uint32]),
     "ptb_present": (C.c_int, [_CTX, C.c_uint32, C.c_uint32, C.c_uint32]),
     "ptb_read_present": (C.c_int, [_CTX, C.c_void_p, C.c_size_t]),
     "ptb_timer_begin": (C.c_int, [_CTX]),

@@ -1,0 +1,99 @@
+// NativeTracer.cs — the P/Invoke binding a maintainer of chairclr/PathTracing adds next to
+// RayTracing/Graphics/Renderer.cs to run the tracing path on libptb200.so instead of the Vulkan
+// compute pipeline.  SOURCE ONLY: there is no .NET SDK on the build or GPU box, so this file is
+// not compiled or exercised here (the executable stand-in is pathtracing_b200/tracer.py, which
+// makes the same calls in the same order).  Signatures mirror include/ptb200.h one to one.
+//
+// Replaces, in Renderer.cs: CreateResources (105-196) + CreateComputePipeline (293-403) ->
+// NativeTracer ctor; ComputeFrame (1006-1040) -> ComputeFrame(); ResetFences/WaitForFences
+// (970-972) -> WaitForFences(); the sampled ComputeImage (1086-1089) -> ReadImage()/Present().
+using System;
+using System.Runtime.InteropServices;
+
+namespace RayTracing.Graphics;
+
+public sealed unsafe class NativeTracer : IDisposable
+{
+    private const string Lib = "ptb200";   // libptb200.so / ptb200.dll on the loader path
+
+    [StructLayout(LayoutKind.Sequential)]
+    public struct Config
+    {
+        public uint StructSize;
+        public int Device;
+        public uint Width, Height;
+        public float UvDivX, UvDivY;            // Test.hlsl:6 `resolution`
+        public fixed float Cam[3];              // Test.hlsl:8
+        public fixed float Centre[3];           // Test.hlsl:12
+        public float Radius;                    // Test.hlsl:13
+        public uint Seed, MaxDepth, Flags;
+        public IntPtr Stream;
+    }
+
+    [DllImport(Lib)] private static extern int ptb_default_config(Config* cfg, uint width, uint height);
+    [DllImport(Lib)] private static extern int ptb_create(Config* cfg, out IntPtr ctx);
+    [DllImport(Lib)] private static extern int ptb_destroy(IntPtr ctx);
+    [DllImport(Lib)] private static extern IntPtr ptb_last_error(IntPtr ctx);
+    [DllImport(Lib)] private static extern int ptb_compute_frame(IntPtr ctx);
+    [DllImport(Lib)] private static extern int ptb_wait(IntPtr ctx);
+    [DllImport(Lib)] private static extern int ptb_read_rgba8(IntPtr ctx, void* hostDst, nuint pitchBytes);
+    [DllImport(Lib)] private static extern int ptb_read_rgba8_async(IntPtr ctx, void* hostDst, nuint pitchBytes);
+    [DllImport(Lib)] private static extern int ptb_accum_reset(IntPtr ctx);
+    [DllImport(Lib)] private static extern int ptb_render_samples(IntPtr ctx, uint firstSample, uint nSamples, int jitter);
+    [DllImport(Lib)] private static extern int ptb_resolve(IntPtr ctx, uint flags);
+    [DllImport(Lib)] private static extern uint ptb_accum_spp(IntPtr ctx);
+    [DllImport(Lib)] private static extern int ptb_present(IntPtr ctx, uint dstW, uint dstH, uint flags);
+    [DllImport(Lib)] private static extern int ptb_read_present(IntPtr ctx, void* hostDst, nuint pitchBytes);
+
+    public const uint ResolveSrgb = 1, ResolveBgra = 2;
+
+    private IntPtr _ctx;
+    public uint Width { get; }
+    public uint Height { get; }
+
+    // ≙ CreateResources + CreateComputePipeline: size from Window.FramebufferSize (Renderer.cs:128-129).
+    public NativeTracer(uint width, uint height, int device = 0, uint seed = 0)
+    {
+        Config cfg;
+        Check(IntPtr.Zero, ptb_default_config(&cfg, width, height));
+        cfg.Device = device;
+        cfg.Seed = seed;
+        Check(IntPtr.Zero, ptb_create(&cfg, out _ctx));
+        Width = width;
+        Height = height;
+    }
+
+    // The reference throws `new Exception(string)` on any non-Success result (Renderer.cs:1036-1039).
+    private static void Check(IntPtr ctx, int status)
+    {
+        if (status != 0)
+            throw new Exception($"ptb status {status}: {Marshal.PtrToStringUTF8(ptb_last_error(ctx))}");
+    }
+
+    public void ComputeFrame() => Check(_ctx, ptb_compute_frame(_ctx));                 // Renderer.cs:1006-1040
+    public void WaitForFences() => Check(_ctx, ptb_wait(_ctx));                         // Renderer.cs:972
+    public void ResetAccumulation() => Check(_ctx, ptb_accum_reset(_ctx));
+    public void RenderSamples(uint first, uint count, bool jitter = true) =>
+        Check(_ctx, ptb_render_samples(_ctx, first, count, jitter ? 1 : 0));
+    public void Resolve(uint flags = 0) => Check(_ctx, ptb_resolve(_ctx, flags));
+    public uint AccumulatedSamples => ptb_accum_spp(_ctx);
+
+    public void ReadImage(Span<byte> rgba8)                                              // W*H*4 bytes
+    {
+        if (rgba8.Length < Width * Height * 4) throw new ArgumentException("buffer too small");
+        fixed (byte* p = rgba8) Check(_ctx, ptb_read_rgba8(_ctx, p, 0));
+    }
+
+    public void ReadImageAsync(byte* pinned) => Check(_ctx, ptb_read_rgba8_async(_ctx, pinned, 0));
+
+    public void Present(uint dstW, uint dstH, Span<byte> bgra8, bool srgb = true)        // ≙ DrawFrame's blit
+    {
+        Check(_ctx, ptb_present(_ctx, dstW, dstH, srgb ? ResolveSrgb : 0));
+        fixed (byte* p = bgra8) Check(_ctx, ptb_read_present(_ctx, p, 0));
+    }
+
+    public void Dispose()
+    {
+        if (_ctx != IntPtr.Zero) { ptb_destroy(_ctx); _ctx = IntPtr.Zero; }
+    }
+}

@@ -156,6 +156,8 @@ int ptb_create(const ptb_config *cfg, ptb_context **out_ctx)
     c->cfg = *cfg;
     c->k.width = cfg->width;
     c->k.height = cfg->height;
+    c->k.row_offset = 0;
+    c->k.row_stride = 1;
     c->k.div_x = cfg->uv_div_x;
     c->k.div_y = cfg->uv_div_y;
     for (int i = 0; i < 3; ++i) {
@@ -188,6 +190,7 @@ int ptb_create(const ptb_config *cfg, ptb_context **out_ctx)
     const size_t n = n_pixels(c);
     // ≙ CreateResources (Renderer.cs:120-179): the W x H RGBA8 storage image.
     if ((e = cudaMalloc(&c->buf.rgba8, n * 4)) != cudaSuccess) return bail(e, "cudaMalloc(rgba8)");
+    if ((e = cudaMemsetAsync(c->buf.rgba8, 0, n * 4, c->stream)) != cudaSuccess) return bail(e, "cudaMemset(rgba8)");
     if (cfg->flags & PTB_CFG_KEEP_F32)
         if ((e = cudaMalloc(&c->buf.f32, n * sizeof(float4))) != cudaSuccess) return bail(e, "cudaMalloc(f32)");
     if (cfg->flags & PTB_CFG_KEEP_HIT_IDS)
@@ -373,6 +376,17 @@ int ptb_set_accum_buffer(ptb_context *ctx, void *device_ptr)
         ctx->buf.accum = ctx->buf.accum_owned;   // may be NULL: allocated lazily again
     }
     ctx->accum_spp = 0;
+    return PTB_OK;
+}
+
+int ptb_set_row_shard(ptb_context *ctx, uint32_t row_offset, uint32_t row_stride)
+{
+    PTB_ENTER(ctx);
+    if (row_stride == 0 || row_offset >= row_stride)
+        return fail(ctx, PTB_ERR_INVALID, "ptb_set_row_shard: need row_stride >= 1 and row_offset < row_stride (got %u, %u)",
+                    row_offset, row_stride);
+    ctx->k.row_offset = row_offset;
+    ctx->k.row_stride = row_stride;
     return PTB_OK;
 }
 

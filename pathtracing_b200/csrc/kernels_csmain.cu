@@ -183,7 +183,7 @@ __global__ void __launch_bounds__(256) csmain_frame_vec4(const FrameK k, uint4 *
                                                          float4 *__restrict__ f32, int4 *__restrict__ hit)
 {
     const uint32_t xq = blockIdx.x * blockDim.x + threadIdx.x;   // quad index along x
-    const uint32_t y = blockIdx.y * blockDim.y + threadIdx.y;
+    const uint32_t y = k.row_offset + (blockIdx.y * blockDim.y + threadIdx.y) * k.row_stride;   // row shard (multi-GPU tiles)
     const uint32_t wq = k.width >> 2;
     if (xq >= wq || y >= k.height) return;                       // the guard Test.hlsl:39 lacks
 
@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(256) csmain_frame_scalar(const FrameK k, uint3
                                                            float4 *__restrict__ f32, int32_t *__restrict__ hit)
 {
     const uint32_t x = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t y = blockIdx.y * blockDim.y + threadIdx.y;
+    const uint32_t y = k.row_offset + (blockIdx.y * blockDim.y + threadIdx.y) * k.row_stride;   // row shard (multi-GPU tiles)
     if (x >= k.width || y >= k.height) return;
     float r, g, b;
     const bool h = csmain_shade<MODE>(k, screen_uv<MODE>(__uint2float_rn(x), k.div_x, k.inv_div_x),
@@ -239,18 +239,25 @@ __global__ void __launch_bounds__(256) csmain_frame_scalar(const FrameK k, uint3
     if (hit) hit[i] = h ? 0 : -1;
 }
 
+// rows this context renders: y = row_offset + i*row_stride < height
+static uint32_t shard_rows(const FrameK &k)
+{
+    return k.row_offset >= k.height ? 0u : (k.height - k.row_offset + k.row_stride - 1) / k.row_stride;
+}
+
 static int pick_mode(const FrameK &k) { return k.fast ? (k.on_axis ? MODE_FAST_ON_AXIS : MODE_FAST) : MODE_GENERIC; }
 
 template <int MODE>
 static cudaError_t launch_frame_t(const FrameK &k, const Buffers &b, cudaStream_t s)
 {
+    if (shard_rows(k) == 0) return cudaSuccess;
     const dim3 block(32, 8);
     if ((k.width & 3u) == 0) {
-        const dim3 grid(((k.width >> 2) + 31) / 32, (k.height + 7) / 8);
+        const dim3 grid(((k.width >> 2) + 31) / 32, (shard_rows(k) + 7) / 8);
         csmain_frame_vec4<MODE><<<grid, block, 0, s>>>(k, reinterpret_cast<uint4 *>(b.rgba8), b.f32,
                                                        reinterpret_cast<int4 *>(b.hit));
     } else {
-        const dim3 grid((k.width + 31) / 32, (k.height + 7) / 8);
+        const dim3 grid((k.width + 31) / 32, (shard_rows(k) + 7) / 8);
         csmain_frame_scalar<MODE><<<grid, block, 0, s>>>(k, b.rgba8, b.f32, b.hit);
     }
     return cudaGetLastError();
@@ -277,7 +284,7 @@ __global__ void __launch_bounds__(256) csmain_accumulate(const FrameK k, float4 
                                                          uint32_t first_sample, uint32_t n_samples, uint32_t seed)
 {
     const uint32_t x = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t y = blockIdx.y * blockDim.y + threadIdx.y;
+    const uint32_t y = k.row_offset + (blockIdx.y * blockDim.y + threadIdx.y) * k.row_stride;   // row shard (multi-GPU tiles)
     if (x >= k.width || y >= k.height) return;
     const uint32_t pix = y * k.width + x;
     const float fx = __uint2float_rn(x), fy = __uint2float_rn(y);
@@ -361,8 +368,9 @@ template <int MODE>
 static cudaError_t launch_acc_t(const FrameK &k, float4 *accum, uint32_t first, uint32_t n, uint32_t seed,
                                 bool jitter, cudaStream_t s)
 {
+    if (shard_rows(k) == 0) return cudaSuccess;
     const dim3 block(32, 8);
-    const dim3 grid((k.width + 31) / 32, (k.height + 7) / 8);
+    const dim3 grid((k.width + 31) / 32, (shard_rows(k) + 7) / 8);
     if (jitter) csmain_accumulate<MODE, true><<<grid, block, 0, s>>>(k, accum, first, n, seed);
     else csmain_accumulate<MODE, false><<<grid, block, 0, s>>>(k, accum, first, n, seed);
     return cudaGetLastError();

@@ -15,6 +15,7 @@ namespace ptb {
 // (prepare_terms kernel, same *_rn intrinsics as the per-pixel code) when the context is created.
 struct FrameK {
     uint32_t width, height;
+    uint32_t row_offset, row_stride;   // this context renders rows row_offset + i*row_stride (default 0,1 = all)
     float div_x, div_y;
     float cam[3];
     float centre[3];

@@ -127,6 +127,9 @@ class NativeTracer:
     def set_accum_spp(self, spp: int) -> None:
         self._ck(self._lib.ptb_set_accum_spp(self._ctx, spp))
 
+    def set_row_shard(self, row_offset: int, row_stride: int) -> None:
+        self._ck(self._lib.ptb_set_row_shard(self._ctx, row_offset, row_stride))
+
     def read_accum(self, out: Optional[np.ndarray] = None) -> np.ndarray:
         if out is None:
             out = np.empty((self.height, self.width, 4), np.float32)

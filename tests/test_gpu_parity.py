@@ -365,3 +365,65 @@ def test_async_readback_is_ordered_and_matches_sync(oracle):
     acc = oracle.accumulate(p, 4, 4, 2, True, accum=acc)
     assert np.array_equal(bufs[2], oracle.resolve(acc, 8, srgb=True))
     assert np.array_equal(sync, bufs[2])
+
+
+# ---- multi-GPU partitioning emulated on one device: one context per "rank" -------------------------
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_row_shards_merge_to_the_single_device_image(world):
+    w, h, spp, seed = 640, 360, 6, 4
+    with NativeTracer(w, h, seed=seed, keep_f32=True) as t:
+        t.compute_frame()
+        full_frame = t.read_rgba8()
+        t.render_samples(0, spp)
+        full_acc = t.read_accum()
+        t.resolve()
+        full_img = t.read_rgba8()
+    merged_frame = np.zeros((h, w), np.uint32)
+    merged_img = np.zeros((h, w), np.uint32)
+    merged_acc = np.zeros((h, w, 4), np.float32)
+    for rank in range(world):
+        with NativeTracer(w, h, seed=seed) as t:
+            t.set_row_shard(rank, world)
+            t.compute_frame()
+            fr = t.read_rgba8()
+            assert not fr[(np.arange(h) % world) != rank].any()          # foreign rows untouched (zero)
+            merged_frame += fr.view(np.uint32).reshape(h, w)
+            t.render_samples(0, spp)
+            merged_acc += t.read_accum()                                 # disjoint rows: sum == gather
+            t.resolve()
+            merged_img += t.read_rgba8().view(np.uint32).reshape(h, w)
+    assert np.array_equal(merged_frame.view(np.uint8).reshape(h, w, 4), full_frame)
+    assert eq_bits(merged_acc, full_acc)
+    assert np.array_equal(merged_img.view(np.uint8).reshape(h, w, 4), full_img)
+
+
+def test_row_shard_argument_errors():
+    with NativeTracer(64, 36) as t:
+        for off, stride in ((0, 0), (2, 2), (5, 3)):
+            with pytest.raises(PtbError) as e:
+                t.set_row_shard(off, stride)
+            assert e.value.status == _lib.PTB_ERR_INVALID
+        t.set_row_shard(40, 64)          # offset beyond the image: nothing to render, not an error
+        t.compute_frame()
+        assert not t.read_rgba8().any()
+
+
+def test_sharded_renderer_single_rank_paths(oracle):
+    """dist.ShardedRenderer over the real GpuEngine (world size 1): both modes equal the plain path."""
+    import torch
+    from pathtracing_b200.dist import GpuEngine, ShardedRenderer
+    w, h = 320, 180
+    p = oracle.frame_params(w, h)
+    ref = oracle.accumulate(p, 0, 4, 9, True)
+    ref = oracle.accumulate(p, 4, 3, 9, True, accum=ref)
+    for mode in ("samples", "tiles"):
+        eng = GpuEngine(w, h, 0, seed=9)
+        sr = ShardedRenderer(eng, mode=mode)
+        sr.render(0, 4)
+        sr.render(4, 3)
+        img = sr.merge(0)
+        torch.cuda.synchronize()
+        assert eq_bits(eng.accum.cpu().numpy(), ref)
+        got = img.cpu().numpy().view(np.uint8).reshape(h, w, 4)
+        assert np.array_equal(got, oracle.resolve(ref, 7))
+        eng.close()
