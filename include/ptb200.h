@@ -143,6 +143,90 @@ int ptb_set_row_shard(ptb_context *ctx, uint32_t row_offset, uint32_t row_stride
 /* Override the spp count used by ptb_resolve after an external merge of accum buffers. */
 int ptb_set_accum_spp(ptb_context *ctx, uint32_t spp_total);
 
+/* ---- scene path (north_star stages n3-n7; NO reference counterpart: the reference's scene is the
+ * literals of Test.hlsl:8,12-13 and its only intersection is Test.hlsl:16-27) -------------------
+ * ptb_upload_scene copies a scene description from HOST memory, packs it into 16 B-aligned device
+ * arrays (spheres: float4 centre+radius; triangles: 3 x float4 = v0|id, e1|material, e2|0, stored
+ * in BVH leaf order), and builds the acceleration structures ON THE GPU: Morton-code LBVH (63-bit
+ * codes, radix sort, Karras hierarchy), bottom-up AABB refit, SAH leaf collapse, flattened into
+ * 64 B two-child nodes.  One hierarchy per primitive class (spheres / triangles).
+ * While a scene is resident, ptb_compute_frame renders sample 0 of every pixel without jitter
+ * (RGBA8 + optional float4 + primary-ray primitive ids: spheres 0..ns-1, triangles ns..ns+nt-1,
+ * -1 = miss) and ptb_render_samples runs the wavefront path tracer (one wave = one sample of
+ * every pixel; per bounce one fused closest-hit + scatter kernel; live paths are repacked with
+ * warp ballot + prefix sum).  ptb_clear_scene returns the context to the literal CSMain path.
+ * The arithmetic spec (ray generation = Test.hlsl:7-10 generalised to a camera basis, sphere
+ * quadratic = Test.hlsl:16-27 + far root, Moeller-Trumbore triangles, Lambert / metal /
+ * dielectric scattering, RNG keys) is frozen in oracle/pt_scene_oracle.h. */
+#define PTB_MAT_LAMBERT    0u
+#define PTB_MAT_METAL      1u
+#define PTB_MAT_DIELECTRIC 2u
+#define PTB_SHADE_PATH     0u   /* multi-bounce paths lit by the sky gradient */
+#define PTB_SHADE_NORMALS  1u   /* Test.hlsl:28-36: hit -> n*0.5+0.5, miss -> (uv.x, uv.y, 0) */
+
+typedef struct ptb_material {   /* 32 bytes */
+    uint32_t type;              /* PTB_MAT_* */
+    float    albedo[3];
+    float    fuzz;              /* metal */
+    float    ior;               /* dielectric */
+    float    pad[2];
+} ptb_material;
+
+typedef struct ptb_scene_desc {
+    uint32_t struct_size;       /* = sizeof(ptb_scene_desc); checked */
+    uint32_t n_spheres;
+    const float    *spheres;        /* host, n_spheres x (cx,cy,cz,r) */
+    const uint32_t *sphere_material;/* host, n_spheres */
+    uint32_t n_triangles;
+    uint32_t n_materials;
+    const float    *tri_vertices;   /* host, n_triangles x (v0,v1,v2) = 9 floats */
+    const uint32_t *tri_material;   /* host, n_triangles */
+    const ptb_material *materials;  /* host, n_materials (>= 1) */
+    float    cam_origin[3];         /* Test.hlsl:8 */
+    float    cam_u[3], cam_v[3], cam_w[3]; /* ray = normalize(uv.x*U + uv.y*V + W); Test.hlsl:10 = (1,0,0),(0,1,0),(0,0,-1) */
+    float    sky_horizon[3], sky_zenith[3];/* escaped paths: lerp by (d.y+1)/2 */
+    float    t_min;                 /* ray epsilon, e.g. 1e-3 */
+    uint32_t shade_mode;            /* PTB_SHADE_* */
+    uint32_t max_leaf;              /* SAH leaf collapse limit (1..8); 0 = default 4 */
+    uint32_t flags;                 /* PTB_SCENE_* */
+} ptb_scene_desc;
+#define PTB_SCENE_COUNT_STATS 0x1u  /* run the counting build of the kernels (ptb_scene_stats) */
+
+typedef struct ptb_scene_info {
+    uint32_t n_spheres, n_triangles;
+    uint32_t sphere_nodes, triangle_nodes;   /* 64 B nodes after leaf collapse */
+    uint32_t sphere_leaves, triangle_leaves;
+    uint32_t max_leaf;
+    float    build_ms;                       /* GPU time of the whole build (CUDA events) */
+    uint64_t device_bytes;                   /* nodes + primitives + materials */
+} ptb_scene_info;
+
+/* Work counters of the counting build, summed over every ray since upload / ptb_scene_stats_reset. */
+typedef struct ptb_scene_stats {
+    uint64_t rays;            /* closest-hit queries (path segments) */
+    uint64_t nodes_visited;   /* 64 B node fetches */
+    uint64_t prims_tested;    /* primitive intersection tests */
+    uint64_t scatters;        /* material evaluations */
+    uint64_t paths;           /* camera rays started */
+    uint64_t max_stack;       /* deepest traversal stack seen */
+} ptb_scene_stats;
+
+int ptb_upload_scene(ptb_context *ctx, const ptb_scene_desc *desc);
+int ptb_clear_scene(ptb_context *ctx);
+int ptb_scene_info_get(ptb_context *ctx, ptb_scene_info *out);
+int ptb_scene_stats_get(ptb_context *ctx, ptb_scene_stats *out);
+int ptb_scene_stats_reset(ptb_context *ctx);
+/* Download one flattened hierarchy for inspection: which = 0 spheres, 1 triangles.
+ * nodes_out: cap_nodes x 16 floats (64 B nodes, layout in csrc/scene.cuh), order_out: cap_prims
+ * primitive ids in leaf order.  Either may be NULL; counts are always written. */
+int ptb_scene_read_bvh(ptb_context *ctx, int which, void *nodes_out, uint32_t cap_nodes, uint32_t *n_nodes,
+                       uint32_t *order_out, uint32_t cap_prims, uint32_t *n_prims);
+/* Ray queries against the resident scene with HOST ray arrays (n x 3 floats each).
+ * mode 0 = closest hit (out_prim = id or -1, out_t = distance or 0), 1 = any hit in (t_min,t_max)
+ * (out_prim = 1/0, out_t may be NULL). */
+int ptb_trace_rays(ptb_context *ctx, uint64_t n_rays, const float *origins, const float *dirs, float t_min,
+                   float t_max, int mode, int32_t *out_prim, float *out_t);
+
 /* ---- present-equivalent -----------------------------------------------
  * ptb_present replaces the full-screen-quad draw (Renderer.cs:1079-1091) + PSMain
  *   (PixelShader.hlsl:8-19): nearest/repeat sampling of the RGBA8 image onto a dst_w x dst_h

@@ -57,6 +57,51 @@ class Config(C.Structure):
     ]
 
 
+MAT_LAMBERT, MAT_METAL, MAT_DIELECTRIC = 0, 1, 2
+SHADE_PATH, SHADE_NORMALS = 0, 1
+SCENE_COUNT_STATS = 0x1
+
+
+class Material(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("albedo", C.c_float * 3), ("fuzz", C.c_float), ("ior", C.c_float),
+                ("pad", C.c_float * 2)]
+
+
+class SceneDesc(C.Structure):
+    _fields_ = [
+        ("struct_size", C.c_uint32),
+        ("n_spheres", C.c_uint32),
+        ("spheres", C.c_void_p),
+        ("sphere_material", C.c_void_p),
+        ("n_triangles", C.c_uint32),
+        ("n_materials", C.c_uint32),
+        ("tri_vertices", C.c_void_p),
+        ("tri_material", C.c_void_p),
+        ("materials", C.c_void_p),
+        ("cam_origin", C.c_float * 3),
+        ("cam_u", C.c_float * 3),
+        ("cam_v", C.c_float * 3),
+        ("cam_w", C.c_float * 3),
+        ("sky_horizon", C.c_float * 3),
+        ("sky_zenith", C.c_float * 3),
+        ("t_min", C.c_float),
+        ("shade_mode", C.c_uint32),
+        ("max_leaf", C.c_uint32),
+        ("flags", C.c_uint32),
+    ]
+
+
+class SceneInfo(C.Structure):
+    _fields_ = [("n_spheres", C.c_uint32), ("n_triangles", C.c_uint32), ("sphere_nodes", C.c_uint32),
+                ("triangle_nodes", C.c_uint32), ("sphere_leaves", C.c_uint32), ("triangle_leaves", C.c_uint32),
+                ("max_leaf", C.c_uint32), ("build_ms", C.c_float), ("device_bytes", C.c_uint64)]
+
+
+class SceneStats(C.Structure):
+    _fields_ = [("rays", C.c_uint64), ("nodes_visited", C.c_uint64), ("prims_tested", C.c_uint64),
+                ("scatters", C.c_uint64), ("paths", C.c_uint64), ("max_stack", C.c_uint64)]
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     """Compile libptb200.so in-tree with nvcc for sm_100a (pathtracing_b200/csrc/Makefile)."""
     srcs = [os.path.join(_CSRC, f) for f in os.listdir(_CSRC) if f.endswith((".cu", ".cuh", ".h"))]
@@ -103,6 +148,15 @@ SIGNATURES = {
     "ptb_set_accum_buffer": (C.c_int, [_CTX, C.c_void_p]),
     "ptb_set_accum_spp": (C.c_int, [_CTX, C.c_uint32]),
     "ptb_set_row_shard": (C.c_int, [_CTX, C.c_uint32, C.c_uint32]),
+    "ptb_upload_scene": (C.c_int, [_CTX, _P(SceneDesc)]),
+    "ptb_clear_scene": (C.c_int, [_CTX]),
+    "ptb_scene_info_get": (C.c_int, [_CTX, _P(SceneInfo)]),
+    "ptb_scene_stats_get": (C.c_int, [_CTX, _P(SceneStats)]),
+    "ptb_scene_stats_reset": (C.c_int, [_CTX]),
+    "ptb_scene_read_bvh": (C.c_int, [_CTX, C.c_int, C.c_void_p, C.c_uint32, _P(C.c_uint32), C.c_void_p, C.c_uint32,
+                                     _P(C.c_uint32)]),
+    "ptb_trace_rays": (C.c_int, [_CTX, C.c_uint64, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_int, C.c_void_p,
+                                 C.c_void_p]),
     "ptb_present": (C.c_int, [_CTX, C.c_uint32, C.c_uint32, C.c_uint32]),
     "ptb_read_present": (C.c_int, [_CTX, C.c_void_p, C.c_size_t]),
     "ptb_timer_begin": (C.c_int, [_CTX]),

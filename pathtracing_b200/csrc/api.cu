@@ -97,7 +97,9 @@ void derive_fast_flags(ptb_context *c)
 }  // namespace
 
 namespace ptb {
-void scene_destroy(ptb_context *ctx);   // scene.cu
+// shared with scene.cu (declared in ptb_internal.h)
+int fail_msg(ptb_context *ctx, int code, const char *msg) { return fail(ctx, code, "%s", msg); }
+int fail_cuda(ptb_context *ctx, cudaError_t e, const char *what) { return cuda_fail(ctx, e, what); }
 }
 
 extern "C" {
@@ -225,6 +227,7 @@ int ptb_compute_frame(ptb_context *ctx)
 {
     PTB_ENTER(ctx);
     if (ctx->copy_pending) PTB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_copy_done, 0));
+    if (ptb::scene_resident(ctx)) return ptb::scene_compute_frame(ctx);   // n3-n7: uploaded scene instead of the literal one
     PTB_CUDA(ctx, ptb::launch_csmain_frame(ctx->k, ctx->buf, ctx->stream));
     ctx->launches += 1;
     return PTB_OK;
@@ -238,6 +241,7 @@ int ptb_wait(ptb_context *ctx)
         PTB_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
         ctx->copy_pending = false;
     }
+    if (ptb::scene_resident(ctx)) return ptb::scene_wait_check(ctx);
     return PTB_OK;
 }
 
@@ -317,6 +321,11 @@ int ptb_render_samples(ptb_context *ctx, uint32_t first_sample, uint32_t n_sampl
         return fail(ctx, PTB_ERR_INVALID, "ptb_render_samples: spp counter would overflow");
     int rc = ensure_accum(ctx);
     if (rc != PTB_OK) return rc;
+    if (ptb::scene_resident(ctx)) {
+        rc = ptb::scene_render_samples(ctx, first_sample, n_samples, jitter);
+        if (rc == PTB_OK) ctx->accum_spp += n_samples;
+        return rc;
+    }
     PTB_CUDA(ctx, ptb::launch_csmain_accumulate(ctx->k, ctx->buf.accum, first_sample, n_samples, ctx->cfg.seed,
                                                 jitter != 0, ctx->stream));
     ctx->launches += 1;

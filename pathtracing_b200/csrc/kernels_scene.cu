@@ -1,0 +1,639 @@
+// kernels_scene.cu — sm_100a kernels of the scene path (north_star stages n3, n5, n6, n7).
+// The reference's only tracing arithmetic is RayTracing/Assets/Shaders/Source/Ray/Test.hlsl:6-39;
+// its camera ray (:7-10), sphere quadratic (:16-27) and normal / miss colours (:28-36) are
+// generalised here, everything else (triangles, hierarchy traversal, materials, bounces, queues)
+// has no reference counterpart.  The arithmetic spec is frozen in oracle/pt_scene_oracle.h; this
+// file restates it independently.
+//
+// THIS TRANSLATION UNIT IS COMPILED WITH -fmad=false (csrc/Makefile): every `*`, `+`, `-`, `/`,
+// sqrtf below is one IEEE binary32 round-to-nearest operation, never contracted, which is what
+// makes the results bit-identical to the CPU oracle.  FMAs appear only where written as fmaf().
+//
+// Wavefront organisation: one wave = one sample of every pixel of this context's row shard.
+// Per bounce ONE fused kernel (closest hit over both hierarchies + scatter), run by a persistent
+// grid whose warps pull 32-path chunks from an atomic cursor.  Paths that continue are repacked
+// into the next queue with warp ballot + prefix popcount + one atomicAdd per warp, so every
+// bounce starts from a dense array (structure of arrays, 40 B per path).  A pixel owns at most
+// one live path per wave, so terminated paths add their radiance to the float4 accumulation
+// buffer with a plain read-modify-write.
+#include <cfloat>
+
+#include "ptb_math.cuh"
+#include "scene.cuh"
+
+namespace ptb {
+namespace {
+
+constexpr int STACK_N = 64;
+constexpr unsigned FULL = 0xFFFFFFFFu;
+
+struct Counters {
+    uint32_t nodes = 0, prims = 0, max_stack = 0;
+};
+
+struct RayT {
+    float ox, oy, oz, dx, dy, dz;
+    float ix, iy, iz;      // 1/d (culling only: never reaches a result)
+    float a, a2, a4;       // d.d, 2*(d.d), 4*(d.d)  (Test.hlsl:17, hoisted per ray)
+};
+
+struct Best {
+    float t;
+    int id;      // unified original primitive id (spheres 0..ns-1, triangles ns..)
+    int pos;     // leaf-order position inside its class
+    int cls;     // 0 sphere, 1 triangle
+};
+
+__device__ __forceinline__ float dot3f(float ax, float ay, float az, float bx, float by, float bz)
+{
+    float s = ax * bx;
+    s = s + ay * by;
+    s = s + az * bz;
+    return s;
+}
+
+__device__ __forceinline__ void make_ray(RayT &r, float ox, float oy, float oz, float dx, float dy, float dz)
+{
+    r.ox = ox; r.oy = oy; r.oz = oz;
+    r.dx = dx; r.dy = dy; r.dz = dz;
+    r.ix = 1.0f / dx; r.iy = 1.0f / dy; r.iz = 1.0f / dz;
+    r.a = dot3f(dx, dy, dz, dx, dy, dz);
+    r.a2 = 2.0f * r.a;
+    r.a4 = 4.0f * r.a;
+}
+
+// Test.hlsl:16-27 generalised; far root when the near one is outside (t_min, t_max).
+__device__ __forceinline__ bool hit_sphere(const float4 cr, const RayT &r, float t_min, float t_max, float &t_out)
+{
+    const float ocx = r.ox - cr.x, ocy = r.oy - cr.y, ocz = r.oz - cr.z;      // :16
+    const float b = 2.0f * dot3f(ocx, ocy, ocz, r.dx, r.dy, r.dz);           // :18
+    const float cc = dot3f(ocx, ocy, ocz, ocx, ocy, ocz) - cr.w * cr.w;      // :19
+    const float disc = b * b - r.a4 * cc;                                    // :21
+    if (!(disc > 0.0f)) return false;                                        // :24
+    const float s = sqrtf(disc);
+    float t = ((-b) - s) / r.a2;                                             // :27
+    if (!(t > t_min && t < t_max)) {
+        t = ((-b) + s) / r.a2;
+        if (!(t > t_min && t < t_max)) return false;
+    }
+    t_out = t;
+    return true;
+}
+
+// Moeller-Trumbore, two-sided.  v0, e1 = v1-v0, e2 = v2-v0 (single exact-rounded subtractions,
+// done once at upload).
+__device__ __forceinline__ bool hit_triangle(const float4 v0, const float4 e1, const float4 e2, const RayT &r, float t_min,
+                                             float t_max, float &t_out)
+{
+    const float px = r.dy * e2.z - r.dz * e2.y;
+    const float py = r.dz * e2.x - r.dx * e2.z;
+    const float pz = r.dx * e2.y - r.dy * e2.x;
+    const float det = dot3f(e1.x, e1.y, e1.z, px, py, pz);
+    if (!(det != 0.0f)) return false;
+    const float inv = 1.0f / det;
+    const float tx = r.ox - v0.x, ty = r.oy - v0.y, tz = r.oz - v0.z;
+    const float u = dot3f(tx, ty, tz, px, py, pz) * inv;
+    if (!(u >= 0.0f && u <= 1.0f)) return false;
+    const float qx = ty * e1.z - tz * e1.y;
+    const float qy = tz * e1.x - tx * e1.z;
+    const float qz = tx * e1.y - ty * e1.x;
+    const float w = dot3f(r.dx, r.dy, r.dz, qx, qy, qz) * inv;
+    if (!(w >= 0.0f && u + w <= 1.0f)) return false;
+    const float t = dot3f(e2.x, e2.y, e2.z, qx, qy, qz) * inv;
+    if (!(t > t_min && t < t_max)) return false;
+    t_out = t;
+    return true;
+}
+
+// Conservative slab test of one child box against [t_min, t_far]: boxes are padded at build
+// time and the interval is widened by ~8 ulp, so a box is never rejected when a primitive
+// inside it would be accepted.  fminf/fmaxf drop the NaN of 0*inf.
+__device__ __forceinline__ bool slab(float lox, float hix, float loy, float hiy, float loz, float hiz, const RayT &r,
+                                     float t_min, float t_far, float &t_near)
+{
+    const float ax = (lox - r.ox) * r.ix, bx = (hix - r.ox) * r.ix;
+    const float ay = (loy - r.oy) * r.iy, by = (hiy - r.oy) * r.iy;
+    const float az = (loz - r.oz) * r.iz, bz = (hiz - r.oz) * r.iz;
+    const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
+    const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_far));
+    t_near = tn * 0.999999f;
+    return t_near <= tf * 1.000001f;
+}
+
+// Stack-based traversal of one hierarchy.  CLS 0 = spheres, 1 = triangles.  ANY: stop at the first
+// hit.  The closest hit keeps the smaller unified id on equal t (order independent).
+template <int CLS, bool ANY, bool STATS>
+__device__ __forceinline__ bool traverse(const SceneK &k, const RayT &r, float t_min, float t_max, Best &best, Counters &cn,
+                                         uint32_t *error_flag)
+{
+    const BvhNode *__restrict__ nodes = CLS == 0 ? k.sph_nodes : k.tri_nodes;
+    int cur = CLS == 0 ? k.sph_root : k.tri_root;
+    if (cur == EMPTY_REF) return false;
+    int stack[STACK_N];
+    float tstack[STACK_N];
+    int sp = 0;
+    for (;;) {
+        if (cur >= 0) {
+            const float4 na = __ldg(&nodes[cur].a), nb = __ldg(&nodes[cur].b), nc = __ldg(&nodes[cur].c);
+            const int4 nd = __ldg(&nodes[cur].d);
+            if (STATS) ++cn.nodes;
+            const float t_far = ANY ? t_max : best.t;
+            float tn0, tn1;
+            bool h0 = slab(na.x, na.y, na.z, na.w, nc.x, nc.y, r, t_min, t_far, tn0);
+            bool h1 = slab(nb.x, nb.y, nb.z, nb.w, nc.z, nc.w, r, t_min, t_far, tn1) && nd.y != EMPTY_REF;
+            if (h0 && h1) {
+                const bool swap = tn1 < tn0;
+                const int near_ref = swap ? nd.y : nd.x, far_ref = swap ? nd.x : nd.y;
+                if (sp < STACK_N) {
+                    stack[sp] = far_ref;
+                    tstack[sp] = swap ? tn0 : tn1;
+                    ++sp;
+                    if (STATS) cn.max_stack = max(cn.max_stack, (uint32_t)sp);
+                } else {
+                    atomicOr(error_flag, 1u);
+                }
+                cur = near_ref;
+                continue;
+            }
+            if (h0) { cur = nd.x; continue; }
+            if (h1) { cur = nd.y; continue; }
+        } else {
+            const uint32_t q = (uint32_t)~cur;
+            const uint32_t first = q & LEAF_FIRST_MASK, count = (q >> LEAF_COUNT_SHIFT) + 1u;
+            for (uint32_t i = first; i < first + count; ++i) {
+                float t;
+                if (STATS) ++cn.prims;
+                if (CLS == 0) {
+                    const float4 cr = __ldg(&k.sph[i]);
+                    if (!hit_sphere(cr, r, t_min, t_max, t)) continue;
+                    if (ANY) return true;
+                    if (t <= best.t) {
+                        const int id = (int)__ldg(&k.sph_meta[i]).x;
+                        if (t < best.t || id < best.id || best.id < 0) { best.t = t; best.id = id; best.pos = (int)i; best.cls = 0; }
+                    }
+                } else {
+                    const float4 v0 = __ldg(&k.tri[3 * (size_t)i]), e1 = __ldg(&k.tri[3 * (size_t)i + 1]),
+                                 e2 = __ldg(&k.tri[3 * (size_t)i + 2]);
+                    if (!hit_triangle(v0, e1, e2, r, t_min, t_max, t)) continue;
+                    if (ANY) return true;
+                    if (t <= best.t) {
+                        const int id = __float_as_int(v0.w);
+                        if (t < best.t || id < best.id || best.id < 0) { best.t = t; best.id = id; best.pos = (int)i; best.cls = 1; }
+                    }
+                }
+            }
+        }
+        // pop, skipping entries that the current closest hit already rules out
+        for (;;) {
+            if (sp == 0) return best.id >= 0;
+            --sp;
+            if (ANY || tstack[sp] <= best.t) { cur = stack[sp]; break; }
+        }
+    }
+}
+
+template <bool STATS>
+__device__ __forceinline__ bool closest_hit(const SceneK &k, const RayT &r, float t_min, float t_max, Best &best, Counters &cn,
+                                            uint32_t *error_flag)
+{
+    best.t = t_max;
+    best.id = -1;
+    best.pos = 0;
+    best.cls = 0;
+    traverse<0, false, STATS>(k, r, t_min, t_max, best, cn, error_flag);
+    traverse<1, false, STATS>(k, r, t_min, t_max, best, cn, error_flag);
+    return best.id >= 0;
+}
+
+// ---- sampling spec (oracle/pt_scene_oracle.c: pto_sincos2pi, pto_unit_vector, pto_scatter) ------
+__device__ __forceinline__ void sincos2pi(float u, float &sn, float &cs)
+{
+    const float x = u * 4.0f;
+    const int q = (int)x;
+    const float f = x - (float)q;
+    const float a = (f - 0.5f) * 1.57079637f;
+    const float a2 = a * a;
+    float ps = 2.75573192e-6f;
+    ps = ps * a2 + -1.98412698e-4f;
+    ps = ps * a2 + 8.33333333e-3f;
+    ps = ps * a2 + -1.66666667e-1f;
+    ps = ps * a2 + 1.0f;
+    const float s = a * ps;
+    float pc = 2.48015873e-5f;
+    pc = pc * a2 + -1.38888889e-3f;
+    pc = pc * a2 + 4.16666667e-2f;
+    pc = pc * a2 + -0.5f;
+    pc = pc * a2 + 1.0f;
+    const float c = pc;
+    const float sb = (s + c) * 0.707106769f;
+    const float cb = (c - s) * 0.707106769f;
+    switch (q & 3) {
+    case 0: sn = sb; cs = cb; break;
+    case 1: sn = cb; cs = -sb; break;
+    case 2: sn = -sb; cs = -cb; break;
+    default: sn = -cb; cs = sb; break;
+    }
+}
+
+__device__ __forceinline__ void unit_vector(float u1, float u2, float &vx, float &vy, float &vz)
+{
+    const float z = 1.0f - 2.0f * u1;
+    const float r2 = 1.0f - z * z;
+    const float rr = sqrtf(fmaxf(r2, 0.0f));
+    float sn, cs;
+    sincos2pi(u2, sn, cs);
+    vx = rr * cs;
+    vy = rr * sn;
+    vz = z;
+}
+
+__device__ __forceinline__ void normalize3f(float &x, float &y, float &z)
+{
+    const float len = sqrtf(dot3f(x, y, z, x, y, z));
+    x = x / len;
+    y = y / len;
+    z = z / len;
+}
+
+// returns false when the path is absorbed; d is replaced by the scattered direction
+__device__ __forceinline__ bool scatter(const ptb_material &m, float &dx, float &dy, float &dz, float nox, float noy, float noz,
+                                        float u1, float u2, float u3)
+{
+    const float dn_out = dot3f(dx, dy, dz, nox, noy, noz);
+    const bool front = dn_out < 0.0f;
+    const float nx = front ? nox : -nox, ny = front ? noy : -noy, nz = front ? noz : -noz;
+    float rx, ry, rz;
+    if (m.type == PTB_MAT_LAMBERT) {
+        float vx, vy, vz;
+        unit_vector(u1, u2, vx, vy, vz);
+        rx = nx + vx; ry = ny + vy; rz = nz + vz;
+        if (fabsf(rx) < 1e-8f && fabsf(ry) < 1e-8f && fabsf(rz) < 1e-8f) { rx = nx; ry = ny; rz = nz; }
+    } else if (m.type == PTB_MAT_METAL) {
+        float vx, vy, vz;
+        unit_vector(u1, u2, vx, vy, vz);
+        const float dn = dot3f(dx, dy, dz, nx, ny, nz);
+        const float kk = 2.0f * dn;
+        float fx = dx - kk * nx, fy = dy - kk * ny, fz = dz - kk * nz;
+        normalize3f(fx, fy, fz);
+        rx = fx + m.fuzz * vx; ry = fy + m.fuzz * vy; rz = fz + m.fuzz * vz;
+        if (!(dot3f(rx, ry, rz, nx, ny, nz) > 0.0f)) return false;
+    } else {
+        const float ri = front ? 1.0f / m.ior : m.ior;
+        const float dn = dot3f(dx, dy, dz, nx, ny, nz);
+        const float cs = fminf(-dn, 1.0f);
+        const float sn = sqrtf(fmaxf(1.0f - cs * cs, 0.0f));
+        const bool cannot = ri * sn > 1.0f;
+        float r0 = (1.0f - ri) / (1.0f + ri);
+        r0 = r0 * r0;
+        const float mm = 1.0f - cs;
+        const float m2 = mm * mm;
+        const float m5 = (m2 * m2) * mm;
+        const float refl = r0 + (1.0f - r0) * m5;
+        if (cannot || refl > u3) {
+            const float kk = 2.0f * dn;
+            rx = dx - kk * nx; ry = dy - kk * ny; rz = dz - kk * nz;
+        } else {
+            const float px = ri * (dx + cs * nx), py = ri * (dy + cs * ny), pz = ri * (dz + cs * nz);
+            const float kk = -sqrtf(fabsf(1.0f - dot3f(px, py, pz, px, py, pz)));
+            rx = px + kk * nx; ry = py + kk * ny; rz = pz + kk * nz;
+        }
+    }
+    normalize3f(rx, ry, rz);
+    dx = rx; dy = ry; dz = rz;
+    return true;
+}
+
+// outward geometric normal at the hit (Test.hlsl:28-29 for spheres) and the material id
+__device__ __forceinline__ void hit_frame(const SceneK &k, const Best &b, float Px, float Py, float Pz, float &nx, float &ny,
+                                          float &nz, uint32_t &mat)
+{
+    if (b.cls == 0) {
+        const float4 cr = __ldg(&k.sph[b.pos]);
+        nx = Px - cr.x; ny = Py - cr.y; nz = Pz - cr.z;
+        mat = __ldg(&k.sph_meta[b.pos]).y;
+    } else {
+        const float4 e1 = __ldg(&k.tri[3 * (size_t)b.pos + 1]), e2 = __ldg(&k.tri[3 * (size_t)b.pos + 2]);
+        nx = e1.y * e2.z - e1.z * e2.y;
+        ny = e1.z * e2.x - e1.x * e2.z;
+        nz = e1.x * e2.y - e1.y * e2.x;
+        mat = (uint32_t)__float_as_int(e1.w);
+    }
+    normalize3f(nx, ny, nz);
+}
+
+// ---- the per-bounce kernel ----------------------------------------------------------------------
+struct WaveArgs {
+    PathQueue in, out;
+    const uint32_t *n_in;     // paths in `in` (depth >= 1)
+    uint32_t *n_out;          // compaction counter of `out`
+    uint32_t *cursor;         // work cursor of this launch
+    uint32_t n0;              // depth 0: pixels in this context's row shard
+    uint32_t depth, sample;
+    int jitter;
+    float4 *accum;
+    int32_t *hit_ids;
+    SceneStatsDev *stats;
+    uint32_t *error_flag;
+};
+
+template <bool DEPTH0, bool STATS>
+__global__ void __launch_bounds__(256) bounce_kernel(const SceneK k, const WaveArgs w)
+{
+    const unsigned lane = threadIdx.x & 31u;
+    const uint32_t n_in = DEPTH0 ? w.n0 : *w.n_in;
+    Counters cn;
+    uint32_t n_rays = 0, n_scatter = 0;
+    for (;;) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(w.cursor, 32u);
+        base = __shfl_sync(FULL, base, 0);
+        if (base >= n_in) break;
+        const uint32_t i = base + lane;
+        bool alive = i < n_in;
+        uint32_t pix = 0;
+        float ox = 0, oy = 0, oz = 0, dx = 0, dy = 0, dz = 1, tr = 1, tg = 1, tb = 1, uvx = 0, uvy = 0;
+        if (alive) {
+            if (DEPTH0) {
+                const uint32_t x = i % k.width, yy = i / k.width;
+                const uint32_t y = k.row_offset + yy * k.row_stride;
+                pix = y * k.width + x;
+                float fx = (float)x, fy = (float)y;
+                if (w.jitter) {
+                    const U3 v = pcg3d(pix, w.sample, k.seed);
+                    fx = fx + bits_to_unit(v.x);
+                    fy = fy + bits_to_unit(v.y);
+                }
+                uvx = (fx / k.div_x) * 2.0f - 1.0f;                      // Test.hlsl:7
+                uvy = (fy / k.div_y) * 2.0f - 1.0f;
+                dx = (uvx * k.cam_u[0] + uvy * k.cam_v[0]) + k.cam_w[0];   // Test.hlsl:10 with a camera basis
+                dy = (uvx * k.cam_u[1] + uvy * k.cam_v[1]) + k.cam_w[1];
+                dz = (uvx * k.cam_u[2] + uvy * k.cam_v[2]) + k.cam_w[2];
+                normalize3f(dx, dy, dz);
+                ox = k.cam_o[0]; oy = k.cam_o[1]; oz = k.cam_o[2];       // Test.hlsl:8
+            } else {
+                const float4 s0 = w.in.s0[i], s1 = w.in.s1[i];
+                const float2 s2 = w.in.s2[i];
+                ox = s0.x; oy = s0.y; oz = s0.z; pix = __float_as_uint(s0.w);
+                dx = s1.x; dy = s1.y; dz = s1.z; tr = s1.w; tg = s2.x; tb = s2.y;
+            }
+        }
+        float cr = 0.0f, cg = 0.0f, cb = 0.0f;     // radiance this path adds now
+        bool add = false;
+        if (alive) {
+            RayT r;
+            make_ray(r, ox, oy, oz, dx, dy, dz);
+            Best best;
+            const bool hit = closest_hit<STATS>(k, r, k.t_min, __int_as_float(0x7F800000) /* +inf */, best, cn, w.error_flag);
+            if (STATS) ++n_rays;
+            if (DEPTH0 && w.hit_ids) w.hit_ids[pix] = hit ? best.id : -1;
+            float Px = 0, Py = 0, Pz = 0, nx = 0, ny = 0, nz = 0;
+            uint32_t mat = 0;
+            if (hit) {
+                Px = ox + best.t * dx; Py = oy + best.t * dy; Pz = oz + best.t * dz;      // Test.hlsl:28
+                hit_frame(k, best, Px, Py, Pz, nx, ny, nz, mat);
+            }
+            if (k.shade_mode == PTB_SHADE_NORMALS) {
+                if (hit) { cr = nx * 0.5f + 0.5f; cg = ny * 0.5f + 0.5f; cb = nz * 0.5f + 0.5f; }   // Test.hlsl:31
+                else { cr = uvx; cg = uvy; cb = 0.0f; }                                              // Test.hlsl:36
+                add = true;
+                alive = false;
+            } else if (!hit) {
+                const float a = (dy + 1.0f) * 0.5f;
+                cr = tr * ((1.0f - a) * k.sky_h[0] + a * k.sky_z[0]);
+                cg = tg * ((1.0f - a) * k.sky_h[1] + a * k.sky_z[1]);
+                cb = tb * ((1.0f - a) * k.sky_h[2] + a * k.sky_z[2]);
+                add = true;
+                alive = false;
+            } else if (w.depth == k.max_depth) {
+                alive = false;                      // bounce budget spent: contributes nothing
+            } else {
+                const ptb_material m = k.materials[mat < k.n_materials ? mat : 0u];
+                const U3 v = pcg3d(pix, w.sample, k.seed + (w.depth + 1u) * 0x9E3779B9u);
+                if (STATS) ++n_scatter;
+                if (scatter(m, dx, dy, dz, nx, ny, nz, bits_to_unit(v.x), bits_to_unit(v.y), bits_to_unit(v.z))) {
+                    tr = tr * m.albedo[0]; tg = tg * m.albedo[1]; tb = tb * m.albedo[2];
+                    ox = Px; oy = Py; oz = Pz;
+                } else {
+                    alive = false;
+                }
+            }
+            if (DEPTH0) {
+                float4 acc = w.accum[pix];
+                acc.x = acc.x + cr; acc.y = acc.y + cg; acc.z = acc.z + cb; acc.w = acc.w + 1.0f;
+                w.accum[pix] = acc;
+            } else if (add) {
+                float4 acc = w.accum[pix];
+                acc.x = acc.x + cr; acc.y = acc.y + cg; acc.z = acc.z + cb;
+                w.accum[pix] = acc;
+            }
+        }
+        // queue compaction: warp ballot + prefix popcount, one atomic per warp
+        const unsigned live = __ballot_sync(FULL, alive);
+        if (live) {
+            uint32_t obase = 0;
+            if (lane == 0) obase = atomicAdd(w.n_out, (uint32_t)__popc(live));
+            obase = __shfl_sync(FULL, obase, 0);
+            if (alive) {
+                const uint32_t o = obase + (uint32_t)__popc(live & ((1u << lane) - 1u));
+                w.out.s0[o] = make_float4(ox, oy, oz, __uint_as_float(pix));
+                w.out.s1[o] = make_float4(dx, dy, dz, tr);
+                w.out.s2[o] = make_float2(tg, tb);
+            }
+        }
+    }
+    if (STATS) {
+        unsigned long long v[4] = {cn.nodes, cn.prims, n_rays, n_scatter};
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int o = 16; o; o >>= 1) v[j] += __shfl_xor_sync(FULL, v[j], o);
+        uint32_t ms = cn.max_stack;
+#pragma unroll
+        for (int o = 16; o; o >>= 1) ms = max(ms, __shfl_xor_sync(FULL, ms, o));
+        if (lane == 0) {
+            atomicAdd(&w.stats->nodes_visited, v[0]);
+            atomicAdd(&w.stats->prims_tested, v[1]);
+            atomicAdd(&w.stats->rays, v[2]);
+            atomicAdd(&w.stats->scatters, v[3]);
+            atomicMax(&w.stats->max_stack, (unsigned long long)ms);
+            if (DEPTH0 && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&w.stats->paths, (unsigned long long)w.n0);
+        }
+    }
+}
+
+// ---- upload helpers -------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) sphere_bounds_kernel(const float4 *__restrict__ sph, uint32_t n, float4 *lo, float4 *hi)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 c = sph[i];
+    const float r = fabsf(c.w);
+    lo[i] = make_float4(c.x - r, c.y - r, c.z - r, 0.0f);
+    hi[i] = make_float4(c.x + r, c.y + r, c.z + r, 0.0f);
+}
+
+__global__ void __launch_bounds__(256) tri_bounds_kernel(const float *__restrict__ v, uint32_t n, float4 *lo, float4 *hi)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float *p = v + 9 * (size_t)i;
+    lo[i] = make_float4(fminf(p[0], fminf(p[3], p[6])), fminf(p[1], fminf(p[4], p[7])), fminf(p[2], fminf(p[5], p[8])), 0.0f);
+    hi[i] = make_float4(fmaxf(p[0], fmaxf(p[3], p[6])), fmaxf(p[1], fmaxf(p[4], p[7])), fmaxf(p[2], fmaxf(p[5], p[8])), 0.0f);
+}
+
+__global__ void __launch_bounds__(256) pack_spheres_kernel(const float4 *__restrict__ in, const uint32_t *__restrict__ mat,
+                                                           const uint32_t *__restrict__ order, uint32_t n, float4 *out, uint2 *meta)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t src = order[i];
+    out[i] = in[src];
+    meta[i] = make_uint2(src, mat[src]);
+}
+
+__global__ void __launch_bounds__(256) pack_tris_kernel(const float *__restrict__ v, const uint32_t *__restrict__ mat,
+                                                        const uint32_t *__restrict__ order, uint32_t n, uint32_t id_base, float4 *out)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t src = order[i];
+    const float *p = v + 9 * (size_t)src;
+    out[3 * (size_t)i + 0] = make_float4(p[0], p[1], p[2], __int_as_float((int)(id_base + src)));
+    out[3 * (size_t)i + 1] = make_float4(p[3] - p[0], p[4] - p[1], p[5] - p[2], __int_as_float((int)mat[src]));
+    out[3 * (size_t)i + 2] = make_float4(p[6] - p[0], p[7] - p[1], p[8] - p[2], 0.0f);
+}
+
+__global__ void __launch_bounds__(256) frame_finish_kernel(const float4 *__restrict__ accum, float4 *f32_out, uint32_t *rgba8_out,
+                                                           uint32_t n)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        float4 c = accum[i];
+        c.w = 1.0f;
+        if (f32_out) f32_out[i] = c;
+        rgba8_out[i] = pack_rgba8(c.x, c.y, c.z, c.w);
+    }
+}
+
+template <bool STATS>
+__global__ void __launch_bounds__(256) trace_rays_kernel(const SceneK k, uint64_t n, const float *__restrict__ o,
+                                                         const float *__restrict__ d, float t_min, float t_max, int mode,
+                                                         int32_t *out_prim, float *out_t, uint32_t *error_flag)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    RayT r;
+    make_ray(r, o[3 * i], o[3 * i + 1], o[3 * i + 2], d[3 * i], d[3 * i + 1], d[3 * i + 2]);
+    Counters cn;
+    Best best;
+    if (mode == 0) {
+        const bool hit = closest_hit<STATS>(k, r, t_min, t_max, best, cn, error_flag);
+        out_prim[i] = hit ? best.id : -1;
+        if (out_t) out_t[i] = hit ? best.t : 0.0f;
+    } else {
+        best.t = t_max; best.id = -1; best.pos = 0; best.cls = 0;
+        bool hit = traverse<0, true, STATS>(k, r, t_min, t_max, best, cn, error_flag);
+        if (!hit) hit = traverse<1, true, STATS>(k, r, t_min, t_max, best, cn, error_flag);
+        out_prim[i] = hit ? 1 : 0;
+    }
+}
+
+int g_wave_blocks[2][2] = {{0, 0}, {0, 0}};
+
+template <bool DEPTH0, bool STATS>
+int wave_blocks()
+{
+    int &cached = g_wave_blocks[DEPTH0][STATS];
+    if (cached == 0) {
+        int per_sm = 0, dev = 0, sms = 148;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bounce_kernel<DEPTH0, STATS>, 256, 0) != cudaSuccess || per_sm < 1)
+            per_sm = 1;
+        cached = per_sm * sms;
+    }
+    return cached;
+}
+
+}  // namespace
+
+cudaError_t launch_sphere_bounds(const float4 *sph, uint32_t n, float4 *lo, float4 *hi, cudaStream_t s)
+{
+    if (n) sphere_bounds_kernel<<<(n + 255u) / 256u, 256, 0, s>>>(sph, n, lo, hi);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_tri_bounds(const float *verts9, uint32_t n, float4 *lo, float4 *hi, cudaStream_t s)
+{
+    if (n) tri_bounds_kernel<<<(n + 255u) / 256u, 256, 0, s>>>(verts9, n, lo, hi);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pack_spheres(const float4 *sph_in, const uint32_t *mat_in, const uint32_t *order, uint32_t n, float4 *sph_out,
+                                uint2 *meta_out, cudaStream_t s)
+{
+    if (n) pack_spheres_kernel<<<(n + 255u) / 256u, 256, 0, s>>>(sph_in, mat_in, order, n, sph_out, meta_out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pack_tris(const float *verts9, const uint32_t *mat_in, const uint32_t *order, uint32_t n, uint32_t id_base,
+                             float4 *tri_out, cudaStream_t s)
+{
+    if (n) pack_tris_kernel<<<(n + 255u) / 256u, 256, 0, s>>>(verts9, mat_in, order, n, id_base, tri_out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, int32_t *hit_ids, uint32_t sample, bool jitter,
+                              cudaStream_t s, uint64_t *launches)
+{
+    const uint32_t rows = k.row_offset < k.height ? (k.height - k.row_offset + k.row_stride - 1u) / k.row_stride : 0u;
+    const uint32_t n0 = rows * k.width;
+    if (n0 == 0) return cudaSuccess;
+    const uint32_t depths = k.shade_mode == PTB_SHADE_NORMALS ? 1u : k.max_depth + 1u;
+    // counters: [0, depths] queue sizes, [depths+1, 2*depths+1] work cursors
+    cudaError_t e = cudaMemsetAsync(st->counts, 0, sizeof(uint32_t) * st->counts_len, s);
+    if (e != cudaSuccess) return e;
+    for (uint32_t d = 0; d < depths; ++d) {
+        WaveArgs w{};
+        w.in = st->q[(d + 1u) & 1u];
+        w.out = st->q[d & 1u];
+        w.n_in = st->counts + d;
+        w.n_out = st->counts + d + 1u;
+        w.cursor = st->counts + (k.max_depth + 2u) + d;
+        w.n0 = n0;
+        w.depth = d;
+        w.sample = sample;
+        w.jitter = jitter ? 1 : 0;
+        w.accum = accum;
+        w.hit_ids = hit_ids;
+        w.stats = st->stats;
+        w.error_flag = st->error_flag;
+        if (d == 0) {
+            if (st->count_stats) bounce_kernel<true, true><<<wave_blocks<true, true>(), 256, 0, s>>>(k, w);
+            else bounce_kernel<true, false><<<wave_blocks<true, false>(), 256, 0, s>>>(k, w);
+        } else {
+            if (st->count_stats) bounce_kernel<false, true><<<wave_blocks<false, true>(), 256, 0, s>>>(k, w);
+            else bounce_kernel<false, false><<<wave_blocks<false, false>(), 256, 0, s>>>(k, w);
+        }
+        if (launches) ++*launches;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_frame_finish(const float4 *accum, float4 *f32_out, uint32_t *rgba8_out, uint32_t n_pixels, cudaStream_t s)
+{
+    const unsigned blocks = min((n_pixels + 255u) / 256u, 148u * 8u);
+    frame_finish_kernel<<<blocks, 256, 0, s>>>(accum, f32_out, rgba8_out, n_pixels);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_trace_rays(const SceneK &k, SceneState *st, uint64_t n, const float *o, const float *d, float t_min, float t_max,
+                              int mode, int32_t *out_prim, float *out_t, cudaStream_t s)
+{
+    if (n == 0) return cudaSuccess;
+    const unsigned blocks = (unsigned)((n + 255u) / 256u);
+    if (st->count_stats) trace_rays_kernel<true><<<blocks, 256, 0, s>>>(k, n, o, d, t_min, t_max, mode, out_prim, out_t, st->error_flag);
+    else trace_rays_kernel<false><<<blocks, 256, 0, s>>>(k, n, o, d, t_min, t_max, mode, out_prim, out_t, st->error_flag);
+    return cudaGetLastError();
+}
+
+}  // namespace ptb

@@ -7,6 +7,8 @@
 
 #include "../../include/ptb200.h"
 
+struct ptb_context;
+
 namespace ptb {
 
 // Launch-uniform parameters of the CSMain-equivalent kernels (passed by value as a kernel
@@ -61,6 +63,16 @@ cudaError_t launch_resolve(const float4 *accum, uint32_t *out8, uint32_t n_pixel
                            uint32_t flags, cudaStream_t s);
 cudaError_t launch_present(const uint32_t *src, uint32_t sw, uint32_t sh, uint32_t *dst, uint32_t dw,
                            uint32_t dh, uint32_t flags, cudaStream_t s);
+
+// scene.cu — the scene path (n3-n7) behind ptb_compute_frame / ptb_render_samples / ptb_wait
+void scene_destroy(ptb_context *ctx);
+bool scene_resident(const ptb_context *ctx);
+int scene_compute_frame(ptb_context *ctx);
+int scene_render_samples(ptb_context *ctx, uint32_t first_sample, uint32_t n_samples, int jitter);
+int scene_wait_check(ptb_context *ctx);
+// api.cu — error plumbing shared by the translation units
+int fail_msg(ptb_context *ctx, int code, const char *msg);
+int fail_cuda(ptb_context *ctx, cudaError_t e, const char *what);
 
 }  // namespace ptb
 

@@ -144,6 +144,65 @@ class NativeTracer:
     def set_accum_buffer(self, device_ptr: Optional[int]) -> None:
         self._ck(self._lib.ptb_set_accum_buffer(self._ctx, device_ptr))
 
+    # -- scene path (n3-n7) ------------------------------------------------------------------
+    def upload_scene(self, scene, *, max_leaf: int = 0, count_stats: bool = False) -> None:
+        """Upload a `scenes.Scene` (host arrays) and build its hierarchies on the GPU."""
+        d = _lib.SceneDesc()
+        d.struct_size = C.sizeof(_lib.SceneDesc)
+        d.n_spheres = scene.n_spheres
+        d.spheres = scene.spheres.ctypes.data
+        d.sphere_material = scene.sphere_material.ctypes.data
+        d.n_triangles = scene.n_triangles
+        d.tri_vertices = scene.triangles.ctypes.data
+        d.tri_material = scene.tri_material.ctypes.data
+        d.n_materials = len(scene.materials)
+        d.materials = scene.materials.ctypes.data
+        for name, src in (("cam_origin", scene.cam_origin), ("cam_u", scene.cam_u), ("cam_v", scene.cam_v),
+                          ("cam_w", scene.cam_w), ("sky_horizon", scene.sky_horizon), ("sky_zenith", scene.sky_zenith)):
+            getattr(d, name)[:] = [float(v) for v in src]
+        d.t_min = float(scene.t_min)
+        d.shade_mode = int(scene.shade_mode)
+        d.max_leaf = max_leaf
+        d.flags = _lib.SCENE_COUNT_STATS if count_stats else 0
+        self._ck(self._lib.ptb_upload_scene(self._ctx, C.byref(d)))
+
+    def clear_scene(self) -> None:
+        self._ck(self._lib.ptb_clear_scene(self._ctx))
+
+    def scene_info(self) -> dict:
+        info = _lib.SceneInfo()
+        self._ck(self._lib.ptb_scene_info_get(self._ctx, C.byref(info)))
+        return {k: getattr(info, k) for k, _ in _lib.SceneInfo._fields_}
+
+    def scene_stats(self) -> dict:
+        st = _lib.SceneStats()
+        self._ck(self._lib.ptb_scene_stats_get(self._ctx, C.byref(st)))
+        return {k: int(getattr(st, k)) for k, _ in _lib.SceneStats._fields_}
+
+    def scene_stats_reset(self) -> None:
+        self._ck(self._lib.ptb_scene_stats_reset(self._ctx))
+
+    def read_bvh(self, which: int):
+        """-> (nodes (n,16) float32 view of the 64 B nodes, order (n_prims,) uint32)."""
+        nn, npr = C.c_uint32(), C.c_uint32()
+        self._ck(self._lib.ptb_scene_read_bvh(self._ctx, which, None, 0, C.byref(nn), None, 0, C.byref(npr)))
+        nodes = np.zeros((nn.value, 16), np.float32)
+        order = np.zeros(npr.value, np.uint32)
+        self._ck(self._lib.ptb_scene_read_bvh(self._ctx, which, nodes.ctypes.data, nn.value, C.byref(nn),
+                                              order.ctypes.data, npr.value, C.byref(npr)))
+        return nodes, order
+
+    def trace_rays(self, origins: np.ndarray, dirs: np.ndarray, t_min: float, t_max: float, any_hit: bool = False):
+        """Closest-hit (-> prim ids, t) or any-hit (-> 0/1 flags, None) queries with host ray arrays."""
+        o = np.ascontiguousarray(origins, np.float32).reshape(-1, 3)
+        d = np.ascontiguousarray(dirs, np.float32).reshape(-1, 3)
+        assert o.shape == d.shape
+        prim = np.empty(len(o), np.int32)
+        t = np.zeros(len(o), np.float32)
+        self._ck(self._lib.ptb_trace_rays(self._ctx, len(o), o.ctypes.data, d.ctypes.data, t_min, t_max,
+                                          1 if any_hit else 0, prim.ctypes.data, t.ctypes.data))
+        return (prim, None) if any_hit else (prim, t)
+
     # -- present-equivalent ----------------------------------------------------------------
     def present(self, dst_w: Optional[int] = None, dst_h: Optional[int] = None, srgb: bool = True) -> None:
         self._ck(self._lib.ptb_present(self._ctx, dst_w or self.width, dst_h or self.height,

@@ -1,0 +1,169 @@
+"""CPU tests of the scene-path oracle (oracle/pt_scene_oracle.c) and the scene generators.
+
+The scene stages (SURVEY.md §8 a' n3-n7) have no reference counterpart, so the oracle is pinned where
+it can be: the default scene in the reference's shading must reproduce pto_csmain_frame (itself
+pinned to SURVEY App. B), the oracle's own BVH must agree with brute force, and the sampling spec is
+checked against analytic properties.  Frozen digests guard against silent spec drift.
+"""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle import pt_oracle as O
+from oracle import pt_scene_oracle as S
+from pathtracing_b200 import scenes
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "scene_digests.json")
+
+
+def bits(a):
+    return np.ascontiguousarray(a, np.float32).view(np.uint32)
+
+
+def digest(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+@pytest.mark.parametrize("size,div", [((320, 180), None), ((1920, 1080), None), ((320, 180), (1080, 1080)), ((97, 33), None)])
+def test_default_scene_reproduces_csmain(size, div):
+    w, h = size
+    ref = O.csmain_frame(O.frame_params(w, h, uv_div=div))
+    for brute in (False, True):
+        fr = S.SceneOracle(scenes.default_scene(), w, h, max_depth=0, uv_div=div).frame(brute=brute)
+        assert np.array_equal(bits(fr["f32"]), bits(ref["f32"]))
+        assert np.array_equal(fr["hit"], ref["hit"])
+        assert np.array_equal(fr["rgba8"], ref["rgba8"])
+        assert fr["hits"] == ref["hits"]
+
+
+def test_default_scene_hit_counts_of_survey_appendix_b():
+    assert S.SceneOracle(scenes.default_scene(), 1920, 1080).frame()["hits"] == 305317
+    assert S.SceneOracle(scenes.default_scene(), 320, 180).frame()["hits"] == 8469
+
+
+@pytest.mark.parametrize("make", [lambda: scenes.mixed_small(), lambda: scenes.random_spheres(120, width=96, height=54),
+                                  lambda: scenes.triangle_terrain(cells=16, layers=2, width=96, height=54)])
+def test_oracle_bvh_equals_brute_force(make):
+    sc = make()
+    w, h = 96, 54
+    so = S.SceneOracle(sc, w, h, max_depth=6)
+    a, b = so.frame(seed=3), so.frame(seed=3, brute=True)
+    assert np.array_equal(a["hit"], b["hit"]) and np.array_equal(bits(a["f32"]), bits(b["f32"]))
+    assert np.array_equal(bits(so.accumulate(0, 3)), bits(so.accumulate(0, 3, brute=True)))
+    rng = np.random.Generator(np.random.PCG64(5))
+    o = rng.uniform(-5, 5, (5000, 3)).astype(np.float32)
+    d = rng.normal(size=(5000, 3)).astype(np.float32)
+    p1, t1 = so.trace_rays(o, d, 1e-3, 1e30)
+    p2, t2 = so.trace_rays(o, d, 1e-3, 1e30, brute=True)
+    assert np.array_equal(p1, p2) and np.array_equal(bits(t1), bits(t2))
+    a1, _ = so.trace_rays(o, d, 1e-3, 2.5, any_hit=True)
+    a2, _ = so.trace_rays(o, d, 1e-3, 2.5, any_hit=True, brute=True)
+    assert np.array_equal(a1, a2)
+    # any-hit is consistent with closest-hit
+    p3, t3 = so.trace_rays(o, d, 1e-3, 2.5)
+    assert np.array_equal(a1 != 0, p3 >= 0)
+
+
+def test_closest_hit_ties_keep_the_smaller_primitive_id():
+    tri = np.array([[-1, -1, 0, 1, -1, 0, 0, 1, 0]], np.float32)
+    sc = scenes.Scene(spheres=np.zeros((0, 4)), sphere_material=[], triangles=np.tile(tri, (5, 1)), tri_material=[0] * 5,
+                      materials=scenes.materials_array([(0, (0.5, 0.5, 0.5), 0, 1.5)]))
+    so = S.SceneOracle(sc, 4, 4)
+    for brute in (False, True):
+        p, t = so.trace_rays([[0, 0, 1]], [[0, 0, -1]], 1e-3, 1e30, brute=brute)
+        assert p[0] == 0 and t[0] == 1.0
+
+
+def test_sincos_polynomial_accuracy_and_symmetry():
+    u = np.linspace(0, 1, 4097, endpoint=False, dtype=np.float32)
+    sc = np.array([S.sincos2pi(float(x)) for x in u])
+    assert np.abs(sc[:, 0] - np.sin(2 * np.pi * u.astype(np.float64))).max() < 2e-7
+    assert np.abs(sc[:, 1] - np.cos(2 * np.pi * u.astype(np.float64))).max() < 2e-7
+    s0, c0 = S.sincos2pi(0.0)
+    assert abs(s0) < 2e-7 and abs(c0 - 1.0) < 2e-7
+    s, c = S.sincos2pi(0.25)
+    assert abs(s - 1.0) < 2e-7 and abs(c) < 2e-7
+
+
+def test_unit_vector_is_unit_and_uniform():
+    rng = np.random.Generator(np.random.PCG64(1))
+    v = np.array([S.unit_vector(float(a), float(b)) for a, b in rng.uniform(0, 1, (4000, 2)).astype(np.float32)])
+    assert np.abs(np.linalg.norm(v, axis=1) - 1).max() < 1e-6
+    assert np.abs(v.mean(axis=0)).max() < 0.05          # no preferred direction
+
+
+def test_scatter_laws():
+    lam, met, mir, die = scenes.materials_array([(0, (0.3, 0.5, 0.7), 0, 1.5), (1, (0.9, 0.8, 0.7), 0.2, 1.5),
+                                                 (1, (1, 1, 1), 0.0, 1.5), (2, (1, 1, 1), 0, 1.5)])
+    n = np.array([0, 1, 0], np.float32)
+    d = np.array([0.6, -0.8, 0.0], np.float32)
+    rng = np.random.Generator(np.random.PCG64(2))
+    for u1, u2, u3 in rng.uniform(0, 1, (200, 3)).astype(np.float32):
+        ok, out, att = S.scatter(lam, d, n, u1, u2, u3)
+        assert ok and out @ n > -1e-6 and abs(np.linalg.norm(out) - 1) < 1e-6 and np.allclose(att, [0.3, 0.5, 0.7])
+        ok, out, att = S.scatter(met, d, n, u1, u2, u3)
+        assert (not ok) or out @ n > 0
+    ok, out, _ = S.scatter(mir, d, n, 0.3, 0.3, 0.3)
+    assert ok and np.allclose(out, [0.6, 0.8, 0.0], atol=1e-6)            # mirror reflection
+    # dielectric: Snell's law when refracting, total internal reflection from inside at a grazing angle
+    ok, out, _ = S.scatter(die, d, n, 0.1, 0.1, 0.999)
+    assert ok and out[1] < 0 and abs(out[0] / 0.6 - 1 / 1.5) < 1e-5
+    ok, out, _ = S.scatter(die, np.array([0.8, 0.6, 0], np.float32), n, 0.1, 0.1, 0.999)   # leaving, sin > 1/1.5
+    assert ok and out[1] < 0                                               # reflected back inside
+    # back faces flip the normal for every material
+    ok, out, _ = S.scatter(lam, np.array([0.6, 0.8, 0], np.float32), n, 0.2, 0.7, 0.5)
+    assert ok and out @ n < 1e-6
+
+
+def test_white_furnace_and_depth_limit():
+    w, h = 48, 27
+    sc = scenes.Scene(spheres=[[0, 0, 0, 0.5]], sphere_material=[0], triangles=np.zeros((0, 9)), tri_material=[],
+                      materials=scenes.materials_array([(0, (1, 1, 1), 0, 1.5)]), sky_horizon=[1, 1, 1], sky_zenith=[1, 1, 1])
+    sc.look_at((0, 0, 2), (0, 0, 0), (0, 1, 0), 40, w, h)
+    acc = S.SceneOracle(sc, w, h, max_depth=16).accumulate(0, 4)
+    assert np.all(acc[..., 3] == 4) and np.all(np.abs(acc[..., :3] - 4) < 1e-4)
+    # max_depth 0: pixels whose primary ray hits stay black
+    so0 = S.SceneOracle(sc, w, h, max_depth=0)
+    fr = so0.frame()
+    assert np.all(fr["f32"][fr["hit"] >= 0][:, :3] == 0) and np.all(fr["f32"][fr["hit"] < 0][:, :3] == 1)
+
+
+def test_accumulate_is_progressive_and_sample_ranges_are_disjoint():
+    sc = scenes.mixed_small(width=64, height=36)
+    so = S.SceneOracle(sc, 64, 36, max_depth=4)
+    a = so.accumulate(0, 5, seed=4)
+    b = so.accumulate(0, 2, seed=4)
+    so.accumulate(2, 3, seed=4, accum=b)
+    assert np.array_equal(bits(a), bits(b))
+    assert not np.array_equal(so.accumulate(0, 1, seed=4), so.accumulate(1, 1, seed=4))
+
+
+def test_generators_are_deterministic_and_match_the_config_sizes():
+    a, b = scenes.random_spheres(500), scenes.random_spheres(500)
+    assert a.n_spheres == 501 and np.array_equal(a.spheres, b.spheres) and np.array_equal(a.materials, b.materials)
+    kinds = a.materials["type"][1:]
+    assert 0.5 < (kinds == 0).mean() < 0.7 and 0.15 < (kinds == 1).mean() < 0.35 and 0.08 < (kinds == 2).mean() < 0.25
+    t = scenes.triangle_terrain(cells=32, layers=2)
+    assert t.n_triangles == 32 * 32 * 2 * 2
+    assert 2 * 512 * 512 * 2 == 1048576            # the full C4 configuration
+
+
+def test_frozen_digests():
+    """Oracle outputs frozen at the commit that introduced the scene spec (tests/golden/make_scene_golden.py)."""
+    gold = json.load(open(GOLD))
+    for name, (make, w, h, depth) in CASES.items():
+        so = S.SceneOracle(make(w, h), w, h, max_depth=depth)
+        fr = so.frame(seed=1)
+        acc = so.accumulate(0, 2, seed=1)
+        got = {"hit": digest(fr["hit"]), "f32": digest(fr["f32"]), "accum2": digest(acc)}
+        assert got == gold[name], name
+
+
+CASES = {
+    "mixed_160x90_d8": (lambda w, h: scenes.mixed_small(width=w, height=h), 160, 90, 8),
+    "spheres500_160x90_d8": (lambda w, h: scenes.random_spheres(500, width=w, height=h), 160, 90, 8),
+    "terrain32_160x90_d4": (lambda w, h: scenes.triangle_terrain(cells=32, layers=2, width=w, height=h), 160, 90, 4),
+}
