@@ -44,7 +44,43 @@ WORKLOADS = {
     "c2": dict(width=1920, height=1080, spp=64, name="BASELINE configs[1]: default scene 1920x1080, 64 spp/step"),
     "c5": dict(width=3840, height=2160, spp=1024, name="BASELINE configs[4]: default scene 3840x2160, 1024 spp/step"),
     "frame": dict(width=1920, height=1080, spp=1, name="literal reference frame: 1920x1080, 1 spp, no jitter, RGBA8"),
+    # scene workloads (SURVEY.md 8 a' rows n3-n7: no reference counterpart, oracle = this repo's own restatement)
+    "c3": dict(width=1920, height=1080, spp=256, scene="spheres", max_depth=8,
+               name="BASELINE configs[2]: 500 random spheres (Lambert/metal/dielectric) 1920x1080, 256 spp/step, max depth 8"),
+    "c4": dict(width=3840, height=2160, spp=256, scene="terrain", max_depth=8,
+               name="BASELINE configs[3]: 1,048,576-triangle terrain, GPU-built BVH, 3840x2160, 256 spp/step, max depth 8"),
 }
+STATE_BYTES_PER_PATH = 40.0     # wavefront path state (2 x float4 + float2), read once and written once per segment
+
+
+def make_scene(wl):
+    from pathtracing_b200 import scenes
+    if wl.get("scene") == "spheres":
+        return scenes.random_spheres(500, seed=1, width=wl["width"], height=wl["height"])
+    if wl.get("scene") == "terrain":
+        return scenes.triangle_terrain(512, 2, seed=2, width=wl["width"], height=wl["height"])
+    return None
+
+
+def cpu_scene_sample(wl, scene, spp_sample, steps, warmup):
+    """Times the scene oracle (own CPU BVH, OpenMP over rows) on `spp_sample` samples per pixel per step."""
+    import numpy as np
+    from oracle import pt_oracle as O
+    from oracle import pt_scene_oracle as S
+    W, H = wl["width"], wl["height"]
+    so = S.SceneOracle(scene, W, H, max_depth=wl["max_depth"])
+    acc = np.zeros((H, W, 4), np.float32)
+    times, first = [], 0
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        so.accumulate(first, spp_sample, seed=0, jitter=True, accum=acc)
+        dt = time.perf_counter() - t0
+        first += spp_sample
+        if i >= warmup:
+            times.append(dt)
+    total = sum(times)
+    so.close()
+    return W * H * spp_sample * len(times) / total / 1e6, 1e3 * total / len(times), O.max_threads()
 
 
 def load_peaks():
@@ -158,13 +194,21 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    wl = WORKLOADS[args.workload]
+    wl = dict(WORKLOADS[args.workload])
+    if args.spp:
+        wl["spp"] = args.spp
     W, H, spp = wl["width"], wl["height"], wl["spp"]
     jitter = args.workload != "frame"
-    spp_sample = 1 if not jitter else max(1, min(spp, args.cpu_spp))
-    ms, ms_step, threads = cpu_sample(W, H, spp_sample, args.steps, args.warmup, jitter)
-    sample = (f"{W}x{H}, {spp_sample} of {spp} spp per step ({'jittered accumulate + resolve' if jitter else 'csmain frame'}), "
-              f"{args.steps} steps; Msamples/s is spp-invariant")
+    if wl.get("scene"):
+        spp_sample = 1
+        ms, ms_step, threads = cpu_scene_sample(wl, make_scene(wl), spp_sample, min(args.steps, 3), min(args.warmup, 1))
+        sample = (f"{W}x{H}, {spp_sample} of {spp} spp per step (scene oracle: multi-bounce paths over its own CPU BVH), "
+                  f"{min(args.steps, 3)} steps; Msamples/s is spp-invariant")
+    else:
+        spp_sample = 1 if not jitter else max(1, min(spp, args.cpu_spp))
+        ms, ms_step, threads = cpu_sample(W, H, spp_sample, args.steps, args.warmup, jitter)
+        sample = (f"{W}x{H}, {spp_sample} of {spp} spp per step ({'jittered accumulate + resolve' if jitter else 'csmain frame'}), "
+                  f"{args.steps} steps; Msamples/s is spp-invariant")
     line = {
         "impl": "reference", "metric": "Msamples/s", "value": ms, "unit": "Msamples/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
@@ -196,8 +240,11 @@ def run_b200(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
 
-    wl = WORKLOADS[args.workload]
+    wl = dict(WORKLOADS[args.workload])
+    if args.spp:
+        wl["spp"] = args.spp
     W, H, spp = wl["width"], wl["height"], wl["spp"]
+    scene = make_scene(wl)
     n_pix = W * H
     strong = args.workload == "c5"
     literal = args.workload == "frame"
@@ -211,7 +258,7 @@ def run_b200(args):
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)                   # > 126 MB L2
 
     with torch.cuda.stream(stream):
-        eng = GpuEngine(W, H, local, seed=0, stream=stream)
+        eng = GpuEngine(W, H, local, seed=0, stream=stream, scene=scene, max_depth=wl.get("max_depth", 0))
         t = eng.tracer
         sr = ShardedRenderer(eng, mode=args.shard)
         merge_every_step = strong or world == 1        # c2 at N>1: one merge for the whole progressive render
@@ -288,9 +335,25 @@ def run_b200(args):
         barrier()
         e2e_s = time.perf_counter() - t0
 
+        # ---- scene workloads: per-sample work counters from the counting build (untimed, 2 spp) ----------------
+        scene_counters = None
+        if scene is not None and rank == 0:
+            with NativeTracer(W, H, device=local, seed=0, max_depth=wl["max_depth"], stream=stream.cuda_stream) as tc:
+                tc.upload_scene(scene, count_stats=True)
+                tc.render_samples(0, 2)
+                tc.wait()
+                st = tc.scene_stats()
+                info = tc.scene_info()
+            p = float(st["paths"])
+            scene_counters = {"segments_per_sample": st["rays"] / p, "nodes_visited_per_sample": st["nodes_visited"] / p,
+                              "prims_tested_per_sample": st["prims_tested"] / p, "scatters_per_sample": st["scatters"] / p,
+                              "max_stack": st["max_stack"], "bvh_build_ms": info["build_ms"],
+                              "nodes": info["sphere_nodes"] + info["triangle_nodes"],
+                              "leaves": info["sphere_leaves"] + info["triangle_leaves"], "scene_bytes": info["device_bytes"]}
+
         # ---- the literal reference frame (1 spp, RGBA8) as a secondary line ------------------------------
         literal_frame = None
-        if rank == 0 and world == 1 and not literal:
+        if rank == 0 and world == 1 and not literal and scene is None:
             with NativeTracer(W, H, device=local, stream=stream.cuda_stream) as tf:
                 for _ in range(5):
                     tf.compute_frame()
@@ -344,6 +407,25 @@ def run_b200(args):
                     "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None,
                     "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peaks['source']})",
                     "algorithmic_bytes_per_launch": alg, "launch_ms": k_ms}
+        elif scene is not None:
+            # algorithmic bytes per sample, COUNTED: 64 B per node visit, 16 B per sphere / 48 B per
+            # triangle test, 2 x 40 B of path state per segment, 32 B accumulation read-modify-write per sample
+            c = scene_counters
+            prim_b = 16.0 if wl["scene"] == "spheres" else 48.0
+            b_sample = (c["nodes_visited_per_sample"] * 64.0 + c["prims_tested_per_sample"] * prim_b +
+                        c["segments_per_sample"] * 2.0 * STATE_BYTES_PER_PATH + ACCUM_BYTES_PER_PIXEL)
+            n_launch = wl["max_depth"] + 1
+            alg = b_sample * pix_rank                                    # one wave (all bounces of one sample)
+            wave_ms = k_ms / max(1.0, spp_rank)
+            achieved = alg / (wave_ms * 1e-3) / 1e9
+            roof = {"kernel": "bounce_kernel", "bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"],
+                    "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None,
+                    "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peaks['source']}); the scene ({c['scene_bytes'] / 1e6:.1f} MB) is "
+                                   "L2-resident, so node/primitive fetch is served by L1/L2 and the kernel is latency / "
+                                   "divergence bound rather than HBM bound (DESIGN.md 7)",
+                    "algorithmic_bytes_per_sample": b_sample, "algorithmic_bytes_per_wave": alg,
+                    "launches_per_wave": n_launch, "wave_ms": wave_ms, "launch_ms": wave_ms / n_launch,
+                    "counters": c}
         else:
             fp32_peak = 148 * 128 * 2 * peaks["sm_max_mhz"] * 1e6 / 1e12     # TFLOP/s at max SM clock
             flops = FLOP_PER_SAMPLE * pix_rank * spp_rank
@@ -364,7 +446,11 @@ def run_b200(args):
 
         # ---- CPU baseline on this box's host cores (bounded sample) ------------------------------------------
         cpu = None
-        if world == 1 and not args.no_cpu_baseline:
+        if world == 1 and not args.no_cpu_baseline and scene is not None:
+            ms, _, threads = cpu_scene_sample(wl, scene, 1, 2, 1)
+            cpu = {"value": ms, "unit": "Msamples/s", "cores": threads, "kind": "port",
+                   "sample": f"{W}x{H}, 1 of {spp} spp per step x 2 steps, scene oracle (own CPU BVH), OpenMP over rows, {cpu_model()}"}
+        elif world == 1 and not args.no_cpu_baseline:
             spp_s = 1 if literal else max(1, min(spp, args.cpu_spp))
             ms, _, threads = cpu_sample(W, H, spp_s, 5, 1, jitter=not literal)
             cpu = {"value": ms, "unit": "Msamples/s", "cores": threads, "kind": "port",
@@ -383,6 +469,7 @@ def run_b200(args):
             "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl["name"], "width": W, "height": H, "spp_per_step_total": spp_step,
                        "spp_per_step_per_rank": spp_rank, "seed": 0, "jitter": not literal, "sharding": sharding,
+                       "max_depth": wl.get("max_depth", 0), "scene": scene.name if scene is not None else "default (Test.hlsl literals)",
                        "l2": "flushed between timed steps (256 MB fill, untimed)",
                        "timing": "per-step CUDA events on the launching stream, summed; max over ranks"},
             "roofline": roof,
@@ -414,6 +501,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel per step")
     ap.add_argument("--cpu-spp", type=int, default=16, help="spp per step of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--shard", default="samples", choices=["samples", "tiles"],

@@ -1,0 +1,28 @@
+"""Quick device timing of the scene workloads (development aid; bench.py --workload c3|c4 is the contract)."""
+import sys, time, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+from pathtracing_b200 import NativeTracer, scenes
+
+def run(name, sc, w, h, spp, depth, max_leaf=4):
+    with NativeTracer(w, h, max_depth=depth) as t:
+        t0 = time.time(); t.upload_scene(sc, max_leaf=max_leaf); up = time.time() - t0
+        info = t.scene_info()
+        t.render_samples(0, 2); t.wait()
+        t.timer_begin(); t.render_samples(2, spp); ms = t.timer_end()
+        print(f"{name}: {w}x{h} {spp}spp depth{depth} leaf{max_leaf}: {ms:.2f} ms -> {w*h*spp/ms/1e3:.1f} Msamples/s; upload {up*1e3:.0f} ms build {info['build_ms']:.2f} ms nodes s{info['sphere_nodes']} t{info['triangle_nodes']} leaves t{info['triangle_leaves']}", flush=True)
+    with NativeTracer(w, h, max_depth=depth) as t:
+        t.upload_scene(sc, max_leaf=max_leaf, count_stats=True)
+        t.render_samples(0, 2); t.wait()
+        st = t.scene_stats()
+        print("   per path: rays %.2f nodes %.1f prims %.1f scatters %.2f max_stack %d" % (st['rays']/st['paths'], st['nodes_visited']/st['paths'], st['prims_tested']/st['paths'], st['scatters']/st['paths'], st['max_stack']), flush=True)
+
+which = sys.argv[1] if len(sys.argv) > 1 else "all"
+if which in ("c3", "all"):
+    sc = scenes.random_spheres(500, width=1920, height=1080)
+    for ml in (1, 4, 8):
+        run("c3", sc, 1920, 1080, 8, 8, ml)
+if which in ("c4", "all"):
+    sc = scenes.triangle_terrain(512, 2, width=3840, height=2160)
+    for ml in (1, 4, 8):
+        run("c4", sc, 3840, 2160, 4, 8, ml)

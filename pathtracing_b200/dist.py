@@ -53,14 +53,19 @@ class LocalEngine(Protocol):
 class GpuEngine:
     """NativeTracer whose accumulation buffer and image are visible to torch.distributed."""
 
-    def __init__(self, width: int, height: int, device: int, seed: int = 0, stream: Optional[torch.cuda.Stream] = None):
+    def __init__(self, width: int, height: int, device: int, seed: int = 0, stream: Optional[torch.cuda.Stream] = None,
+                 scene=None, max_depth: int = 0, count_stats: bool = False):
         from .tracer import NativeTracer
         self.width, self.height = width, height
         self.device = torch.device("cuda", device)
         self.stream = stream or torch.cuda.current_stream(self.device)
         self.accum = torch.zeros((height, width, 4), dtype=torch.float32, device=self.device)
-        self.tracer = NativeTracer(width, height, device=device, seed=seed, stream=self.stream.cuda_stream)
+        self.tracer = NativeTracer(width, height, device=device, seed=seed, max_depth=max_depth,
+                                   stream=self.stream.cuda_stream)
         self.tracer.set_accum_buffer(self.accum.data_ptr())
+        if scene is not None:
+            # every rank holds a replica of the (read-only) scene and builds its own hierarchy (SURVEY.md §8e)
+            self.tracer.upload_scene(scene, count_stats=count_stats)
         self._image = None
 
     def set_row_shard(self, row_offset, row_stride):
