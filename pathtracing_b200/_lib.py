@@ -11,7 +11,7 @@ import subprocess
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
 _CSRC = os.path.join(_PKG, "csrc")
-LIB_PATH = os.path.join(_PKG, "libptb200.so")
+LIB_PATH = os.environ.get("PTB200_LIB") or os.path.join(_PKG, "libptb200.so")   # override: A/B experiments only
 HEADER_PATH = os.path.join(os.path.dirname(_PKG), "include", "ptb200.h")
 
 PTB_OK = 0

@@ -25,6 +25,9 @@ namespace ptb {
 namespace {
 
 constexpr int STACK_N = 64;
+#ifndef PTB_BOUNCE_MIN_BLOCKS
+#define PTB_BOUNCE_MIN_BLOCKS 4   // resident 256-thread blocks per SM the bounce kernel is compiled for (register cap)
+#endif
 constexpr unsigned FULL = 0xFFFFFFFFu;
 
 struct Counters {
@@ -33,15 +36,17 @@ struct Counters {
 
 struct RayT {
     float ox, oy, oz, dx, dy, dz;
-    float ix, iy, iz;      // 1/d (culling only: never reaches a result)
+    float ix, iy, iz;      // ~1/d      (culling only: never reaches a result)
+    float px, py, pz;      // -o * (1/d) (culling only; FMA form of the slab test)
     float a, a2, a4;       // d.d, 2*(d.d), 4*(d.d)  (Test.hlsl:17, hoisted per ray)
 };
 
 struct Best {
     float t;
-    int id;      // unified original primitive id (spheres 0..ns-1, triangles ns..)
-    int pos;     // leaf-order position inside its class
-    int cls;     // 0 sphere, 1 triangle
+    float t_cull;  // t * (1 + 2^-19): what node culling and stack pruning compare against
+    int id;        // unified original primitive id (spheres 0..ns-1, triangles ns..)
+    int pos;       // leaf-order position inside its class
+    int cls;       // 0 sphere, 1 triangle
 };
 
 __device__ __forceinline__ float dot3f(float ax, float ay, float az, float bx, float by, float bz)
@@ -52,11 +57,19 @@ __device__ __forceinline__ float dot3f(float ax, float ay, float az, float bx, f
     return s;
 }
 
+__device__ __forceinline__ float rcp_approx(float x)
+{
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
 __device__ __forceinline__ void make_ray(RayT &r, float ox, float oy, float oz, float dx, float dy, float dz)
 {
     r.ox = ox; r.oy = oy; r.oz = oz;
     r.dx = dx; r.dy = dy; r.dz = dz;
-    r.ix = 1.0f / dx; r.iy = 1.0f / dy; r.iz = 1.0f / dz;
+    r.ix = rcp_approx(dx); r.iy = rcp_approx(dy); r.iz = rcp_approx(dz);   // 1 ulp; absorbed by the culling slack
+    r.px = -(ox * r.ix); r.py = -(oy * r.iy); r.pz = -(oz * r.iz);
     r.a = dot3f(dx, dy, dz, dx, dy, dz);
     r.a2 = 2.0f * r.a;
     r.a4 = 4.0f * r.a;
@@ -105,24 +118,72 @@ __device__ __forceinline__ bool hit_triangle(const float4 v0, const float4 e1, c
     return true;
 }
 
-// Conservative slab test of one child box against [t_min, t_far]: boxes are padded at build
-// time and the interval is widened by ~8 ulp, so a box is never rejected when a primitive
-// inside it would be accepted.  fminf/fmaxf drop the NaN of 0*inf.
+// Conservative slab test of one child box against [t_min, t_far].  FMA_SLAB: t = fma(plane, 1/d, -o/d)
+// (6 FFMA per box; its cancellation error is at most half an ulp of the ray origin in space, covered
+// by the 2^-18-of-scene-extent padding the boxes get at build time, which includes the camera);
+// otherwise t = (plane - o) * (1/d) for rays whose origin may lie far outside the scene
+// (ptb_trace_rays).  The interval is widened by 2^-19 relative (approximate reciprocal + 3 roundings),
+// so a box is never rejected when a primitive inside it would be accepted.  fminf/fmaxf drop NaNs.
+template <bool FMA_SLAB>
 __device__ __forceinline__ bool slab(float lox, float hix, float loy, float hiy, float loz, float hiz, const RayT &r,
                                      float t_min, float t_far, float &t_near)
 {
-    const float ax = (lox - r.ox) * r.ix, bx = (hix - r.ox) * r.ix;
-    const float ay = (loy - r.oy) * r.iy, by = (hiy - r.oy) * r.iy;
-    const float az = (loz - r.oz) * r.iz, bz = (hiz - r.oz) * r.iz;
-    const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
+    float ax, bx, ay, by, az, bz;
+    if (FMA_SLAB) {
+        ax = fmaf(lox, r.ix, r.px); bx = fmaf(hix, r.ix, r.px);
+        ay = fmaf(loy, r.iy, r.py); by = fmaf(hiy, r.iy, r.py);
+        az = fmaf(loz, r.iz, r.pz); bz = fmaf(hiz, r.iz, r.pz);
+    } else {
+        ax = (lox - r.ox) * r.ix; bx = (hix - r.ox) * r.ix;
+        ay = (loy - r.oy) * r.iy; by = (hiy - r.oy) * r.iy;
+        az = (loz - r.oz) * r.iz; bz = (hiz - r.oz) * r.iz;
+    }
+    t_near = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
     const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_far));
-    t_near = tn * 0.999999f;
-    return t_near <= tf * 1.000001f;
+    return t_near <= tf * 1.000002f;
 }
 
-// Stack-based traversal of one hierarchy.  CLS 0 = spheres, 1 = triangles.  ANY: stop at the first
-// hit.  The closest hit keeps the smaller unified id on equal t (order independent).
-template <int CLS, bool ANY, bool STATS>
+template <int CLS, bool ANY>
+__device__ __forceinline__ bool test_leaf(const SceneK &k, int leaf, const RayT &r, float t_min, float t_max, Best &best,
+                                          uint32_t &prims)
+{
+    const uint32_t q = (uint32_t)~leaf;
+    const uint32_t first = q & LEAF_FIRST_MASK, count = (q >> LEAF_COUNT_SHIFT) + 1u;
+    prims += count;
+    for (uint32_t i = first; i < first + count; ++i) {
+        float t;
+        int id;
+        if (CLS == 0) {
+            const float4 cr = __ldg(&k.sph[i]);
+            if (!hit_sphere(cr, r, t_min, t_max, t)) continue;
+            if (ANY) return true;
+            if (!(t <= best.t)) continue;
+            id = (int)__ldg(&k.sph_meta[i]).x;
+        } else {
+            const float4 v0 = __ldg(&k.tri[3 * (size_t)i]), e1 = __ldg(&k.tri[3 * (size_t)i + 1]),
+                         e2 = __ldg(&k.tri[3 * (size_t)i + 2]);
+            if (!hit_triangle(v0, e1, e2, r, t_min, t_max, t)) continue;
+            if (ANY) return true;
+            if (!(t <= best.t)) continue;
+            id = __float_as_int(v0.w);
+        }
+        if (t < best.t || id < best.id || best.id < 0) {     // equal t: the smaller id wins (order independent)
+            best.t = t;
+            best.t_cull = t * 1.000002f;
+            best.id = id;
+            best.pos = (int)i;
+            best.cls = CLS;
+        }
+    }
+    return false;
+}
+
+// Stack-based traversal of one hierarchy: one loop, the current reference is either a node (test both
+// child boxes, descend into the nearer, push the farther with its entry distance) or a leaf (test its
+// primitives).  A "while-while" variant with a parked leaf was measured and was slower here (more
+// registers, later shrinking of the closest distance): profiles/r01_notes.md.
+// CLS 0 = spheres, 1 = triangles.  ANY: stop at the first hit.
+template <int CLS, bool ANY, bool STATS, bool FMA_SLAB>
 __device__ __forceinline__ bool traverse(const SceneK &k, const RayT &r, float t_min, float t_max, Best &best, Counters &cn,
                                          uint32_t *error_flag)
 {
@@ -132,76 +193,57 @@ __device__ __forceinline__ bool traverse(const SceneK &k, const RayT &r, float t
     int stack[STACK_N];
     float tstack[STACK_N];
     int sp = 0;
+    uint32_t prims = 0;
     for (;;) {
         if (cur >= 0) {
             const float4 na = __ldg(&nodes[cur].a), nb = __ldg(&nodes[cur].b), nc = __ldg(&nodes[cur].c);
             const int4 nd = __ldg(&nodes[cur].d);
             if (STATS) ++cn.nodes;
-            const float t_far = ANY ? t_max : best.t;
+            const float t_far = ANY ? t_max : best.t_cull;
             float tn0, tn1;
-            bool h0 = slab(na.x, na.y, na.z, na.w, nc.x, nc.y, r, t_min, t_far, tn0);
-            bool h1 = slab(nb.x, nb.y, nb.z, nb.w, nc.z, nc.w, r, t_min, t_far, tn1) && nd.y != EMPTY_REF;
+            const bool h0 = slab<FMA_SLAB>(na.x, na.y, na.z, na.w, nc.x, nc.y, r, t_min, t_far, tn0);
+            const bool h1 = slab<FMA_SLAB>(nb.x, nb.y, nb.z, nb.w, nc.z, nc.w, r, t_min, t_far, tn1) && nd.y != EMPTY_REF;
             if (h0 && h1) {
                 const bool swap = tn1 < tn0;
-                const int near_ref = swap ? nd.y : nd.x, far_ref = swap ? nd.x : nd.y;
+                cur = swap ? nd.y : nd.x;
                 if (sp < STACK_N) {
-                    stack[sp] = far_ref;
+                    stack[sp] = swap ? nd.x : nd.y;
                     tstack[sp] = swap ? tn0 : tn1;
                     ++sp;
                     if (STATS) cn.max_stack = max(cn.max_stack, (uint32_t)sp);
                 } else {
                     atomicOr(error_flag, 1u);
                 }
-                cur = near_ref;
                 continue;
             }
             if (h0) { cur = nd.x; continue; }
             if (h1) { cur = nd.y; continue; }
         } else {
-            const uint32_t q = (uint32_t)~cur;
-            const uint32_t first = q & LEAF_FIRST_MASK, count = (q >> LEAF_COUNT_SHIFT) + 1u;
-            for (uint32_t i = first; i < first + count; ++i) {
-                float t;
-                if (STATS) ++cn.prims;
-                if (CLS == 0) {
-                    const float4 cr = __ldg(&k.sph[i]);
-                    if (!hit_sphere(cr, r, t_min, t_max, t)) continue;
-                    if (ANY) return true;
-                    if (t <= best.t) {
-                        const int id = (int)__ldg(&k.sph_meta[i]).x;
-                        if (t < best.t || id < best.id || best.id < 0) { best.t = t; best.id = id; best.pos = (int)i; best.cls = 0; }
-                    }
-                } else {
-                    const float4 v0 = __ldg(&k.tri[3 * (size_t)i]), e1 = __ldg(&k.tri[3 * (size_t)i + 1]),
-                                 e2 = __ldg(&k.tri[3 * (size_t)i + 2]);
-                    if (!hit_triangle(v0, e1, e2, r, t_min, t_max, t)) continue;
-                    if (ANY) return true;
-                    if (t <= best.t) {
-                        const int id = __float_as_int(v0.w);
-                        if (t < best.t || id < best.id || best.id < 0) { best.t = t; best.id = id; best.pos = (int)i; best.cls = 1; }
-                    }
-                }
-            }
+            if (test_leaf<CLS, ANY>(k, cur, r, t_min, t_max, best, prims)) return true;
         }
         // pop, skipping entries that the current closest hit already rules out
         for (;;) {
-            if (sp == 0) return best.id >= 0;
+            if (sp == 0) {
+                if (STATS) cn.prims += prims;
+                return best.id >= 0;
+            }
             --sp;
-            if (ANY || tstack[sp] <= best.t) { cur = stack[sp]; break; }
+            if (ANY || tstack[sp] <= best.t_cull) { cur = stack[sp]; break; }
         }
     }
 }
 
-template <bool STATS>
+template <bool STATS, bool FMA_SLAB>
 __device__ __forceinline__ bool closest_hit(const SceneK &k, const RayT &r, float t_min, float t_max, Best &best, Counters &cn,
                                             uint32_t *error_flag)
 {
     best.t = t_max;
+    best.t_cull = t_max;
     best.id = -1;
     best.pos = 0;
     best.cls = 0;
-    traverse<0, false, STATS>(k, r, t_min, t_max, best, cn, error_flag);
-    traverse<1, false, STATS>(k, r, t_min, t_max, best, cn, error_flag);
+    traverse<0, false, STATS, FMA_SLAB>(k, r, t_min, t_max, best, cn, error_flag);
+    traverse<1, false, STATS, FMA_SLAB>(k, r, t_min, t_max, best, cn, error_flag);
     return best.id >= 0;
 }
 
@@ -337,7 +379,7 @@ struct WaveArgs {
 };
 
 template <bool DEPTH0, bool STATS>
-__global__ void __launch_bounds__(256) bounce_kernel(const SceneK k, const WaveArgs w)
+__global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(const SceneK k, const WaveArgs w)
 {
     const unsigned lane = threadIdx.x & 31u;
     const uint32_t n_in = DEPTH0 ? w.n0 : *w.n_in;
@@ -371,8 +413,10 @@ __global__ void __launch_bounds__(256) bounce_kernel(const SceneK k, const WaveA
                 normalize3f(dx, dy, dz);
                 ox = k.cam_o[0]; oy = k.cam_o[1]; oz = k.cam_o[2];       // Test.hlsl:8
             } else {
-                const float4 s0 = w.in.s0[i], s1 = w.in.s1[i];
-                const float2 s2 = w.in.s2[i];
+                // streaming (evict-first) access: the path state is touched once per bounce and must not
+                // push the hierarchy out of L2
+                const float4 s0 = __ldcs(&w.in.s0[i]), s1 = __ldcs(&w.in.s1[i]);
+                const float2 s2 = __ldcs(&w.in.s2[i]);
                 ox = s0.x; oy = s0.y; oz = s0.z; pix = __float_as_uint(s0.w);
                 dx = s1.x; dy = s1.y; dz = s1.z; tr = s1.w; tg = s2.x; tb = s2.y;
             }
@@ -383,7 +427,7 @@ __global__ void __launch_bounds__(256) bounce_kernel(const SceneK k, const WaveA
             RayT r;
             make_ray(r, ox, oy, oz, dx, dy, dz);
             Best best;
-            const bool hit = closest_hit<STATS>(k, r, k.t_min, __int_as_float(0x7F800000) /* +inf */, best, cn, w.error_flag);
+            const bool hit = closest_hit<STATS, true>(k, r, k.t_min, __int_as_float(0x7F800000) /* +inf */, best, cn, w.error_flag);
             if (STATS) ++n_rays;
             if (DEPTH0 && w.hit_ids) w.hit_ids[pix] = hit ? best.id : -1;
             float Px = 0, Py = 0, Pz = 0, nx = 0, ny = 0, nz = 0;
@@ -435,9 +479,9 @@ __global__ void __launch_bounds__(256) bounce_kernel(const SceneK k, const WaveA
             obase = __shfl_sync(FULL, obase, 0);
             if (alive) {
                 const uint32_t o = obase + (uint32_t)__popc(live & ((1u << lane) - 1u));
-                w.out.s0[o] = make_float4(ox, oy, oz, __uint_as_float(pix));
-                w.out.s1[o] = make_float4(dx, dy, dz, tr);
-                w.out.s2[o] = make_float2(tg, tb);
+                __stcs(&w.out.s0[o], make_float4(ox, oy, oz, __uint_as_float(pix)));
+                __stcs(&w.out.s1[o], make_float4(dx, dy, dz, tr));
+                __stcs(&w.out.s2[o], make_float2(tg, tb));
             }
         }
     }
@@ -526,13 +570,13 @@ __global__ void __launch_bounds__(256) trace_rays_kernel(const SceneK k, uint64_
     Counters cn;
     Best best;
     if (mode == 0) {
-        const bool hit = closest_hit<STATS>(k, r, t_min, t_max, best, cn, error_flag);
+        const bool hit = closest_hit<STATS, false>(k, r, t_min, t_max, best, cn, error_flag);
         out_prim[i] = hit ? best.id : -1;
         if (out_t) out_t[i] = hit ? best.t : 0.0f;
     } else {
-        best.t = t_max; best.id = -1; best.pos = 0; best.cls = 0;
-        bool hit = traverse<0, true, STATS>(k, r, t_min, t_max, best, cn, error_flag);
-        if (!hit) hit = traverse<1, true, STATS>(k, r, t_min, t_max, best, cn, error_flag);
+        best.t = t_max; best.t_cull = t_max; best.id = -1; best.pos = 0; best.cls = 0;
+        bool hit = traverse<0, true, STATS, false>(k, r, t_min, t_max, best, cn, error_flag);
+        if (!hit) hit = traverse<1, true, STATS, false>(k, r, t_min, t_max, best, cn, error_flag);
         out_prim[i] = hit ? 1 : 0;
     }
 }
