@@ -45,6 +45,41 @@ public sealed unsafe class NativeTracer : IDisposable
     [DllImport(Lib)] private static extern int ptb_present(IntPtr ctx, uint dstW, uint dstH, uint flags);
     [DllImport(Lib)] private static extern int ptb_read_present(IntPtr ctx, void* hostDst, nuint pitchBytes);
 
+    // ---- scene path (no reference counterpart: the reference's scene is the literals of Test.hlsl:8,12-13)
+    [StructLayout(LayoutKind.Sequential)]
+    public struct Material                      // 32 bytes == ptb_material
+    {
+        public uint Type;                       // 0 Lambert, 1 metal, 2 dielectric
+        public fixed float Albedo[3];
+        public float Fuzz, Ior;
+        public fixed float Pad[2];
+    }
+
+    [StructLayout(LayoutKind.Sequential)]
+    public struct SceneDesc                     // == ptb_scene_desc
+    {
+        public uint StructSize, NSpheres;
+        public float* Spheres;                  // n x (cx,cy,cz,r)
+        public uint* SphereMaterial;
+        public uint NTriangles, NMaterials;
+        public float* TriVertices;              // n x 9
+        public uint* TriMaterial;
+        public Material* Materials;
+        public fixed float CamOrigin[3];        // Test.hlsl:8
+        public fixed float CamU[3];             // Test.hlsl:10 generalised: ray = normalize(uv.x*U + uv.y*V + W)
+        public fixed float CamV[3];
+        public fixed float CamW[3];
+        public fixed float SkyHorizon[3];
+        public fixed float SkyZenith[3];
+        public float TMin;
+        public uint ShadeMode, MaxLeaf, Flags;
+    }
+
+    [DllImport(Lib)] private static extern int ptb_upload_scene(IntPtr ctx, SceneDesc* desc);
+    [DllImport(Lib)] private static extern int ptb_clear_scene(IntPtr ctx);
+    [DllImport(Lib)] private static extern int ptb_trace_rays(IntPtr ctx, ulong nRays, float* origins, float* dirs, float tMin,
+                                                              float tMax, int mode, int* outPrim, float* outT);
+
     public const uint ResolveSrgb = 1, ResolveBgra = 2;
 
     private IntPtr _ctx;
@@ -90,6 +125,23 @@ public sealed unsafe class NativeTracer : IDisposable
     {
         Check(_ctx, ptb_present(_ctx, dstW, dstH, srgb ? ResolveSrgb : 0));
         fixed (byte* p = bgra8) Check(_ctx, ptb_read_present(_ctx, p, 0));
+    }
+
+    // Scene upload + GPU BVH build; afterwards ComputeFrame / RenderSamples trace the uploaded scene.
+    public void UploadScene(ref SceneDesc desc)
+    {
+        desc.StructSize = (uint)sizeof(SceneDesc);
+        fixed (SceneDesc* p = &desc) Check(_ctx, ptb_upload_scene(_ctx, p));
+    }
+
+    public void ClearScene() => Check(_ctx, ptb_clear_scene(_ctx));
+
+    public void TraceRays(ReadOnlySpan<float> origins, ReadOnlySpan<float> dirs, float tMin, float tMax, bool anyHit,
+                          Span<int> prim, Span<float> t)
+    {
+        fixed (float* o = origins, d = dirs, tt = t)
+        fixed (int* pp = prim)
+            Check(_ctx, ptb_trace_rays(_ctx, (ulong)prim.Length, o, d, tMin, tMax, anyHit ? 1 : 0, pp, anyHit ? null : tt));
     }
 
     public void Dispose()
