@@ -53,6 +53,28 @@ class OracleEngine:
         return self.img
 
 
+class OracleSceneEngine(OracleEngine):
+    """The same contract over the scene oracle (multi-bounce paths through a small mixed scene)."""
+
+    def __init__(self, width, height, seed):
+        super().__init__(width, height, seed)
+        from oracle import pt_scene_oracle as S
+        from pathtracing_b200 import scenes
+        self.so = S.SceneOracle(scenes.mixed_small(width=width, height=height), width, height, max_depth=5)
+
+        self.full = np.zeros((height, width, 4), np.float32)
+
+    def accum_reset(self):
+        super().accum_reset()
+        self.full[:] = 0
+
+    def render_samples(self, first, n):
+        # the scene path adds every sample straight into the accumulator (no per-launch partial sum)
+        self.so.accumulate(first, n, seed=self.seed, jitter=True, accum=self.full)
+        off, stride = self.rows
+        self.acc[off::stride] = torch.from_numpy(self.full)[off::stride]
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
@@ -61,12 +83,12 @@ def _free_port():
     return port
 
 
-def _worker(rank, world, port, mode, q):
+def _worker(rank, world, port, mode, q, kind="csmain"):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
-        eng = OracleEngine(W, H, SEED)
+        eng = OracleSceneEngine(W, H, SEED) if kind == "scene" else OracleEngine(W, H, SEED)
         r = ShardedRenderer(eng, mode=mode)
         r.render(0, 6)
         r.render(6, 5)                      # progressive: a second batch, odd size
@@ -80,11 +102,11 @@ def _worker(rank, world, port, mode, q):
         dist.destroy_process_group()
 
 
-def _run(world, mode):
+def _run(world, mode, kind="csmain"):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, mode, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, mode, q, kind)) for r in range(world)]
     for p in procs:
         p.start()
     out = [q.get(timeout=120) for _ in range(world)]
@@ -140,6 +162,39 @@ def test_sample_sharding_two_ranks(oracle):
     # and against one big sequential accumulation: float-sum reorder tolerance, <= 1 code in RGBA8
     acc1, img1 = _single(oracle)
     np.testing.assert_allclose(acc, acc1, rtol=2e-6, atol=1e-5)
+    assert np.abs(img.view(np.uint8).reshape(H, W, 4).astype(int) - img1.astype(int)).max() <= 1
+
+
+def _single_scene():
+    from oracle import pt_oracle as O
+    from oracle import pt_scene_oracle as S
+    from pathtracing_b200 import scenes
+    so = S.SceneOracle(scenes.mixed_small(width=W, height=H), W, H, max_depth=5)
+    acc = so.accumulate(0, 11, seed=SEED)
+    return so, acc, O.resolve(acc, 11)
+
+
+def test_scene_tile_sharding_two_ranks_is_bit_identical():
+    """n8 partitioning A on the scene path (BASELINE configs[3] shards image tiles across GPUs)."""
+    _, img, _acc = _run(2, "tiles", "scene")
+    _, _, img1 = _single_scene()
+    assert np.array_equal(img.view(np.uint8).reshape(H, W, 4), img1)
+
+
+def test_scene_sample_sharding_two_ranks():
+    _, img, acc = _run(2, "samples", "scene")
+    so, acc1, img1 = _single_scene()
+    parts = []
+    for rank in range(2):
+        a = np.zeros((H, W, 4), np.float32)
+        for first, count in ((0, 6), (6, 5)):
+            st, n = sample_range(first, count, rank, 2)
+            so.accumulate(st, n, seed=SEED, accum=a)
+        parts.append(a)
+    ref = parts[0] + parts[1]
+    assert np.array_equal(acc.view(np.uint32), ref.view(np.uint32))
+    assert np.all(acc[..., 3] == 11.0)
+    np.testing.assert_allclose(acc, acc1, rtol=3e-6, atol=1e-5)
     assert np.abs(img.view(np.uint8).reshape(H, W, 4).astype(int) - img1.astype(int)).max() <= 1
 
 
