@@ -10,6 +10,7 @@ def run(name, sc, w, h, spp, depth, max_leaf=4):
         info = t.scene_info()
         t.render_samples(0, 2); t.wait()
         t.timer_begin(); t.render_samples(2, spp); ms = t.timer_end()
+        print("   queue sizes", t.scene_queue_sizes(), flush=True)
         print(f"{name}: {w}x{h} {spp}spp depth{depth} leaf{max_leaf}: {ms:.2f} ms -> {w*h*spp/ms/1e3:.1f} Msamples/s; upload {up*1e3:.0f} ms build {info['build_ms']:.2f} ms nodes s{info['sphere_nodes']} t{info['triangle_nodes']} leaves t{info['triangle_leaves']}", flush=True)
     with NativeTracer(w, h, max_depth=depth) as t:
         t.upload_scene(sc, max_leaf=max_leaf, count_stats=True)

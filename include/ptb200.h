@@ -216,6 +216,9 @@ int ptb_clear_scene(ptb_context *ctx);
 int ptb_scene_info_get(ptb_context *ctx, ptb_scene_info *out);
 int ptb_scene_stats_get(ptb_context *ctx, ptb_scene_stats *out);
 int ptb_scene_stats_reset(ptb_context *ctx);
+/* Live paths entering each bounce of the LAST wave rendered (out[0] = camera rays, out[d] = paths that survived d
+ * scatters); writes min(cap, max_depth + 1) entries and their number to *n.  Synchronises. */
+int ptb_scene_queue_sizes(ptb_context *ctx, uint32_t *out, uint32_t cap, uint32_t *n);
 /* Download one flattened hierarchy for inspection: which = 0 spheres, 1 triangles.
  * nodes_out: cap_nodes x 16 floats (64 B nodes, layout in csrc/scene.cuh), order_out: cap_prims
  * primitive ids in leaf order.  Either may be NULL; counts are always written. */

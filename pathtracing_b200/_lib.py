@@ -153,6 +153,7 @@ SIGNATURES = {
     "ptb_scene_info_get": (C.c_int, [_CTX, _P(SceneInfo)]),
     "ptb_scene_stats_get": (C.c_int, [_CTX, _P(SceneStats)]),
     "ptb_scene_stats_reset": (C.c_int, [_CTX]),
+    "ptb_scene_queue_sizes": (C.c_int, [_CTX, _P(C.c_uint32), C.c_uint32, _P(C.c_uint32)]),
     "ptb_scene_read_bvh": (C.c_int, [_CTX, C.c_int, C.c_void_p, C.c_uint32, _P(C.c_uint32), C.c_void_p, C.c_uint32,
                                      _P(C.c_uint32)]),
     "ptb_trace_rays": (C.c_int, [_CTX, C.c_uint64, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_int, C.c_void_p,

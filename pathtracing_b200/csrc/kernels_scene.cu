@@ -178,24 +178,42 @@ __device__ __forceinline__ bool test_leaf(const SceneK &k, int leaf, const RayT 
     return false;
 }
 
-// Stack-based traversal of one hierarchy: one loop, the current reference is either a node (test both
-// child boxes, descend into the nearer, push the farther with its entry distance) or a leaf (test its
-// primitives).  A "while-while" variant with a parked leaf was measured and was slower here (more
-// registers, later shrinking of the closest distance): profiles/r01_notes.md.
+// Stack-based traversal of one hierarchy, warp-synchronous "while-while".  MUST be called by all 32
+// lanes of a warp (lanes without a ray pass active = false): the inner loop descends through nodes
+// (test both child boxes, go to the nearer, push the farther with its entry distance) until the lane
+// holds a leaf or has finished; __syncwarp() behind the inner loop makes the primitive tests — the
+// expensive, exactly rounded part — run with every lane that holds a leaf, and nobody leaves the outer
+// loop before the whole warp is done, so the caller continues converged.  Without the explicit
+// reconvergence, independent thread scheduling let every lane run its leaf tests AND the shading that
+// follows on its own: 2.6-3.0 active threads per instruction there (profiles/r01_notes.md).
 // CLS 0 = spheres, 1 = triangles.  ANY: stop at the first hit.
 template <int CLS, bool ANY, bool STATS, bool FMA_SLAB>
-__device__ __forceinline__ bool traverse(const SceneK &k, const RayT &r, float t_min, float t_max, Best &best, Counters &cn,
-                                         uint32_t *error_flag)
+__device__ __forceinline__ bool traverse(const SceneK &k, const RayT &r, float t_min, float t_max, bool active, Best &best,
+                                         Counters &cn, uint32_t *error_flag)
 {
     const BvhNode *__restrict__ nodes = CLS == 0 ? k.sph_nodes : k.tri_nodes;
-    int cur = CLS == 0 ? k.sph_root : k.tri_root;
-    if (cur == EMPTY_REF) return false;
+    const int root = CLS == 0 ? k.sph_root : k.tri_root;
+    if (root == EMPTY_REF) return false;               // launch-uniform
+    const bool lockstep = (CLS == 0 ? k.sph_lockstep : k.tri_lockstep) != 0;
+    int cur = active ? root : EMPTY_REF;               // node (>= 0), leaf (< 0) or EMPTY_REF = finished
     int stack[STACK_N];
     float tstack[STACK_N];
     int sp = 0;
     uint32_t prims = 0;
+    bool found = false;
+
+    // next entry of the stack that the current closest hit does not rule out, else EMPTY_REF
+#define PTB_POP()                                                                \
+    do {                                                                         \
+        cur = EMPTY_REF;                                                         \
+        while (sp > 0) {                                                         \
+            --sp;                                                                \
+            if (ANY || tstack[sp] <= best.t_cull) { cur = stack[sp]; break; }    \
+        }                                                                        \
+    } while (0)
+
     for (;;) {
-        if (cur >= 0) {
+        while (cur >= 0) {
             const float4 na = __ldg(&nodes[cur].a), nb = __ldg(&nodes[cur].b), nc = __ldg(&nodes[cur].c);
             const int4 nd = __ldg(&nodes[cur].d);
             if (STATS) ++cn.nodes;
@@ -214,36 +232,47 @@ __device__ __forceinline__ bool traverse(const SceneK &k, const RayT &r, float t
                 } else {
                     atomicOr(error_flag, 1u);
                 }
-                continue;
+            } else if (h0) {
+                cur = nd.x;
+            } else if (h1) {
+                cur = nd.y;
+            } else {
+                PTB_POP();
             }
-            if (h0) { cur = nd.x; continue; }
-            if (h1) { cur = nd.y; continue; }
-        } else {
-            if (test_leaf<CLS, ANY>(k, cur, r, t_min, t_max, best, prims)) return true;
         }
-        // pop, skipping entries that the current closest hit already rules out
-        for (;;) {
-            if (sp == 0) {
-                if (STATS) cn.prims += prims;
-                return best.id >= 0;
+        if (lockstep) {                                 // launch-uniform
+            __syncwarp();
+            if (!__any_sync(FULL, cur != EMPTY_REF)) break;
+        } else if (cur == EMPTY_REF) {
+            break;
+        }
+        if (cur != EMPTY_REF) {
+            if (test_leaf<CLS, ANY>(k, cur, r, t_min, t_max, best, prims)) {
+                found = true;
+                cur = EMPTY_REF;
+            } else {
+                PTB_POP();
             }
-            --sp;
-            if (ANY || tstack[sp] <= best.t_cull) { cur = stack[sp]; break; }
         }
+        if (lockstep) __syncwarp();
     }
+#undef PTB_POP
+    if (STATS) cn.prims += prims;
+    return ANY ? found : best.id >= 0;
 }
 
+// all 32 lanes of the warp must call this (active = false for lanes without a ray)
 template <bool STATS, bool FMA_SLAB>
-__device__ __forceinline__ bool closest_hit(const SceneK &k, const RayT &r, float t_min, float t_max, Best &best, Counters &cn,
-                                            uint32_t *error_flag)
+__device__ __forceinline__ bool closest_hit(const SceneK &k, const RayT &r, float t_min, float t_max, bool active, Best &best,
+                                            Counters &cn, uint32_t *error_flag)
 {
     best.t = t_max;
     best.t_cull = t_max;
     best.id = -1;
     best.pos = 0;
     best.cls = 0;
-    traverse<0, false, STATS, FMA_SLAB>(k, r, t_min, t_max, best, cn, error_flag);
-    traverse<1, false, STATS, FMA_SLAB>(k, r, t_min, t_max, best, cn, error_flag);
+    traverse<0, false, STATS, FMA_SLAB>(k, r, t_min, t_max, active, best, cn, error_flag);
+    traverse<1, false, STATS, FMA_SLAB>(k, r, t_min, t_max, active, best, cn, error_flag);
     return best.id >= 0;
 }
 
@@ -423,11 +452,13 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
         }
         float cr = 0.0f, cg = 0.0f, cb = 0.0f;     // radiance this path adds now
         bool add = false;
+        // closest hit: warp-synchronous, every lane takes part (lanes past the end of the queue idle)
+        RayT r;
+        make_ray(r, ox, oy, oz, dx, dy, dz);
+        Best best;
+        const bool hit = closest_hit<STATS, true>(k, r, k.t_min, __int_as_float(0x7F800000) /* +inf */, alive, best, cn, w.error_flag);
+        __syncwarp();
         if (alive) {
-            RayT r;
-            make_ray(r, ox, oy, oz, dx, dy, dz);
-            Best best;
-            const bool hit = closest_hit<STATS, true>(k, r, k.t_min, __int_as_float(0x7F800000) /* +inf */, best, cn, w.error_flag);
             if (STATS) ++n_rays;
             if (DEPTH0 && w.hit_ids) w.hit_ids[pix] = hit ? best.id : -1;
             float Px = 0, Py = 0, Pz = 0, nx = 0, ny = 0, nz = 0;
@@ -564,20 +595,23 @@ __global__ void __launch_bounds__(256) trace_rays_kernel(const SceneK k, uint64_
                                                          int32_t *out_prim, float *out_t, uint32_t *error_flag)
 {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    const bool active = i < n;                          // no early return: the traversal is warp-synchronous
+    const uint64_t j = active ? i : 0;
     RayT r;
-    make_ray(r, o[3 * i], o[3 * i + 1], o[3 * i + 2], d[3 * i], d[3 * i + 1], d[3 * i + 2]);
+    make_ray(r, o[3 * j], o[3 * j + 1], o[3 * j + 2], d[3 * j], d[3 * j + 1], d[3 * j + 2]);
     Counters cn;
     Best best;
-    if (mode == 0) {
-        const bool hit = closest_hit<STATS, false>(k, r, t_min, t_max, best, cn, error_flag);
-        out_prim[i] = hit ? best.id : -1;
-        if (out_t) out_t[i] = hit ? best.t : 0.0f;
+    if (mode == 0) {                                    // launch-uniform
+        const bool hit = closest_hit<STATS, false>(k, r, t_min, t_max, active, best, cn, error_flag);
+        if (active) {
+            out_prim[i] = hit ? best.id : -1;
+            if (out_t) out_t[i] = hit ? best.t : 0.0f;
+        }
     } else {
         best.t = t_max; best.t_cull = t_max; best.id = -1; best.pos = 0; best.cls = 0;
-        bool hit = traverse<0, true, STATS, false>(k, r, t_min, t_max, best, cn, error_flag);
-        if (!hit) hit = traverse<1, true, STATS, false>(k, r, t_min, t_max, best, cn, error_flag);
-        out_prim[i] = hit ? 1 : 0;
+        bool hit = traverse<0, true, STATS, false>(k, r, t_min, t_max, active, best, cn, error_flag);
+        hit = traverse<1, true, STATS, false>(k, r, t_min, t_max, active && !hit, best, cn, error_flag) || hit;
+        if (active) out_prim[i] = hit ? 1 : 0;
     }
 }
 

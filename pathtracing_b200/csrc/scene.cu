@@ -6,6 +6,7 @@
 // scene_build.cu (GPU LBVH) and kernels_scene.cu (wavefront path tracer).
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -50,6 +51,15 @@ void free_state(SceneState *st)
     delete st;
 }
 
+// Lockstep primitive tests when the hierarchy fits the SM's L1 (measured: profiles/r01_notes.md).
+// PTB200_LOCKSTEP=0/1 forces the choice (A/B experiments).
+uint32_t lockstep_for(uint32_t n_nodes)
+{
+    static const char *env = std::getenv("PTB200_LOCKSTEP");
+    if (env && (env[0] == '0' || env[0] == '1')) return env[0] == '1';
+    return (uint64_t)n_nodes * 64u <= 128u * 1024u ? 1u : 0u;
+}
+
 ptb::SceneK make_k(const ptb_context *ctx, const SceneState *st)
 {
     ptb::SceneK k{};
@@ -82,7 +92,15 @@ ptb::SceneK make_k(const ptb_context *ctx, const SceneState *st)
     k.tri_nodes = st->tri_bvh.nodes;
     k.tri_root = st->tri_bvh.root_ref;
     k.materials = st->materials;
+    k.sph_lockstep = lockstep_for(st->sph_bvh.n_nodes);
+    k.tri_lockstep = lockstep_for(st->tri_bvh.n_nodes);
     return k;
+}
+
+uint32_t wave_paths(const ptb_context *ctx)
+{
+    const uint32_t h = ctx->cfg.height, off = ctx->k.row_offset, stride = ctx->k.row_stride;
+    return off < h ? ((h - off + stride - 1u) / stride) * ctx->cfg.width : 0u;
 }
 
 int check_error_flag(ptb_context *ctx, SceneState *st)
@@ -115,6 +133,7 @@ int scene_compute_frame(ptb_context *ctx)
     SC_CUDA(ctx, cudaMemsetAsync(st->frame_accum, 0, n * sizeof(float4), ctx->stream));
     if (ctx->buf.hit) SC_CUDA(ctx, cudaMemsetAsync(ctx->buf.hit, 0xFF, n * sizeof(int32_t), ctx->stream));
     const SceneK k = make_k(ctx, st);
+    st->last_n0 = wave_paths(ctx);
     SC_CUDA(ctx, launch_scene_wave(k, st, st->frame_accum, ctx->buf.hit, 0u, false, ctx->stream, &ctx->launches));
     SC_CUDA(ctx, launch_frame_finish(st->frame_accum, ctx->buf.f32, ctx->buf.rgba8, (uint32_t)n, ctx->stream));
     ctx->launches += 1;
@@ -125,6 +144,7 @@ int scene_render_samples(ptb_context *ctx, uint32_t first_sample, uint32_t n_sam
 {
     SceneState *st = state(ctx);
     const SceneK k = make_k(ctx, st);
+    st->last_n0 = wave_paths(ctx);
     for (uint32_t s = 0; s < n_samples; ++s)
         SC_CUDA(ctx, launch_scene_wave(k, st, ctx->buf.accum, nullptr, first_sample + s, jitter != 0, ctx->stream, &ctx->launches));
     return PTB_OK;
@@ -315,6 +335,22 @@ int ptb_scene_stats_reset(ptb_context *ctx)
     if (!ctx->scene) return ptb::fail_msg(ctx, PTB_ERR_STATE, "ptb_scene_stats_reset: no scene resident");
     SC_CUDA(ctx, cudaSetDevice(ctx->cfg.device));
     SC_CUDA(ctx, cudaMemsetAsync(state(ctx)->stats, 0, sizeof(ptb::SceneStatsDev), ctx->stream));
+    return PTB_OK;
+}
+
+int ptb_scene_queue_sizes(ptb_context *ctx, uint32_t *out, uint32_t cap, uint32_t *n)
+{
+    if (!ctx) return ptb::fail_msg(nullptr, PTB_ERR_INVALID, "ptb_scene_queue_sizes: ctx is NULL");
+    if (!out || !n) return ptb::fail_msg(ctx, PTB_ERR_INVALID, "ptb_scene_queue_sizes: NULL argument");
+    if (!ctx->scene) return ptb::fail_msg(ctx, PTB_ERR_STATE, "ptb_scene_queue_sizes: no scene resident");
+    SC_CUDA(ctx, cudaSetDevice(ctx->cfg.device));
+    SceneState *st = state(ctx);
+    uint32_t cnt = ctx->cfg.max_depth + 1u;
+    if (cnt > cap) cnt = cap;
+    if (cnt) SC_CUDA(ctx, cudaMemcpyAsync(out, st->counts, sizeof(uint32_t) * cnt, cudaMemcpyDeviceToHost, ctx->stream));
+    SC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (cnt) out[0] = st->last_n0;
+    *n = cnt;
     return PTB_OK;
 }
 

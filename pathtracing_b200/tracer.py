@@ -182,6 +182,13 @@ class NativeTracer:
     def scene_stats_reset(self) -> None:
         self._ck(self._lib.ptb_scene_stats_reset(self._ctx))
 
+    def scene_queue_sizes(self):
+        """Live paths entering each bounce of the last wave: [camera rays, after 1 scatter, ...]."""
+        out = (C.c_uint32 * 256)()
+        n = C.c_uint32()
+        self._ck(self._lib.ptb_scene_queue_sizes(self._ctx, out, 256, C.byref(n)))
+        return [int(v) for v in out[:n.value]]
+
     def read_bvh(self, which: int):
         """-> (nodes (n,16) float32 view of the 64 B nodes, order (n_prims,) uint32)."""
         nn, npr = C.c_uint32(), C.c_uint32()
