@@ -248,7 +248,9 @@ uint64_t ptb_launch_count(const ptb_context *ctx);
 int ptb_kernel_mode(const ptb_context *ctx);
 /* Proof by exhaustion, on the device, that a shortened sequence equals the IEEE intrinsic on its
  * whole domain: which = 0 sqrt over [2^-20,2^24), 1 reciprocal over [2^-12,2^12), 2 division of
- * every float in [2^-24,2^17) by `divisor`.  Writes the number of disagreeing inputs (must be 0
+ * every float in [2^-24,2^17) by `divisor`, 3 = the per-pixel "every sample of this pixel misses" classification of THIS
+ * context's parameters against the exact discriminant at an 8x8 grid of jitter positions (both extremes included) of
+ * every pixel so classified.  Writes the number of disagreeing inputs (must be 0
  * for the fast kernels to be selected) and the number of inputs tested. */
 int ptb_selftest_exact_math(ptb_context *ctx, int which, float divisor, uint64_t *mismatches, uint64_t *tested);
 

@@ -4,6 +4,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -78,6 +79,8 @@ void derive_fast_flags(ptb_context *c)
     ptb::FrameK &k = c->k;
     k.fast = 0;
     k.on_axis = 0;
+    k.cm_on = 0;
+    k.cm_sx = k.cm_sy = k.cm_K = 0.0f;
     if (c->cfg.flags & PTB_CFG_FORCE_IEEE) return;
     const float vals[] = {k.cam[0], k.cam[1], k.cam[2], k.centre[0], k.centre[1], k.centre[2], k.radius,
                           k.oc[0], k.oc[1], k.oc[2], k.c, k.c4, k.inv_div_x, k.inv_div_y};
@@ -90,6 +93,11 @@ void derive_fast_flags(ptb_context *c)
     if (!ptb::uniform_divisor_verified(k.div_x, c->stream)) return;
     if (!ptb::uniform_divisor_verified(k.div_y, c->stream)) return;
     k.fast = 1;
+    // per-pixel certain-miss classification: only bounds are needed, so plain host arithmetic is fine
+    k.cm_sx = 2.0f / k.div_x;
+    k.cm_sy = 2.0f / k.div_y;
+    k.cm_K = std::fabs(k.c) + (k.oc[0] * k.oc[0] + k.oc[1] * k.oc[1] + k.oc[2] * k.oc[2]);
+    k.cm_on = (std::isfinite(k.cm_K) && k.cm_K > 0.0f && k.cm_K < 1e30f && !std::getenv("PTB200_NO_CERTAIN_MISS")) ? 1u : 0u;
     const float az = std::fabs(k.oc[2]);
     k.on_axis = (k.oc[0] == 0.0f && k.oc[1] == 0.0f && az >= 8.67e-19f /*~2^-60*/ && az <= 1.15e18f /*~2^60*/) ? 1u : 0u;
 }
@@ -466,8 +474,16 @@ int ptb_kernel_mode(const ptb_context *ctx)
 int ptb_selftest_exact_math(ptb_context *ctx, int which, float divisor, uint64_t *mismatches, uint64_t *tested)
 {
     PTB_ENTER(ctx);
-    if (which < 0 || which > 2 || !mismatches || !tested)
+    if (which < 0 || which > 3 || !mismatches || !tested)
         return fail(ctx, PTB_ERR_INVALID, "ptb_selftest_exact_math: bad argument");
+    if (which == 3) {
+        unsigned long long bad3 = 0, n3 = 0;
+        PTB_CUDA(ctx, ptb::selftest_certain_miss(ctx->k, &bad3, &n3, ctx->stream));
+        ctx->launches += 1;
+        *mismatches = bad3;
+        *tested = n3;
+        return PTB_OK;
+    }
     if (which == 2 && !(std::fabs(divisor) > 0.0f && std::isfinite(divisor)))
         return fail(ctx, PTB_ERR_INVALID, "ptb_selftest_exact_math: divisor must be finite and non-zero");
     unsigned long long bad = 0, n = 0;

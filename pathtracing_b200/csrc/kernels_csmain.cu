@@ -111,6 +111,30 @@ __device__ __forceinline__ bool csmain_shade(const FrameK &k, float uvx, float u
     return false;
 }
 
+// Conservative classification of a whole pixel: true only if EVERY sample position in [x,x+1] x [y,y+1] certainly
+// evaluates to disc <= 0 (a miss) in the exactly-rounded csmain_shade.  With exact arithmetic
+//   disc = -(4/|raw|^2) * G(u,v),   G = c*(u^2+v^2+1) - (oc.x*u + oc.y*v - oc.z)^2,   raw = (u, v, -1);
+// the rounded evaluation differs from it by at most ~5e-6*K (K = |c| + |oc|^2: d, a, b each carry a few ulp), i.e. the
+// computed disc is certainly <= 0 wherever G >= 1.3e-6*K*|raw|^2.  G over the pixel is bounded from its value and
+// gradient at the pixel centre plus the second-order term (|Hessian| <= 2K): the test below asks for 1e-4*K*|raw|max^2,
+// ~80x the requirement, which also swallows the rounding of this (ordinary float) evaluation and of the per-sample
+// uv.  Such pixels (85 % of a 16:9 frame of the default scene) skip normalisation, discriminant and hit branch for all
+// of their samples: their colour is (uv.x, uv.y, 0) (Test.hlsl:36).  NaN anywhere -> false -> the full path.
+// Checked by exhaustion per context (ptb_selftest_exact_math which = 3) in the GPU tests.
+__device__ __forceinline__ bool certain_miss(const FrameK &k, float fx, float fy)
+{
+    if (!k.cm_on) return false;
+    const float u = (fx + 0.5f) * k.cm_sx - 1.0f, v = (fy + 0.5f) * k.cm_sy - 1.0f;   // pixel centre in uv
+    const float hx = fabsf(k.cm_sx) * 0.5005f, hy = fabsf(k.cm_sy) * 0.5005f;          // half extents (inflated)
+    const float s = k.oc[0] * u + k.oc[1] * v - k.oc[2];
+    const float G = k.c * (u * u + v * v + 1.0f) - s * s;
+    const float gu = fabsf(2.0f * (k.c * u - s * k.oc[0])), gv = fabsf(2.0f * (k.c * v - s * k.oc[1]));
+    const float au = fabsf(u) + hx, av = fabsf(v) + hy;
+    const float r2max = au * au + av * av + 1.0f;
+    const float lower = G - gu * hx - gv * hy - k.cm_K * (hx * hx + hy * hy);
+    return lower >= 1e-4f * k.cm_K * r2max;
+}
+
 // Two samples per instruction (FFMA2/FMUL2/FADD2), fast modes only.  Lane i of every F2 is exactly
 // the scalar csmain_shade<MODE> evaluation of sample i: same ops, same order, one rounding each.
 // Negated lengths are carried (xn, lenN, denN) so the Markstein residuals fma(q, -y, v) need no
@@ -296,6 +320,7 @@ __global__ void __launch_bounds__(256) csmain_accumulate(const FrameK k, float4 
 
     float sr = 0.0f, sg = 0.0f, sb = 0.0f, sa = 0.0f;
     uint32_t i = 0;
+    const bool lean = MODE != MODE_GENERIC && certain_miss(k, fx, fy);   // every sample of this pixel misses
     if (MODE != MODE_GENERIC && JITTER) {
         // two samples per iteration in FP32x2 lanes; the sums stay sequential in sample order
         for (; i + 2 <= n_samples; i += 2) {
@@ -319,10 +344,15 @@ __global__ void __launch_bounds__(256) csmain_accumulate(const FrameK k, float4 
             by += bz * bx;
             const F2 px = fadd2(splat(fxm1), make_float2(bits_to_unit_plus_one(ax), bits_to_unit_plus_one(bx)));
             const F2 py = fadd2(splat(fym1), make_float2(bits_to_unit_plus_one(ay), bits_to_unit_plus_one(by)));
+            const F2 uvx2 = screen_uv2(px, k.div_x, k.inv_div_x), uvy2 = screen_uv2(py, k.div_y, k.inv_div_y);
+            if (lean) {                      // Test.hlsl:36 for both samples, nothing else to evaluate
+                sr = fadd(fadd(sr, uvx2.x), uvx2.y);
+                sg = fadd(fadd(sg, uvy2.x), uvy2.y);
+                continue;
+            }
             F2 r, g, b;
             bool h0, h1;
-            csmain_shade2<MODE>(k, screen_uv2(px, k.div_x, k.inv_div_x), screen_uv2(py, k.div_y, k.inv_div_y), r, g, b,
-                                h0, h1);
+            csmain_shade2<MODE>(k, uvx2, uvy2, r, g, b, h0, h1);
             sr = fadd(fadd(sr, r.x), r.y);
             sg = fadd(fadd(sg, g.x), g.y);
             sb = fadd(fadd(sb, b.x), b.y);   // a miss adds +0.0 to a sum that is never -0.0: identity
@@ -343,6 +373,11 @@ __global__ void __launch_bounds__(256) csmain_accumulate(const FrameK k, float4 
             uvx = screen_uv<MODE>(fadd(fxm1, bits_to_unit_plus_one(vx)), k.div_x, k.inv_div_x);
             uvy = screen_uv<MODE>(fadd(fym1, bits_to_unit_plus_one(vy)), k.div_y, k.inv_div_y);
         }
+        if (lean) {
+            sr = fadd(sr, uvx);
+            sg = fadd(sg, uvy);
+            continue;
+        }
         float r, g, b;
         const bool h = csmain_shade<MODE>(k, uvx, uvy, r, g, b);
         sr = fadd(sr, r);
@@ -362,6 +397,59 @@ __global__ void __launch_bounds__(256) csmain_accumulate(const FrameK k, float4 
     acc.z = fadd(acc.z, sb);
     acc.w = fadd(acc.w, sa);
     accum[pix] = acc;
+}
+
+// ptb_selftest_exact_math which = 3: brute-force check of certain_miss for this context's parameters.
+template <int MODE>
+__global__ void __launch_bounds__(256) certain_miss_check_kernel(const FrameK k, unsigned long long *out)
+{
+    unsigned long long bad = 0, n = 0;
+    const uint64_t total = (uint64_t)k.width * k.height;
+    for (uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t x = (uint32_t)(p % k.width), y = (uint32_t)(p / k.width);
+        const float fx = __uint2float_rn(x), fy = __uint2float_rn(y);
+        if (!certain_miss(k, fx, fy)) continue;
+        for (int jy = 0; jy < 8; ++jy)
+            for (int jx = 0; jx < 8; ++jx) {
+                // jitter values the RNG can produce: multiples of 2^-23 in [0, 1 - 2^-23]
+                const float ox = jx == 7 ? 0.99999988079071044921875f : (float)jx * 0.140625f;
+                const float oy = jy == 7 ? 0.99999988079071044921875f : (float)jy * 0.140625f;
+                float r, g, b;
+                bad += csmain_shade<MODE>(k, screen_uv<MODE>(fadd(fx, ox), k.div_x, k.inv_div_x),
+                                          screen_uv<MODE>(fadd(fy, oy), k.div_y, k.inv_div_y), r, g, b) ? 1u : 0u;
+                ++n;
+            }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        bad += __shfl_down_sync(0xFFFFFFFFu, bad, o);
+        n += __shfl_down_sync(0xFFFFFFFFu, n, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&out[0], bad);
+        atomicAdd(&out[1], n);
+    }
+}
+
+cudaError_t selftest_certain_miss(const FrameK &k, unsigned long long *mismatches, unsigned long long *tested, cudaStream_t s)
+{
+    unsigned long long *d = nullptr, h[2] = {0, 0};
+    cudaError_t e = cudaMalloc(&d, sizeof h);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(d, 0, sizeof h, s);
+    if (e == cudaSuccess) {
+        switch (pick_mode(k)) {
+        case MODE_FAST_ON_AXIS: certain_miss_check_kernel<MODE_FAST_ON_AXIS><<<148 * 8, 256, 0, s>>>(k, d); break;
+        case MODE_FAST: certain_miss_check_kernel<MODE_FAST><<<148 * 8, 256, 0, s>>>(k, d); break;
+        default: certain_miss_check_kernel<MODE_GENERIC><<<148 * 8, 256, 0, s>>>(k, d); break;
+        }
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h, d, sizeof h, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaFree(d);
+    *mismatches = h[0];
+    *tested = h[1];
+    return e;
 }
 
 template <int MODE>

@@ -32,6 +32,10 @@ struct FrameK {
     // launch-uniform validity of the short exact sequences (api.cu: derive_fast_flags)
     uint32_t fast;                // 1: uv division / sqrt / rcp domains verified for these parameters
     uint32_t on_axis;             // 1: oc.x == oc.y == 0 and oc.z is a moderate normal number
+    // conservative per-pixel "every sample of this pixel misses" classification (kernels_csmain.cu: certain_miss)
+    uint32_t cm_on;               // 1: enabled (fast mode, finite terms)
+    float cm_sx, cm_sy;           // 2/div: uv per pixel
+    float cm_K;                   // |c| + |oc|^2: scale of the discriminant's terms
 };
 
 struct Buffers {
@@ -48,6 +52,9 @@ struct Buffers {
 // kernels_csmain.cu
 cudaError_t prepare_terms(FrameK *k_host, cudaStream_t s);   // fills the derived fields (device-evaluated)
 cudaError_t launch_csmain_frame(const FrameK &k, const Buffers &b, cudaStream_t s);
+// counts, over every pixel classified "certain miss", the jitter positions (8x8 grid incl. both extremes) whose exact
+// discriminant says HIT — must be 0; tested = positions evaluated (ptb_selftest_exact_math which = 3)
+cudaError_t selftest_certain_miss(const FrameK &k, unsigned long long *mismatches, unsigned long long *tested, cudaStream_t s);
 cudaError_t launch_csmain_accumulate(const FrameK &k, float4 *accum, uint32_t first_sample,
                                      uint32_t n_samples, uint32_t seed, bool jitter, cudaStream_t s);
 // selftest.cu — exhaustive proofs of the short exact sequences in ptb_math.cuh

@@ -333,6 +333,30 @@ def test_fast_and_ieee_kernels_agree_bitwise(oracle, kw):
         assert eq_bits(acc, ref_acc), mode
 
 
+@pytest.mark.parametrize("size,kw", [
+    ((1920, 1080), dict()), ((3840, 2160), dict()), ((320, 180), dict()), ((333, 77), dict()),
+    ((1280, 720), dict(cam=(0.25, -0.5, 2.0), centre=(-0.3, 0.2, -0.4), radius=0.9)),
+    ((1280, 720), dict(uv_div=(777.0, 1234.567))), ((1280, 720), dict(cam=(0, 0, 40.0), radius=30.0)),
+    ((1280, 720), dict(cam=(0, 0, 1.0), radius=1.0)), ((640, 360), dict(cam=(0, 0, 0.25))), ((1280, 720), dict(radius=1e-3)),
+    ((640, 360), dict(cam=(3.0, 0.1, 0.2), centre=(0.0, 0.0, -0.5), radius=0.7)), ((64, 36), dict(uv_div=(7.0, 5.0))),
+    ((1280, 720), dict(cam=(0.0, 0.0, 1000.0), radius=400.0)), ((640, 360), dict(cam=(0.0, 0.0, -2.0)))],
+    ids=["1080p", "4k", "c1", "ragged", "moved", "odd_div", "huge_sphere", "camera_on_surface", "camera_inside", "tiny",
+         "side_view", "coarse_pixels", "far_camera", "sphere_behind"])
+def test_certain_miss_classification_is_conservative(oracle, size, kw):
+    """Pixels the accumulate kernel treats as 'every sample misses' (no normalisation, no discriminant) really miss at
+    every jitter position tried (8x8 grid incl. both extremes, exact discriminant), and the accumulation stays bit-exact."""
+    w, h = size
+    with NativeTracer(w, h, seed=4, **kw) as t:
+        bad, n = t.selftest_exact_math(3)
+        assert bad == 0, f"{bad} sample positions of 'certain miss' pixels actually hit"
+        frac = n / 64 / (w * h)
+        if not kw and w * 9 == h * 16:
+            assert 0.80 < frac < 0.86          # default scene, 16:9: 85.3 % of the pixels miss; the silhouette band stays out
+        t.render_samples(5, 3)
+        ref = oracle.accumulate(oracle.frame_params(w, h, **kw), 5, 3, 4, True)
+        assert eq_bits(t.read_accum(), ref)
+
+
 def test_generic_kernel_handles_degenerate_parameters(oracle):
     """Parameters outside the proven domains run the literal kernels and still match the oracle (NaN-aware)."""
     kw = dict(uv_div=(1e-3, 36.0), cam=(0.0, 0.0, 1e20))
