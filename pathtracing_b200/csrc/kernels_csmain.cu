@@ -211,7 +211,8 @@ __global__ void __launch_bounds__(256) csmain_frame_vec4(const FrameK k, uint4 *
     const uint32_t wq = k.width >> 2;
     if (xq >= wq || y >= k.height) return;                       // the guard Test.hlsl:39 lacks
 
-    const float uvy = screen_uv<MODE>(__uint2float_rn(y), k.div_y, k.inv_div_y);
+    const float fy = __uint2float_rn(y);
+    const float uvy = screen_uv<MODE>(fy, k.div_y, k.inv_div_y);
     uint32_t px8[4];
     int32_t hid[4];
     const size_t q = (size_t)y * wq + xq;
@@ -230,8 +231,15 @@ __global__ void __launch_bounds__(256) csmain_frame_vec4(const FrameK k, uint4 *
         for (int i = 0; i < 4; i += 2) {   // two pixels per FP32x2 instruction
             const F2 px = make_float2(__uint2float_rn(xq * 4u + i), __uint2float_rn(xq * 4u + i + 1));
             F2 r, g, b;
-            bool h0, h1;
-            csmain_shade2<MODE>(k, screen_uv2(px, k.div_x, k.inv_div_x), splat(uvy), r, g, b, h0, h1);
+            bool h0 = false, h1 = false;
+            const F2 uvx2 = screen_uv2(px, k.div_x, k.inv_div_x);
+            if (certain_miss(k, px.x, fy) && certain_miss(k, px.y, fy)) {   // Test.hlsl:36 for both pixels
+                r = uvx2;
+                g = splat(uvy);
+                b = splat(0.0f);
+            } else {
+                csmain_shade2<MODE>(k, uvx2, splat(uvy), r, g, b, h0, h1);
+            }
             px8[i] = pack_rgba8(r.x, g.x, b.x, 1.0f);
             px8[i + 1] = pack_rgba8(r.y, g.y, b.y, 1.0f);
             hid[i] = h0 ? 0 : -1;
