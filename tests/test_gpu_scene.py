@@ -224,6 +224,53 @@ def test_accumulation_bit_exact_and_progressive(S, name):
         assert np.array_equal(t.read_rgba8(), pt_oracle.resolve(ref, 6, srgb=True))
 
 
+# ---- BASELINE's full-size configurations ------------------------------------------------------------
+def test_config3_full_size_500_spheres_1080p(S):
+    """BASELINE configs[2] at its real size: 501 spheres, 1920x1080, depth 8 — primary ids and 2 jittered samples of
+    EVERY pixel against the oracle (its own BVH), bit for bit."""
+    w, h = 1920, 1080
+    sc = scenes.random_spheres(500, seed=1, width=w, height=h)
+    so = S.SceneOracle(sc, w, h, max_depth=8)
+    with NativeTracer(w, h, seed=0, max_depth=8, keep_f32=True, keep_hit_ids=True) as t:
+        t.upload_scene(sc)
+        t.compute_frame()
+        t.wait()
+        ref = so.frame(seed=0)
+        assert np.array_equal(t.read_hit_ids(), ref["hit"])
+        assert_images_equal(t.read_f32(), ref["f32"], "c3 1-sample radiance")
+        t.render_samples(0, 2)
+        assert_images_equal(t.read_accum(), so.accumulate(0, 2, seed=0), "c3 2-sample accumulation")
+        q = t.scene_queue_sizes()
+        assert q[0] == w * h and all(a >= b for a, b in zip(q, q[1:]))       # paths only ever die
+
+
+def test_config4_full_size_million_triangles_4k(S):
+    """BASELINE configs[3] at its real size: 1,048,576 triangles, GPU-built BVH, 3840x2160, depth 8 — primary ids and one
+    jittered sample of EVERY pixel against the oracle (its own median-split BVH), bit for bit; plus tile sharding:
+    the union of 8 interleaved row shards (what 8 GPUs would render) equals the full frame."""
+    w, h = 3840, 2160
+    sc = scenes.triangle_terrain(512, 2, seed=2, width=w, height=h)
+    assert sc.n_triangles == 1048576
+    so = S.SceneOracle(sc, w, h, max_depth=8)
+    with NativeTracer(w, h, seed=0, max_depth=8, keep_hit_ids=True) as t:
+        t.upload_scene(sc)
+        info = t.scene_info()
+        assert info["triangle_nodes"] < sc.n_triangles and info["build_ms"] < 2000
+        t.compute_frame()
+        t.wait()
+        assert np.array_equal(t.read_hit_ids(), so.frame(seed=0)["hit"])
+        t.render_samples(0, 1)
+        full = t.read_accum()
+        assert_images_equal(full, so.accumulate(0, 1, seed=0), "c4 1-sample accumulation")
+        total = np.zeros_like(full)
+        for r in range(8):
+            t.accum_reset()
+            t.set_row_shard(r, 8)
+            t.render_samples(0, 1)
+            total += t.read_accum()
+        assert_images_equal(total, full, "c4 8-way row-sharded merge")
+
+
 def test_results_do_not_depend_on_the_hierarchy(S):
     """max_leaf changes the tree (and with it traversal order and compaction order); results may not change."""
     w, h = 160, 90
