@@ -65,6 +65,56 @@ class Scene:
     def n_triangles(self) -> int:
         return len(self.triangles)
 
+    # -- scene files (the reference has none: its scene is literals in the shader) -------------
+    _VEC_FIELDS = ("cam_origin", "cam_u", "cam_v", "cam_w", "sky_horizon", "sky_zenith")
+
+    def to_dict(self) -> dict:
+        """JSON-able description (lists of Python floats; float32 values survive the round trip exactly)."""
+        d = {"format": "ptb200-scene-1", "name": self.name, "t_min": float(self.t_min), "shade_mode": int(self.shade_mode),
+             "spheres": self.spheres.astype(np.float64).tolist(), "sphere_material": self.sphere_material.tolist(),
+             "triangles": self.triangles.astype(np.float64).tolist(), "tri_material": self.tri_material.tolist(),
+             "materials": [{"type": int(m["type"]), "albedo": [float(x) for x in m["albedo"]], "fuzz": float(m["fuzz"]),
+                            "ior": float(m["ior"])} for m in self.materials]}
+        for f in self._VEC_FIELDS:
+            d[f] = [float(x) for x in getattr(self, f)]
+        return d
+
+    @classmethod
+    def from_dict(cls, d: dict) -> "Scene":
+        if d.get("format") != "ptb200-scene-1":
+            raise ValueError(f"not a ptb200 scene description: format={d.get('format')!r}")
+        mats = materials_array((m["type"], m["albedo"], m.get("fuzz", 0.0), m.get("ior", 1.5)) for m in d["materials"])
+        kw = {f: d[f] for f in cls._VEC_FIELDS if f in d}
+        return cls(spheres=np.asarray(d.get("spheres", []), np.float32).reshape(-1, 4), sphere_material=d.get("sphere_material", []),
+                   triangles=np.asarray(d.get("triangles", []), np.float32).reshape(-1, 9), tri_material=d.get("tri_material", []),
+                   materials=mats, t_min=d.get("t_min", 1e-3), shade_mode=d.get("shade_mode", SHADE_PATH),
+                   name=d.get("name", "scene"), **kw)
+
+    def save(self, path: str) -> None:
+        """`.json` -> text description; anything else -> numpy `.npz` (binary, for million-primitive scenes)."""
+        if path.endswith(".json"):
+            import json
+            with open(path, "w") as f:
+                json.dump(self.to_dict(), f)
+            return
+        np.savez_compressed(path, format=np.array("ptb200-scene-1"), name=np.array(self.name), t_min=np.float32(self.t_min),
+                            shade_mode=np.uint32(self.shade_mode), spheres=self.spheres, sphere_material=self.sphere_material,
+                            triangles=self.triangles, tri_material=self.tri_material, materials=self.materials,
+                            **{f: getattr(self, f) for f in self._VEC_FIELDS})
+
+    @classmethod
+    def load(cls, path: str) -> "Scene":
+        if path.endswith(".json"):
+            import json
+            with open(path) as f:
+                return cls.from_dict(json.load(f))
+        with np.load(path, allow_pickle=False) as z:
+            if str(z["format"]) != "ptb200-scene-1":
+                raise ValueError("not a ptb200 scene file")
+            return cls(spheres=z["spheres"], sphere_material=z["sphere_material"], triangles=z["triangles"],
+                       tri_material=z["tri_material"], materials=z["materials"], t_min=float(z["t_min"]),
+                       shade_mode=int(z["shade_mode"]), name=str(z["name"]), **{f: z[f] for f in cls._VEC_FIELDS})
+
     def look_at(self, look_from, look_at, vup, vfov_deg: float, width: int, height: int) -> "Scene":
         """Pinhole camera in the reference's screen convention (Test.hlsl:7: uv = p/H*2-1 on BOTH axes, no
         y flip, so uv.x runs from -1 to 2W/H-1): U and V span the image plane, W is shifted so the view

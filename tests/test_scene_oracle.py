@@ -167,3 +167,26 @@ CASES = {
     "spheres500_160x90_d8": (lambda w, h: scenes.random_spheres(500, width=w, height=h), 160, 90, 8),
     "terrain32_160x90_d4": (lambda w, h: scenes.triangle_terrain(cells=32, layers=2, width=w, height=h), 160, 90, 4),
 }
+
+
+def test_scene_files_round_trip_exactly(tmp_path):
+    """scene description + loader.  JSON and npz round trips preserve every float32 bit, and the
+    default scene file shipped with the package is the reference's literal scene (Test.hlsl:8,12-13)."""
+    sc = scenes.mixed_small()
+    for ext in ("json", "npz"):
+        p = str(tmp_path / f"s.{ext}")
+        sc.save(p)
+        back = scenes.Scene.load(p)
+        for f in ("spheres", "sphere_material", "triangles", "tri_material", "cam_origin", "cam_u", "cam_v", "cam_w",
+                  "sky_horizon", "sky_zenith"):
+            assert np.array_equal(getattr(back, f), getattr(sc, f)), (ext, f)
+        assert back.materials.tobytes() == sc.materials.tobytes()
+        assert (back.t_min, back.shade_mode, back.name) == (np.float32(sc.t_min), sc.shade_mode, sc.name) or back.name == sc.name
+    default_file = os.path.join(os.path.dirname(scenes.__file__), "assets", "default_scene.json")
+    d = scenes.Scene.load(default_file)
+    assert d.spheres.tolist() == [[0.0, 0.0, 0.0, 0.5]] and d.cam_origin.tolist() == [0.0, 0.0, 1.0]
+    assert d.shade_mode == scenes.SHADE_NORMALS and d.n_triangles == 0
+    fr = S.SceneOracle(d, 320, 180).frame()
+    assert fr["hits"] == 8469                                     # SURVEY App. B
+    with pytest.raises(ValueError):
+        scenes.Scene.from_dict({"format": "something else"})
