@@ -238,7 +238,12 @@ def run_b200(args):
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        opts = None
+        try:   # NCCL kernels on a high-priority stream: the rendezvous of a pipelined merge must not queue behind render blocks
+            opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)
+        except Exception:
+            opts = None
+        dist.init_process_group("nccl", device_id=dev, pg_options=opts)
 
     wl = dict(WORKLOADS[args.workload])
     if args.spp:
@@ -258,7 +263,8 @@ def run_b200(args):
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)                   # > 126 MB L2
 
     with torch.cuda.stream(stream):
-        eng = GpuEngine(W, H, local, seed=0, stream=stream, scene=scene, max_depth=wl.get("max_depth", 0))
+        eng = GpuEngine(W, H, local, seed=0, stream=stream, scene=scene, max_depth=wl.get("max_depth", 0),
+                        peer_memory=args.shard == "p2p")
         t = eng.tracer
         sr = ShardedRenderer(eng, mode=args.shard)
         merge_every_step = strong or world == 1        # c2 at N>1: one merge for the whole progressive render
@@ -268,17 +274,27 @@ def run_b200(args):
                 dist.barrier()
             torch.cuda.synchronize()
 
+        pipelined = args.shard == "p2p" and not os.environ.get("PTB200_NO_PIPELINE")      # merge of frame k overlaps the rendering of frame k+1 (double-buffered partials)
+
+        def do_merge():
+            if pipelined:
+                sr.merge(0, pipelined=True)
+            else:
+                sr.merge(0)
+
         def step_device(step):
             if literal:
                 t.compute_frame()
                 return
             sr.render(step * spp_step, spp_step)
             if merge_every_step:
-                sr.merge(0)
+                do_merge()
 
         # ---- device-timed value ---------------------------------------------------------------------
         for s in range(Wm):
             step_device(s)
+        if pipelined:
+            sr.finish()
         barrier()
         clocks = ClockSampler(local)
         if rank == 0:
@@ -297,11 +313,13 @@ def run_b200(args):
                 sr.render((Wm + s) * spp_step, spp_step)
             kern_ev[s][1].record(stream)
             if not literal and merge_every_step:
-                sr.merge(0)
+                do_merge()
             ev[s][1].record(stream)
         ev[K][0].record(stream)
         if not literal and not merge_every_step:
             sr.merge(0)                                # timed: NCCL reduce over NVLink + resolve on rank 0
+        if pipelined:
+            sr.finish()                                # timed: drain the merges still in flight
         ev[K][1].record(stream)
         barrier()
         launches = t.launch_count - launches0
@@ -309,6 +327,10 @@ def run_b200(args):
         merge_ms = ev[K][0].elapsed_time(ev[K][1])
         kern_ms = [a.elapsed_time(b) for a, b in kern_ev]
         total_ms = sum(step_ms) + merge_ms
+        if pipelined:
+            # merges overlap the following step (and the L2 flush between steps): time the whole loop as ONE interval,
+            # flush fills included, so nothing a merge does can hide in an untimed gap
+            total_ms = ev[0][0].elapsed_time(ev[K][1])
         clk = clocks.stop() if rank == 0 else None
 
         # ---- e2e: C ABI with host buffers, image delivered to pinned host memory EVERY step -------------
@@ -394,8 +416,8 @@ def run_b200(args):
     samples_per_step = n_pix * spp_step                  # all ranks together
     value = samples_per_step * K / (total_ms * 1e-3) / 1e6
     e2e_value = samples_per_step * e2e_steps / (e2e_ms * 1e-3) / 1e6
-    spp_rank = spp_step / world if args.shard == "samples" else spp_step   # per-pixel samples one launch evaluates
-    pix_rank = n_pix if args.shard == "samples" else n_pix / world
+    spp_rank = spp_step / world if args.shard != "tiles" else spp_step   # per-pixel samples one launch evaluates
+    pix_rank = n_pix if args.shard != "tiles" else n_pix / world
 
     if rank == 0:
         # ---- roofline of the dominant kernel, from the live per-launch event durations -------------------
@@ -460,6 +482,11 @@ def run_b200(args):
             sharding = "none"
         elif args.shard == "tiles":
             sharding = "interleaved image rows per rank; merge = NCCL reduce of disjoint RGBA8 rows"
+        elif args.shard == "p2p":
+            sharding = ("disjoint sample ranges per rank; merge = one fused kernel per GPU over NVLink peer memory (P2P loads of "
+                        "the partial accumulation buffers for the rank's pixel slab, rank-order sum, resolve, P2P store into rank 0's "
+                        "image), double-buffered partials: the merge of frame k overlaps the rendering of frame k+1, drained inside "
+                        "the timed total")
         else:
             sharding = "disjoint sample ranges per rank; merge = NCCL reduce(sum) of float4 accumulation buffers + resolve on rank 0"
         sharding += "" if world == 1 else (", every step" if merge_every_step else ", once, inside the timed total")
@@ -471,7 +498,8 @@ def run_b200(args):
                        "spp_per_step_per_rank": spp_rank, "seed": 0, "jitter": not literal, "sharding": sharding,
                        "max_depth": wl.get("max_depth", 0), "scene": scene.name if scene is not None else "default (Test.hlsl literals)",
                        "l2": "flushed between timed steps (256 MB fill, untimed)",
-                       "timing": "per-step CUDA events on the launching stream, summed; max over ranks"},
+                       "timing": ("one CUDA-event interval over all K steps incl. the L2-flush fills and the drain of in-flight merges; max over ranks"
+                                  if pipelined else "per-step CUDA events on the launching stream, summed; max over ranks")},
             "roofline": roof,
             "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": 128, "d2h_bytes_per_step": n_pix * 4,
@@ -504,8 +532,9 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel per step")
     ap.add_argument("--cpu-spp", type=int, default=16, help="spp per step of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--shard", default="samples", choices=["samples", "tiles"],
-                    help="multi-GPU partitioning: disjoint sample ranges (default) or interleaved image rows")
+    ap.add_argument("--shard", default="samples", choices=["samples", "tiles", "p2p"],
+                    help="multi-GPU partitioning: disjoint sample ranges merged by NCCL reduce (default), interleaved image "
+                         "rows, or sample ranges merged by the fused peer-memory kernel (p2p)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3           # timing rule: W >= 3

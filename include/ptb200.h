@@ -230,6 +230,25 @@ int ptb_scene_read_bvh(ptb_context *ctx, int which, void *nodes_out, uint32_t ca
 int ptb_trace_rays(ptb_context *ctx, uint64_t n_rays, const float *origins, const float *dirs, float t_min,
                    float t_max, int mode, int32_t *out_prim, float *out_t);
 
+/* ---- fused multi-GPU merge over NVLink peer memory (north_star stage n8; no reference counterpart) -------------
+ * With sample-range sharding every GPU holds a partial accumulation buffer of the whole frame.  ptb_peer_merge, called
+ * on every GPU for its own slab of pixels [slab_first, slab_first+slab_count), loads the partials of those pixels from
+ * all peers (device pointers into peer memory, rank order), adds them in that order, adds the sum to this context's
+ * slab of the running total (the partials are NOT cleared: every GPU calls ptb_accum_clear on its own buffer once all
+ * merges have finished), resolves (total / spp_total -> UNORM8, PTB_RESOLVE_*) and stores the
+ * pixels into dst_image (the RGBA8 image of the destination GPU, also peer memory).  One kernel, no staging buffer.
+ * The caller provides the cross-GPU ordering: every peer's samples are rendered before, and nobody renders again until
+ * every GPU's merge has finished (pathtracing_b200/dist.py uses a 1-element all-reduce on the same stream).
+ * ptb_ipc_export / ptb_ipc_open move the pointers between processes (cudaIpcMemHandle_t, 64 bytes);
+ * which = 0 this context's accumulation buffer, 1 its RGBA8 image.  Mappings are closed by ptb_destroy. */
+#define PTB_MAX_PEERS 16
+#define PTB_IPC_HANDLE_BYTES 64
+int ptb_ipc_export(ptb_context *ctx, int which, void *handle_out);
+int ptb_ipc_open(ptb_context *ctx, const void *handle, void **device_ptr_out);
+int ptb_accum_clear(ptb_context *ctx);   /* zero the accumulation buffer only (keeps the slab total and the spp count) */
+int ptb_peer_merge(ptb_context *ctx, uint32_t n_peers, void *const *peer_accum, void *dst_image, uint32_t slab_first,
+                   uint32_t slab_count, uint32_t spp_total, uint32_t flags);
+
 /* ---- present-equivalent -----------------------------------------------
  * ptb_present replaces the full-screen-quad draw (Renderer.cs:1079-1091) + PSMain
  *   (PixelShader.hlsl:8-19): nearest/repeat sampling of the RGBA8 image onto a dst_w x dst_h

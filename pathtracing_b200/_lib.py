@@ -158,6 +158,10 @@ SIGNATURES = {
                                      _P(C.c_uint32)]),
     "ptb_trace_rays": (C.c_int, [_CTX, C.c_uint64, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_int, C.c_void_p,
                                  C.c_void_p]),
+    "ptb_accum_clear": (C.c_int, [_CTX]),
+    "ptb_ipc_export": (C.c_int, [_CTX, C.c_int, C.c_void_p]),
+    "ptb_ipc_open": (C.c_int, [_CTX, C.c_void_p, _P(C.c_void_p)]),
+    "ptb_peer_merge": (C.c_int, [_CTX, C.c_uint32, _P(C.c_void_p), C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]),
     "ptb_present": (C.c_int, [_CTX, C.c_uint32, C.c_uint32, C.c_uint32]),
     "ptb_read_present": (C.c_int, [_CTX, C.c_void_p, C.c_size_t]),
     "ptb_timer_begin": (C.c_int, [_CTX]),

@@ -215,6 +215,9 @@ int ptb_destroy(ptb_context *ctx)
     cudaSetDevice(ctx->cfg.device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     ptb::scene_destroy(ctx);
+    for (void *p : ctx->ipc_opened) cudaIpcCloseMemHandle(p);
+    ctx->ipc_opened.clear();
+    cudaFree(ctx->slab_total);
     free_buffers(ctx);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -317,6 +320,8 @@ int ptb_accum_reset(ptb_context *ctx)
     int rc = ensure_accum(ctx);
     if (rc != PTB_OK) return rc;
     PTB_CUDA(ctx, cudaMemsetAsync(ctx->buf.accum, 0, n_pixels(ctx) * sizeof(float4), ctx->stream));
+    if (ctx->slab_total)
+        PTB_CUDA(ctx, cudaMemsetAsync(ctx->slab_total, 0, (size_t)ctx->slab_count * sizeof(float4), ctx->stream));
     ctx->accum_spp = 0;
     return PTB_OK;
 }
@@ -411,6 +416,75 @@ int ptb_set_accum_spp(ptb_context *ctx, uint32_t spp_total)
 {
     PTB_ENTER(ctx);
     ctx->accum_spp = spp_total;
+    return PTB_OK;
+}
+
+int ptb_accum_clear(ptb_context *ctx)
+{
+    PTB_ENTER(ctx);
+    int rc = ensure_accum(ctx);
+    if (rc != PTB_OK) return rc;
+    PTB_CUDA(ctx, cudaMemsetAsync(ctx->buf.accum, 0, n_pixels(ctx) * sizeof(float4), ctx->stream));
+    return PTB_OK;
+}
+
+int ptb_ipc_export(ptb_context *ctx, int which, void *handle_out)
+{
+    PTB_ENTER(ctx);
+    if (!handle_out || which < 0 || which > 1) return fail(ctx, PTB_ERR_INVALID, "ptb_ipc_export: bad argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == PTB_IPC_HANDLE_BYTES, "IPC handle size");
+    void *ptr = nullptr;
+    if (which == 0) {
+        int rc = ensure_accum(ctx);
+        if (rc != PTB_OK) return rc;
+        if (ctx->buf.accum != ctx->buf.accum_owned)
+            return fail(ctx, PTB_ERR_STATE, "ptb_ipc_export: the accumulation buffer is caller-owned (ptb_set_accum_buffer)");
+        ptr = ctx->buf.accum_owned;
+    } else {
+        ptr = ctx->buf.rgba8;
+    }
+    cudaIpcMemHandle_t h;
+    PTB_CUDA(ctx, cudaIpcGetMemHandle(&h, ptr));
+    std::memcpy(handle_out, &h, sizeof h);
+    return PTB_OK;
+}
+
+int ptb_ipc_open(ptb_context *ctx, const void *handle, void **device_ptr_out)
+{
+    PTB_ENTER(ctx);
+    if (!handle || !device_ptr_out) return fail(ctx, PTB_ERR_INVALID, "ptb_ipc_open: NULL argument");
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, sizeof h);
+    void *p = nullptr;
+    PTB_CUDA(ctx, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    ctx->ipc_opened.push_back(p);
+    *device_ptr_out = p;
+    return PTB_OK;
+}
+
+int ptb_peer_merge(ptb_context *ctx, uint32_t n_peers, void *const *peer_accum, void *dst_image, uint32_t slab_first,
+                   uint32_t slab_count, uint32_t spp_total, uint32_t flags)
+{
+    PTB_ENTER(ctx);
+    if (n_peers == 0 || n_peers > PTB_MAX_PEERS || !peer_accum || !dst_image)
+        return fail(ctx, PTB_ERR_INVALID, "ptb_peer_merge: need 1..%d peers and a destination image", PTB_MAX_PEERS);
+    if (flags & ~(PTB_RESOLVE_SRGB | PTB_RESOLVE_BGRA)) return fail(ctx, PTB_ERR_INVALID, "ptb_peer_merge: unknown flags 0x%x", flags);
+    if (spp_total == 0) return fail(ctx, PTB_ERR_STATE, "ptb_peer_merge: 0 spp");
+    if ((uint64_t)slab_first + slab_count > n_pixels(ctx)) return fail(ctx, PTB_ERR_INVALID, "ptb_peer_merge: slab beyond the image");
+    for (uint32_t q = 0; q < n_peers; ++q)
+        if (!peer_accum[q] || ((uintptr_t)peer_accum[q] & 15u)) return fail(ctx, PTB_ERR_INVALID, "ptb_peer_merge: peer %u pointer", q);
+    if (slab_count == 0) return PTB_OK;
+    if (!ctx->slab_total || ctx->slab_first != slab_first || ctx->slab_count != slab_count) {
+        cudaFree(ctx->slab_total);
+        ctx->slab_total = nullptr;
+        PTB_CUDA(ctx, cudaMalloc(&ctx->slab_total, (size_t)slab_count * sizeof(float4)));
+        PTB_CUDA(ctx, cudaMemsetAsync(ctx->slab_total, 0, (size_t)slab_count * sizeof(float4), ctx->stream));
+        ctx->slab_first = slab_first;
+        ctx->slab_count = slab_count;
+    }
+    PTB_CUDA(ctx, ptb::launch_peer_merge(peer_accum, n_peers, ctx->slab_total, static_cast<uint32_t *>(dst_image), slab_first,
+                                         slab_count, spp_total, flags, ctx->stream));
+    ctx->launches += 1;
     return PTB_OK;
 }
 

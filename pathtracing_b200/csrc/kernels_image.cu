@@ -102,6 +102,80 @@ cudaError_t launch_resolve(const float4 *accum, uint32_t *out8, uint32_t n_pixel
     return cudaGetLastError();
 }
 
+// ---- fused multi-GPU merge + resolve over NVLink peer memory (north_star stage n8) ----------------------------
+// Sample-range sharding leaves G partial float4 accumulation buffers, one per GPU.  Instead of an NCCL reduce of the
+// whole 133 MB frame to one GPU followed by a resolve there, every GPU runs THIS kernel over its own 1/G slab of the
+// pixels: it loads the G partials of each pixel straight from the peers' memory (P2P loads through NVSwitch), adds them
+// in rank order (a fixed order: the merged image does not depend on timing), folds the sum into its slab of the
+// running total, resolves to UNORM8 and stores the pixel into the destination GPU's image (P2P store).  Per GPU
+// (G-1)/G of one frame's partials cross NVLink inbound, spread over all G-1 peers at once through the switch, and 1/G of
+// the RGBA8 image goes out; one launch, no staging buffer, no second pass for the resolve.  Each GPU clears its own
+// partial buffer afterwards (local memset, ptb_accum_clear) instead of paying for remote zero stores.
+struct PeerPtrs {
+    float4 *p[PTB_MAX_PEERS];
+};
+
+template <bool SRGB, bool BGRA>
+__global__ void __launch_bounds__(256) peer_merge_kernel(const PeerPtrs peers, uint32_t n_peers, float4 *__restrict__ total,
+                                                         uint32_t *__restrict__ dst_img, uint32_t first, uint32_t count, float spp)
+{
+    __shared__ float th[256];
+    if (SRGB) {
+        th[threadIdx.x] = c_srgb_thresh[threadIdx.x];
+        __syncthreads();
+    }
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
+        const uint32_t p = first + i;
+        float4 parts[PTB_MAX_PEERS];
+#pragma unroll
+        for (uint32_t q = 0; q < PTB_MAX_PEERS; ++q)          // all loads in flight before the first add
+            if (q < n_peers) parts[q] = __ldcs(peers.p[q] + p);
+        float4 sum = parts[0];
+#pragma unroll
+        for (uint32_t q = 1; q < PTB_MAX_PEERS; ++q)
+            if (q < n_peers) {
+                sum.x = fadd(sum.x, parts[q].x); sum.y = fadd(sum.y, parts[q].y);
+                sum.z = fadd(sum.z, parts[q].z); sum.w = fadd(sum.w, parts[q].w);
+            }
+        float4 t = total[i];
+        t.x = fadd(t.x, sum.x); t.y = fadd(t.y, sum.y); t.z = fadd(t.z, sum.z); t.w = fadd(t.w, sum.w);
+        total[i] = t;
+        const float r = fdiv(t.x, spp), g = fdiv(t.y, spp), b = fdiv(t.z, spp), al = fdiv(t.w, spp);
+        uint32_t r8, g8, b8;
+        if (SRGB) {
+            r8 = srgb8_from_linear(th, r);
+            g8 = srgb8_from_linear(th, g);
+            b8 = srgb8_from_linear(th, b);
+        } else {
+            r8 = unorm8(r);
+            g8 = unorm8(g);
+            b8 = unorm8(b);
+        }
+        const uint32_t a8 = unorm8(al);
+        dst_img[p] = BGRA ? (b8 | (g8 << 8) | (r8 << 16) | (a8 << 24)) : (r8 | (g8 << 8) | (b8 << 16) | (a8 << 24));
+    }
+}
+
+cudaError_t launch_peer_merge(void *const *peer_accum, uint32_t n_peers, float4 *total, uint32_t *dst_img, uint32_t first,
+                              uint32_t count, uint32_t spp_total, uint32_t flags, cudaStream_t s)
+{
+    if (count == 0) return cudaSuccess;
+    PeerPtrs pp{};
+    for (uint32_t q = 0; q < n_peers; ++q) pp.p[q] = static_cast<float4 *>(peer_accum[q]);
+    const int block = 256;
+    int grid = (int)((count + block - 1) / block);
+    const int cap = 148 * 8;
+    if (grid > cap) grid = cap;
+    const float spp = (float)spp_total;
+    const bool srgb = flags & PTB_RESOLVE_SRGB, bgra = flags & PTB_RESOLVE_BGRA;
+    if (srgb && bgra) peer_merge_kernel<true, true><<<grid, block, 0, s>>>(pp, n_peers, total, dst_img, first, count, spp);
+    else if (srgb) peer_merge_kernel<true, false><<<grid, block, 0, s>>>(pp, n_peers, total, dst_img, first, count, spp);
+    else if (bgra) peer_merge_kernel<false, true><<<grid, block, 0, s>>>(pp, n_peers, total, dst_img, first, count, spp);
+    else peer_merge_kernel<false, false><<<grid, block, 0, s>>>(pp, n_peers, total, dst_img, first, count, spp);
+    return cudaGetLastError();
+}
+
 template <bool SRGB>
 __global__ void __launch_bounds__(256) present_kernel(const uint32_t *__restrict__ src, uint32_t sw, uint32_t sh,
                                                       uint32_t *__restrict__ dst, uint32_t dw, uint32_t dh)

@@ -3,6 +3,7 @@
 #pragma once
 #include <cstdint>
 #include <string>
+#include <vector>
 #include <cuda_runtime.h>
 
 #include "../../include/ptb200.h"
@@ -71,6 +72,9 @@ cudaError_t launch_resolve(const float4 *accum, uint32_t *out8, uint32_t n_pixel
 cudaError_t launch_present(const uint32_t *src, uint32_t sw, uint32_t sh, uint32_t *dst, uint32_t dw,
                            uint32_t dh, uint32_t flags, cudaStream_t s);
 
+cudaError_t launch_peer_merge(void *const *peer_accum, uint32_t n_peers, float4 *total, uint32_t *dst_img, uint32_t first,
+                              uint32_t count, uint32_t spp_total, uint32_t flags, cudaStream_t s);
+
 // scene.cu — the scene path (n3-n7) behind ptb_compute_frame / ptb_render_samples / ptb_wait
 void scene_destroy(ptb_context *ctx);
 bool scene_resident(const ptb_context *ctx);
@@ -100,4 +104,8 @@ struct ptb_context {
     uint64_t launches = 0;
     std::string err;
     void *scene = nullptr;       // ptb::SceneState*, owned (scene.cu)
+    // fused peer merge (ptb_peer_merge): this GPU's slab of the running total, and the IPC mappings it opened
+    float4 *slab_total = nullptr;
+    uint32_t slab_first = 0, slab_count = 0;
+    std::vector<void *> ipc_opened;
 };

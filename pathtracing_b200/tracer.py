@@ -210,6 +210,28 @@ class NativeTracer:
                                           1 if any_hit else 0, prim.ctypes.data, t.ctypes.data))
         return (prim, None) if any_hit else (prim, t)
 
+    # -- fused multi-GPU merge over peer memory ---------------------------------------------------
+    def accum_clear(self) -> None:
+        self._ck(self._lib.ptb_accum_clear(self._ctx))
+
+    def ipc_export(self, which: int) -> bytes:
+        """cudaIpcMemHandle_t (64 bytes) of this context's accumulation buffer (0) or RGBA8 image (1)."""
+        buf = C.create_string_buffer(64)
+        self._ck(self._lib.ptb_ipc_export(self._ctx, which, buf))
+        return buf.raw
+
+    def ipc_open(self, handle: bytes) -> int:
+        ptr = C.c_void_p()
+        self._ck(self._lib.ptb_ipc_open(self._ctx, handle, C.byref(ptr)))
+        return int(ptr.value)
+
+    def peer_merge(self, peer_accum, dst_image: int, slab_first: int, slab_count: int, spp_total: int,
+                   srgb: bool = False, bgra: bool = False) -> None:
+        """Sum the peers' partial accumulation buffers over this GPU's slab, resolve, store into dst_image."""
+        arr = (C.c_void_p * len(peer_accum))(*peer_accum)
+        self._ck(self._lib.ptb_peer_merge(self._ctx, len(peer_accum), arr, dst_image, slab_first, slab_count, spp_total,
+                                          (RESOLVE_SRGB if srgb else 0) | (RESOLVE_BGRA if bgra else 0)))
+
     # -- present-equivalent ----------------------------------------------------------------
     def present(self, dst_w: Optional[int] = None, dst_h: Optional[int] = None, srgb: bool = True) -> None:
         self._ck(self._lib.ptb_present(self._ctx, dst_w or self.width, dst_h or self.height,

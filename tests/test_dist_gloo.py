@@ -15,7 +15,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-from pathtracing_b200.dist import ShardedRenderer, row_shard, sample_range  # noqa: E402
+from pathtracing_b200.dist import ShardedRenderer, row_shard, sample_range, slab_range  # noqa: E402
 
 W, H, SEED = 96, 54, 5
 
@@ -130,6 +130,11 @@ def test_sample_range_partition():
         assert covered == list(range(first, first + count))          # disjoint, ordered, complete
         assert max(n for _, n in spans) - min(n for _, n in spans) <= 1
     assert [row_shard(r, 4) for r in range(4)] == [(0, 4), (1, 4), (2, 4), (3, 4)]
+    # pixel slabs of the fused peer merge: contiguous, disjoint, complete
+    for n, world in [(3840 * 2160, 8), (1920 * 1080, 3), (5, 8)]:
+        slabs = [slab_range(r, world, n) for r in range(world)]
+        assert slabs[0][0] == 0 and sum(c for _, c in slabs) == n
+        assert all(slabs[i][0] + slabs[i][1] == slabs[i + 1][0] for i in range(world - 1))
 
 
 def test_tile_sharding_two_ranks_is_bit_identical(oracle):

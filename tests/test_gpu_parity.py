@@ -451,3 +451,62 @@ def test_sharded_renderer_single_rank_paths(oracle):
         got = img.cpu().numpy().view(np.uint8).reshape(h, w, 4)
         assert np.array_equal(got, oracle.resolve(ref, 7))
         eng.close()
+
+
+def test_fused_peer_merge_kernel_single_process(oracle):
+    """ptb_peer_merge (n8, the fused merge+resolve over peer memory) with three 'ranks' = three contexts on one device:
+    every rank merges its own pixel slab from all three partial accumulation buffers into rank 0's image.  Sum order is
+    rank order, so the merged accumulation is reproducible exactly on the CPU; partials are cleared; a second progressive
+    batch lands on top of the running total."""
+    from pathtracing_b200.dist import sample_range, slab_range
+    w, h, seed, world = 200, 90, 6, 3
+    p = oracle.frame_params(w, h)
+    ranks = [NativeTracer(w, h, seed=seed) for _ in range(world)]
+    try:
+        accum_ptrs = [t.device_accum() for t in ranks]
+        for t in ranks:
+            t.accum_reset()
+        total = np.zeros((h, w, 4), np.float32)
+        spp = 0
+        for first, count in ((0, 7), (7, 5)):
+            parts = []
+            for r, t in enumerate(ranks):
+                st, n = sample_range(first, count, r, world)
+                t.render_samples(st, n)
+                parts.append(oracle.accumulate(p, st, n, seed, True))
+            for t in ranks:
+                t.wait()
+            spp += count
+            for r, t in enumerate(ranks):
+                s0, sn = slab_range(r, world, w * h)
+                t.peer_merge(accum_ptrs, ranks[0].device_rgba8(), s0, sn, spp, srgb=True)
+            for t in ranks:
+                t.wait()
+            total = total + ((parts[0] + parts[1]) + parts[2])          # rank order, then onto the running total
+            assert np.array_equal(ranks[0].read_rgba8(), oracle.resolve(total, spp, srgb=True))
+            for t in ranks:
+                t.accum_clear()                                          # each rank clears its own partials afterwards
+                assert not t.read_accum().any()
+    finally:
+        for t in ranks:
+            t.destroy()
+
+
+def test_sharded_renderer_p2p_single_rank(oracle):
+    import torch
+    from pathtracing_b200.dist import GpuEngine, ShardedRenderer
+    w, h = 320, 180
+    p = oracle.frame_params(w, h)
+    eng = GpuEngine(w, h, 0, seed=9, peer_memory=True)
+    sr = ShardedRenderer(eng, mode="p2p")
+    sr.render(0, 4)
+    a = oracle.accumulate(p, 0, 4, 9, True)
+    img = sr.merge(0)
+    torch.cuda.synchronize()
+    assert np.array_equal(img.cpu().numpy().view(np.uint8).reshape(h, w, 4), oracle.resolve(a, 4))
+    sr.render(4, 3)
+    b = oracle.accumulate(p, 4, 3, 9, True)
+    img = sr.merge(0)
+    torch.cuda.synchronize()
+    assert np.array_equal(img.cpu().numpy().view(np.uint8).reshape(h, w, 4), oracle.resolve(a + b, 7))
+    eng.close()
