@@ -17,6 +17,7 @@
 // one live path per wave, so terminated paths add their radiance to the float4 accumulation
 // buffer with a plain read-modify-write.
 #include <cfloat>
+#include <cstdlib>
 
 #include "ptb_math.cuh"
 #include "scene.cuh"
@@ -401,6 +402,7 @@ struct WaveArgs {
     uint32_t n0;              // depth 0: pixels in this context's row shard
     uint32_t depth, sample;
     int jitter;
+    int tail;                 // 1: finish every path of this launch in-kernel (bounce loop, no more queues)
     float4 *accum;
     int32_t *hit_ids;
     SceneStatsDev *stats;
@@ -450,6 +452,8 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
                 dx = s1.x; dy = s1.y; dz = s1.z; tr = s1.w; tg = s2.x; tb = s2.y;
             }
         }
+        uint32_t depth = w.depth;
+      bounce_again:
         float cr = 0.0f, cg = 0.0f, cb = 0.0f;     // radiance this path adds now
         bool add = false;
         // closest hit: warp-synchronous, every lane takes part (lanes past the end of the queue idle)
@@ -479,11 +483,11 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
                 cb = tb * ((1.0f - a) * k.sky_h[2] + a * k.sky_z[2]);
                 add = true;
                 alive = false;
-            } else if (w.depth == k.max_depth) {
+            } else if (depth == k.max_depth) {
                 alive = false;                      // bounce budget spent: contributes nothing
             } else {
                 const ptb_material m = k.materials[mat < k.n_materials ? mat : 0u];
-                const U3 v = pcg3d(pix, w.sample, k.seed + (w.depth + 1u) * 0x9E3779B9u);
+                const U3 v = pcg3d(pix, w.sample, k.seed + (depth + 1u) * 0x9E3779B9u);
                 if (STATS) ++n_scatter;
                 if (scatter(m, dx, dy, dz, nx, ny, nz, bits_to_unit(v.x), bits_to_unit(v.y), bits_to_unit(v.z))) {
                     tr = tr * m.albedo[0]; tg = tg * m.albedo[1]; tb = tb * m.albedo[2];
@@ -502,8 +506,18 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
                 w.accum[pix] = acc;
             }
         }
-        // queue compaction: warp ballot + prefix popcount, one atomic per warp
         const unsigned live = __ballot_sync(FULL, alive);
+        if (!DEPTH0 && w.tail) {
+            // tail mode (launch-uniform): the few paths still alive at this depth finish here, bounce after bounce, with
+            // no further launches or queues — deep queues are too small to fill the GPU, so their per-launch latency
+            // dominated (profiles/r01_notes.md).  Lanes whose path has ended idle until the warp's last path ends.
+            if (live) {
+                ++depth;
+                goto bounce_again;
+            }
+            continue;
+        }
+        // queue compaction: warp ballot + prefix popcount, one atomic per warp
         if (live) {
             uint32_t obase = 0;
             if (lane == 0) obase = atomicAdd(w.n_out, (uint32_t)__popc(live));
@@ -667,6 +681,11 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
     const uint32_t n0 = rows * k.width;
     if (n0 == 0) return cudaSuccess;
     const uint32_t depths = k.shade_mode == PTB_SHADE_NORMALS ? 1u : k.max_depth + 1u;
+    // bounces >= tail_depth run inside ONE launch (0 disables); PTB200_TAIL_DEPTH overrides for A/B runs
+    static const uint32_t tail_depth = [] {
+        const char *e = std::getenv("PTB200_TAIL_DEPTH");
+        return e ? (uint32_t)std::atoi(e) : 4u;
+    }();
     // counters: [0, depths] queue sizes, [depths+1, 2*depths+1] work cursors
     cudaError_t e = cudaMemsetAsync(st->counts, 0, sizeof(uint32_t) * st->counts_len, s);
     if (e != cudaSuccess) return e;
@@ -681,6 +700,7 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
         w.depth = d;
         w.sample = sample;
         w.jitter = jitter ? 1 : 0;
+        w.tail = (tail_depth > 0 && d >= tail_depth && d + 1u < depths) ? 1 : 0;
         w.accum = accum;
         w.hit_ids = hit_ids;
         w.stats = st->stats;
@@ -693,6 +713,7 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
             else bounce_kernel<false, false><<<wave_blocks<false, false>(), 256, 0, s>>>(k, w);
         }
         if (launches) ++*launches;
+        if (w.tail) break;
     }
     return cudaGetLastError();
 }
