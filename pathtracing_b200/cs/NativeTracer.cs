@@ -80,6 +80,18 @@ public sealed unsafe class NativeTracer : IDisposable
     [DllImport(Lib)] private static extern int ptb_trace_rays(IntPtr ctx, ulong nRays, float* origins, float* dirs, float tMin,
                                                               float tMax, int mode, int* outPrim, float* outT);
 
+    // ---- multi-GPU: row shards, external accumulation buffers, fused merge over NVLink peer memory
+    [DllImport(Lib)] private static extern int ptb_set_row_shard(IntPtr ctx, uint rowOffset, uint rowStride);
+    [DllImport(Lib)] private static extern int ptb_set_accum_buffer(IntPtr ctx, void* devicePtr);
+    [DllImport(Lib)] private static extern int ptb_set_accum_spp(IntPtr ctx, uint sppTotal);
+    [DllImport(Lib)] private static extern int ptb_accum_clear(IntPtr ctx);
+    [DllImport(Lib)] private static extern void* ptb_device_accum(IntPtr ctx);
+    [DllImport(Lib)] private static extern void* ptb_device_rgba8(IntPtr ctx);
+    [DllImport(Lib)] private static extern int ptb_ipc_export(IntPtr ctx, int which, byte* handle64);
+    [DllImport(Lib)] private static extern int ptb_ipc_open(IntPtr ctx, byte* handle64, out IntPtr devicePtr);
+    [DllImport(Lib)] private static extern int ptb_peer_merge(IntPtr ctx, uint nPeers, IntPtr* peerAccum, IntPtr dstImage,
+                                                              uint slabFirst, uint slabCount, uint sppTotal, uint flags);
+
     public const uint ResolveSrgb = 1, ResolveBgra = 2;
 
     private IntPtr _ctx;
@@ -142,6 +154,30 @@ public sealed unsafe class NativeTracer : IDisposable
         fixed (float* o = origins, d = dirs, tt = t)
         fixed (int* pp = prim)
             Check(_ctx, ptb_trace_rays(_ctx, (ulong)prim.Length, o, d, tMin, tMax, anyHit ? 1 : 0, pp, anyHit ? null : tt));
+    }
+
+    public void SetRowShard(uint rowOffset, uint rowStride) => Check(_ctx, ptb_set_row_shard(_ctx, rowOffset, rowStride));
+    public IntPtr DeviceAccum => (IntPtr)ptb_device_accum(_ctx);
+    public IntPtr DeviceImage => (IntPtr)ptb_device_rgba8(_ctx);
+    public void ClearPartials() => Check(_ctx, ptb_accum_clear(_ctx));
+
+    public byte[] IpcExport(int which)                                   // 0 accumulation buffer, 1 RGBA8 image
+    {
+        var h = new byte[64];
+        fixed (byte* p = h) Check(_ctx, ptb_ipc_export(_ctx, which, p));
+        return h;
+    }
+
+    public IntPtr IpcOpen(byte[] handle)
+    {
+        fixed (byte* p = handle) { Check(_ctx, ptb_ipc_open(_ctx, p, out IntPtr ptr)); return ptr; }
+    }
+
+    // This GPU's pixel slab: sum the peers' partial buffers in rank order, resolve, store into dstImage (peer memory).
+    public void PeerMerge(ReadOnlySpan<IntPtr> peerAccum, IntPtr dstImage, uint slabFirst, uint slabCount, uint sppTotal, uint flags = 0)
+    {
+        fixed (IntPtr* p = peerAccum)
+            Check(_ctx, ptb_peer_merge(_ctx, (uint)peerAccum.Length, p, dstImage, slabFirst, slabCount, sppTotal, flags));
     }
 
     public void Dispose()

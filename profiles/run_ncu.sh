@@ -10,4 +10,4 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
 $CMD > gpurun_out/plain2.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:csmain_accumulate -s 3 -c 2 \
     -f -o gpurun_out/prof_accumulate $CMD > gpurun_out/ncu_full.log 2>&1
-tail -2 gpurun_out/ncu_launches.log gpurun_out/ncu_full.log
+tail -q -n 2 gpurun_out/ncu_launches.log gpurun_out/ncu_full.log
