@@ -405,8 +405,8 @@ def run_b200(args):
                                  "achieved": bytes_frame / (iso_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"],
                                  "frac": bytes_frame / (iso_ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
                                  "algorithmic_bytes_per_launch": bytes_frame,
-                                 "note": "8.3 MB written per launch = 1.3 us at the HBM roof; ~40 exact-rounded FP32 "
-                                         "instructions per pixel make even the 1-spp frame FP32-issue bound"}}
+                                 "note": "8.3 MB written per launch = 1.3 us at the HBM roof; the back-to-back figure is dominated by "
+                                         "launch latency (one ~5 us kernel per frame, nothing to overlap it with)"}}
 
     tot = torch.tensor([total_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
     if world > 1:
@@ -444,7 +444,7 @@ def run_b200(args):
                     "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None,
                     "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peaks['source']}); the scene ({c['scene_bytes'] / 1e6:.1f} MB) is "
                                    "L2-resident, so node/primitive fetch is served by L1/L2 and the kernel is latency / "
-                                   "divergence bound rather than HBM bound (DESIGN.md 7)",
+                                   "divergence bound rather than HBM bound (DESIGN.md 5)",
                     "algorithmic_bytes_per_sample": b_sample, "algorithmic_bytes_per_wave": alg,
                     "launches_per_wave": n_launch, "wave_ms": wave_ms, "launch_ms": wave_ms / n_launch,
                     "counters": c}
