@@ -114,6 +114,7 @@ int ptb_read_hit_ids(ptb_context *ctx, int32_t *host_dst, size_t pitch_bytes);/*
 void *ptb_device_rgba8(ptb_context *ctx);
 void *ptb_device_f32(ptb_context *ctx);
 void *ptb_device_accum(ptb_context *ctx);
+void *ptb_device_peer_flags(ptb_context *ctx);   /* this context's rendezvous flag block (ptb_peer_barrier) */
 
 /* ---- multi-sample accumulation (north_star stages n1/n2; no reference counterpart) ------
  * ptb_render_samples: for each pixel, samples s in [first_sample, first_sample+n_samples)
@@ -240,11 +241,19 @@ int ptb_trace_rays(ptb_context *ctx, uint64_t n_rays, const float *origins, cons
  * The caller provides the cross-GPU ordering: every peer's samples are rendered before, and nobody renders again until
  * every GPU's merge has finished (pathtracing_b200/dist.py uses a 1-element all-reduce on the same stream).
  * ptb_ipc_export / ptb_ipc_open move the pointers between processes (cudaIpcMemHandle_t, 64 bytes);
- * which = 0 this context's accumulation buffer, 1 its RGBA8 image.  Mappings are closed by ptb_destroy. */
+ * which = 0 this context's accumulation buffer, 1 its RGBA8 image, 2 its rendezvous flag block.  Mappings are closed by ptb_destroy. */
+#define PTB_MERGE_BACKGROUND 0x10u  /* ptb_peer_merge flag: small grid (one block per SM) for a merge that overlaps a render */
 #define PTB_MAX_PEERS 16
 #define PTB_IPC_HANDLE_BYTES 64
 int ptb_ipc_export(ptb_context *ctx, int which, void *handle_out);
 int ptb_ipc_open(ptb_context *ctx, const void *handle, void **device_ptr_out);
+/* Rendezvous of the GPUs taking part in a peer merge, on the context's stream, without the host: a one-warp kernel
+ * stores `epoch` into this GPU's slot of every peer's flag block (ptb_ipc_export which = 2; peer_flags in rank order,
+ * own block included) and waits until every peer has stored `epoch` into this GPU's block.  phase 0 / 1 are two
+ * independent sets of slots (e.g. "rendered" and "merged").  Epochs must increase by one per use of a phase.
+ * Gives up after ~10 s (PTB_ERR_STATE from the next ptb_wait). */
+int ptb_peer_barrier(ptb_context *ctx, uint32_t n_peers, void *const *peer_flags, uint32_t self_rank, uint32_t phase,
+                     uint32_t epoch);
 int ptb_accum_clear(ptb_context *ctx);   /* zero the accumulation buffer only (keeps the slab total and the spp count) */
 int ptb_peer_merge(ptb_context *ctx, uint32_t n_peers, void *const *peer_accum, void *dst_image, uint32_t slab_first,
                    uint32_t slab_count, uint32_t spp_total, uint32_t flags);

@@ -159,6 +159,8 @@ SIGNATURES = {
     "ptb_trace_rays": (C.c_int, [_CTX, C.c_uint64, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_int, C.c_void_p,
                                  C.c_void_p]),
     "ptb_accum_clear": (C.c_int, [_CTX]),
+    "ptb_device_peer_flags": (C.c_void_p, [_CTX]),
+    "ptb_peer_barrier": (C.c_int, [_CTX, C.c_uint32, _P(C.c_void_p), C.c_uint32, C.c_uint32, C.c_uint32]),
     "ptb_ipc_export": (C.c_int, [_CTX, C.c_int, C.c_void_p]),
     "ptb_ipc_open": (C.c_int, [_CTX, C.c_void_p, _P(C.c_void_p)]),
     "ptb_peer_merge": (C.c_int, [_CTX, C.c_uint32, _P(C.c_void_p), C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]),

@@ -218,6 +218,7 @@ int ptb_destroy(ptb_context *ctx)
     for (void *p : ctx->ipc_opened) cudaIpcCloseMemHandle(p);
     ctx->ipc_opened.clear();
     cudaFree(ctx->slab_total);
+    cudaFree(ctx->peer_flags);
     free_buffers(ctx);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -251,6 +252,11 @@ int ptb_wait(ptb_context *ctx)
     if (ctx->copy_pending) {
         PTB_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
         ctx->copy_pending = false;
+    }
+    if (ctx->peer_flags) {
+        uint32_t err = 0;
+        PTB_CUDA(ctx, cudaMemcpy(&err, ctx->peer_flags + 2 * PTB_MAX_PEERS, sizeof err, cudaMemcpyDeviceToHost));
+        if (err) return fail(ctx, PTB_ERR_STATE, "ptb_peer_barrier timed out waiting for a peer GPU (10 s)");
     }
     if (ptb::scene_resident(ctx)) return ptb::scene_wait_check(ctx);
     return PTB_OK;
@@ -419,6 +425,39 @@ int ptb_set_accum_spp(ptb_context *ctx, uint32_t spp_total)
     return PTB_OK;
 }
 
+static int ensure_peer_flags(ptb_context *ctx)
+{
+    if (ctx->peer_flags) return PTB_OK;
+    const size_t bytes = (2 * PTB_MAX_PEERS + 1) * sizeof(uint32_t);
+    PTB_CUDA(ctx, cudaMalloc(&ctx->peer_flags, bytes));
+    PTB_CUDA(ctx, cudaMemset(ctx->peer_flags, 0, bytes));
+    return PTB_OK;
+}
+
+void *ptb_device_peer_flags(ptb_context *ctx)
+{
+    if (!ctx || cudaSetDevice(ctx->cfg.device) != cudaSuccess || ensure_peer_flags(ctx) != PTB_OK) return nullptr;
+    return ctx->peer_flags;
+}
+
+int ptb_peer_barrier(ptb_context *ctx, uint32_t n_peers, void *const *peer_flags, uint32_t self_rank, uint32_t phase,
+                     uint32_t epoch)
+{
+    PTB_ENTER(ctx);
+    if (n_peers == 0 || n_peers > PTB_MAX_PEERS || !peer_flags || self_rank >= n_peers || phase > 1)
+        return fail(ctx, PTB_ERR_INVALID, "ptb_peer_barrier: bad argument");
+    for (uint32_t q = 0; q < n_peers; ++q)
+        if (!peer_flags[q]) return fail(ctx, PTB_ERR_INVALID, "ptb_peer_barrier: peer %u pointer is NULL", q);
+    int rc = ensure_peer_flags(ctx);
+    if (rc != PTB_OK) return rc;
+    if (peer_flags[self_rank] != ctx->peer_flags)
+        return fail(ctx, PTB_ERR_INVALID, "ptb_peer_barrier: peer_flags[self_rank] must be this context's own flag block");
+    PTB_CUDA(ctx, ptb::launch_peer_barrier(peer_flags, n_peers, self_rank, phase, epoch, ctx->peer_flags + 2 * PTB_MAX_PEERS,
+                                           ctx->stream));
+    ctx->launches += 1;
+    return PTB_OK;
+}
+
 int ptb_accum_clear(ptb_context *ctx)
 {
     PTB_ENTER(ctx);
@@ -431,7 +470,7 @@ int ptb_accum_clear(ptb_context *ctx)
 int ptb_ipc_export(ptb_context *ctx, int which, void *handle_out)
 {
     PTB_ENTER(ctx);
-    if (!handle_out || which < 0 || which > 1) return fail(ctx, PTB_ERR_INVALID, "ptb_ipc_export: bad argument");
+    if (!handle_out || which < 0 || which > 2) return fail(ctx, PTB_ERR_INVALID, "ptb_ipc_export: bad argument");
     static_assert(sizeof(cudaIpcMemHandle_t) == PTB_IPC_HANDLE_BYTES, "IPC handle size");
     void *ptr = nullptr;
     if (which == 0) {
@@ -440,8 +479,12 @@ int ptb_ipc_export(ptb_context *ctx, int which, void *handle_out)
         if (ctx->buf.accum != ctx->buf.accum_owned)
             return fail(ctx, PTB_ERR_STATE, "ptb_ipc_export: the accumulation buffer is caller-owned (ptb_set_accum_buffer)");
         ptr = ctx->buf.accum_owned;
-    } else {
+    } else if (which == 1) {
         ptr = ctx->buf.rgba8;
+    } else {
+        int rc = ensure_peer_flags(ctx);
+        if (rc != PTB_OK) return rc;
+        ptr = ctx->peer_flags;
     }
     cudaIpcMemHandle_t h;
     PTB_CUDA(ctx, cudaIpcGetMemHandle(&h, ptr));
@@ -468,7 +511,8 @@ int ptb_peer_merge(ptb_context *ctx, uint32_t n_peers, void *const *peer_accum, 
     PTB_ENTER(ctx);
     if (n_peers == 0 || n_peers > PTB_MAX_PEERS || !peer_accum || !dst_image)
         return fail(ctx, PTB_ERR_INVALID, "ptb_peer_merge: need 1..%d peers and a destination image", PTB_MAX_PEERS);
-    if (flags & ~(PTB_RESOLVE_SRGB | PTB_RESOLVE_BGRA)) return fail(ctx, PTB_ERR_INVALID, "ptb_peer_merge: unknown flags 0x%x", flags);
+    if (flags & ~(PTB_RESOLVE_SRGB | PTB_RESOLVE_BGRA | PTB_MERGE_BACKGROUND))
+        return fail(ctx, PTB_ERR_INVALID, "ptb_peer_merge: unknown flags 0x%x", flags);
     if (spp_total == 0) return fail(ctx, PTB_ERR_STATE, "ptb_peer_merge: 0 spp");
     if ((uint64_t)slab_first + slab_count > n_pixels(ctx)) return fail(ctx, PTB_ERR_INVALID, "ptb_peer_merge: slab beyond the image");
     for (uint32_t q = 0; q < n_peers; ++q)

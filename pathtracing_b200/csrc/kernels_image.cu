@@ -8,6 +8,7 @@
 //             (Assets/Shaders/Source/Basic/PixelShader.hlsl:8-19; sampler nearest/repeat,
 //             Renderer.cs:181-191; quad uv without flip, Renderer.cs:45-56) as a headless copy.
 #include <cmath>
+#include <cstdlib>
 #include <mutex>
 
 #include "ptb_internal.h"
@@ -114,46 +115,68 @@ cudaError_t launch_resolve(const float4 *accum, uint32_t *out8, uint32_t n_pixel
 struct PeerPtrs {
     float4 *p[PTB_MAX_PEERS];
 };
+struct PeerFlagPtrs {
+    uint32_t *p[PTB_MAX_PEERS];
+};
 
-template <bool SRGB, bool BGRA>
+// NP = compile-time bound on the number of peers, UNROLL pixels per thread per iteration so that every thread keeps
+// >= 8 independent 16 B loads in flight.  The grid is deliberately SMALL (one 256-thread block per SM): the kernel is
+// bound by NVLink / HBM latency, not by threads, and a machine-filling grid on the high-priority merge stream would take
+// every SM slot away from the next frame's render kernel for the whole duration of the merge — measured: no overlap at
+// all with a 148x8-block grid (experiments/overlap_check.py, profiles/r01_notes.md).
+template <int NP, int UNROLL>
 __global__ void __launch_bounds__(256) peer_merge_kernel(const PeerPtrs peers, uint32_t n_peers, float4 *__restrict__ total,
-                                                         uint32_t *__restrict__ dst_img, uint32_t first, uint32_t count, float spp)
+                                                         uint32_t *__restrict__ dst_img, uint32_t first, uint32_t count, float spp,
+                                                         uint32_t flags)
 {
     __shared__ float th[256];
-    if (SRGB) {
+    const bool srgb = flags & PTB_RESOLVE_SRGB, bgra = flags & PTB_RESOLVE_BGRA;     // launch-uniform
+    if (srgb) {
         th[threadIdx.x] = c_srgb_thresh[threadIdx.x];
         __syncthreads();
     }
     const uint32_t stride = gridDim.x * blockDim.x;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += stride) {
-        const uint32_t p = first + i;
-        float4 parts[PTB_MAX_PEERS];
+    for (uint32_t base = blockIdx.x * blockDim.x + threadIdx.x; base < count; base += stride * UNROLL) {
+        float4 parts[UNROLL][NP];
+        float4 tot[UNROLL];
 #pragma unroll
-        for (uint32_t q = 0; q < PTB_MAX_PEERS; ++q)          // all loads in flight before the first add
-            if (q < n_peers) parts[q] = __ldcs(peers.p[q] + p);
-        float4 sum = parts[0];
+        for (int u = 0; u < UNROLL; ++u) {                    // all loads in flight before the first add
+            const uint32_t i = base + u * stride;
+            if (i < count) {
 #pragma unroll
-        for (uint32_t q = 1; q < PTB_MAX_PEERS; ++q)
-            if (q < n_peers) {
-                sum.x = fadd(sum.x, parts[q].x); sum.y = fadd(sum.y, parts[q].y);
-                sum.z = fadd(sum.z, parts[q].z); sum.w = fadd(sum.w, parts[q].w);
+                for (int q = 0; q < NP; ++q)
+                    if ((uint32_t)q < n_peers) parts[u][q] = __ldcs(peers.p[q] + first + i);
+                tot[u] = total[i];
             }
-        float4 t = total[i];
-        t.x = fadd(t.x, sum.x); t.y = fadd(t.y, sum.y); t.z = fadd(t.z, sum.z); t.w = fadd(t.w, sum.w);
-        total[i] = t;
-        const float r = fdiv(t.x, spp), g = fdiv(t.y, spp), b = fdiv(t.z, spp), al = fdiv(t.w, spp);
-        uint32_t r8, g8, b8;
-        if (SRGB) {
-            r8 = srgb8_from_linear(th, r);
-            g8 = srgb8_from_linear(th, g);
-            b8 = srgb8_from_linear(th, b);
-        } else {
-            r8 = unorm8(r);
-            g8 = unorm8(g);
-            b8 = unorm8(b);
         }
-        const uint32_t a8 = unorm8(al);
-        dst_img[p] = BGRA ? (b8 | (g8 << 8) | (r8 << 16) | (a8 << 24)) : (r8 | (g8 << 8) | (b8 << 16) | (a8 << 24));
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            const uint32_t i = base + u * stride;
+            if (i >= count) continue;
+            float4 sum = parts[u][0];
+#pragma unroll
+            for (int q = 1; q < NP; ++q)
+                if ((uint32_t)q < n_peers) {
+                    sum.x = fadd(sum.x, parts[u][q].x); sum.y = fadd(sum.y, parts[u][q].y);
+                    sum.z = fadd(sum.z, parts[u][q].z); sum.w = fadd(sum.w, parts[u][q].w);
+                }
+            float4 t = tot[u];
+            t.x = fadd(t.x, sum.x); t.y = fadd(t.y, sum.y); t.z = fadd(t.z, sum.z); t.w = fadd(t.w, sum.w);
+            total[i] = t;
+            const float r = fdiv(t.x, spp), g = fdiv(t.y, spp), b = fdiv(t.z, spp), al = fdiv(t.w, spp);
+            uint32_t r8, g8, b8;
+            if (srgb) {
+                r8 = srgb8_from_linear(th, r);
+                g8 = srgb8_from_linear(th, g);
+                b8 = srgb8_from_linear(th, b);
+            } else {
+                r8 = unorm8(r);
+                g8 = unorm8(g);
+                b8 = unorm8(b);
+            }
+            const uint32_t a8 = unorm8(al);
+            dst_img[first + i] = bgra ? (b8 | (g8 << 8) | (r8 << 16) | (a8 << 24)) : (r8 | (g8 << 8) | (b8 << 16) | (a8 << 24));
+        }
     }
 }
 
@@ -163,16 +186,66 @@ cudaError_t launch_peer_merge(void *const *peer_accum, uint32_t n_peers, float4 
     if (count == 0) return cudaSuccess;
     PeerPtrs pp{};
     for (uint32_t q = 0; q < n_peers; ++q) pp.p[q] = static_cast<float4 *>(peer_accum[q]);
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    // PTB_MERGE_BACKGROUND: one block per SM, so the merge shares the machine with a concurrent render kernel instead
+    // of displacing it; otherwise a machine-filling grid (fastest when nothing else runs).  Measured on one B200, 4K frame,
+    // 64-spp render 0.703 ms: merge behind it on the same stream +0.076 ms (8 blocks/SM) / +0.140 ms (1 block/SM); on a
+    // second high-priority stream overlapping the NEXT render +0.061 ms (8/SM) / +0.041 ms (1/SM).
+    static const int env_per_sm = [] {
+        const char *e = std::getenv("PTB200_MERGE_BLOCKS_PER_SM");     // A/B experiments
+        const int v = e ? std::atoi(e) : 0;
+        return v >= 1 && v <= 8 ? v : 0;
+    }();
+    const int per_sm = env_per_sm ? env_per_sm : ((flags & PTB_MERGE_BACKGROUND) ? 1 : 8);
     const int block = 256;
     int grid = (int)((count + block - 1) / block);
-    const int cap = 148 * 8;
-    if (grid > cap) grid = cap;
+    if (grid > sms * per_sm) grid = sms * per_sm;
     const float spp = (float)spp_total;
-    const bool srgb = flags & PTB_RESOLVE_SRGB, bgra = flags & PTB_RESOLVE_BGRA;
-    if (srgb && bgra) peer_merge_kernel<true, true><<<grid, block, 0, s>>>(pp, n_peers, total, dst_img, first, count, spp);
-    else if (srgb) peer_merge_kernel<true, false><<<grid, block, 0, s>>>(pp, n_peers, total, dst_img, first, count, spp);
-    else if (bgra) peer_merge_kernel<false, true><<<grid, block, 0, s>>>(pp, n_peers, total, dst_img, first, count, spp);
-    else peer_merge_kernel<false, false><<<grid, block, 0, s>>>(pp, n_peers, total, dst_img, first, count, spp);
+    if (n_peers <= 2) peer_merge_kernel<2, 4><<<grid, block, 0, s>>>(pp, n_peers, total, dst_img, first, count, spp, flags);
+    else if (n_peers <= 4) peer_merge_kernel<4, 2><<<grid, block, 0, s>>>(pp, n_peers, total, dst_img, first, count, spp, flags);
+    else if (n_peers <= 8) peer_merge_kernel<8, 1><<<grid, block, 0, s>>>(pp, n_peers, total, dst_img, first, count, spp, flags);
+    else peer_merge_kernel<16, 1><<<grid, block, 0, s>>>(pp, n_peers, total, dst_img, first, count, spp, flags);
+    return cudaGetLastError();
+}
+
+// Cross-GPU rendezvous through peer memory: one warp.  Lane q stores `epoch` into slot [phase][self] of peer q's flag
+// array (system-scope release: everything this GPU's stream did before is visible to a peer that observes the flag),
+// then spins until slot [phase][q] of its OWN array reaches `epoch`.  A 32-thread block fits into any SM slot that
+// frees up, so the rendezvous is not starved by a large render grid running at lower priority — which is what happened
+// to the (640-thread) NCCL kernels of a 1-element all-reduce in the pipelined merge (profiles/r01_notes.md).
+// Bounded spin: after ~10 s the kernel gives up and raises *error instead of hanging the GPU.
+__global__ void peer_barrier_kernel(const PeerFlagPtrs peers, uint32_t n_peers, uint32_t self, uint32_t phase, uint32_t epoch,
+                                    uint32_t *error)
+{
+    const uint32_t q = threadIdx.x;
+    if (q >= n_peers) return;
+    __threadfence_system();
+    volatile uint32_t *remote = peers.p[q] + phase * PTB_MAX_PEERS + self;
+    *remote = epoch;
+    __threadfence_system();
+    volatile uint32_t *mine = peers.p[self] + phase * PTB_MAX_PEERS + q;
+    unsigned long long t0 = 0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    while ((int32_t)(*mine - epoch) < 0) {
+        unsigned long long t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        if (t1 - t0 > 10000000000ull) {
+            atomicOr(error, 2u);
+            break;
+        }
+        __nanosleep(200);
+    }
+    __threadfence_system();
+}
+
+cudaError_t launch_peer_barrier(void *const *peer_flags, uint32_t n_peers, uint32_t self, uint32_t phase, uint32_t epoch,
+                                uint32_t *error, cudaStream_t s)
+{
+    PeerFlagPtrs pf{};
+    for (uint32_t q = 0; q < n_peers; ++q) pf.p[q] = static_cast<uint32_t *>(peer_flags[q]);
+    peer_barrier_kernel<<<1, 32, 0, s>>>(pf, n_peers, self, phase, epoch, error);
     return cudaGetLastError();
 }
 

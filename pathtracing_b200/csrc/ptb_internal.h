@@ -75,6 +75,9 @@ cudaError_t launch_present(const uint32_t *src, uint32_t sw, uint32_t sh, uint32
 cudaError_t launch_peer_merge(void *const *peer_accum, uint32_t n_peers, float4 *total, uint32_t *dst_img, uint32_t first,
                               uint32_t count, uint32_t spp_total, uint32_t flags, cudaStream_t s);
 
+cudaError_t launch_peer_barrier(void *const *peer_flags, uint32_t n_peers, uint32_t self, uint32_t phase, uint32_t epoch,
+                                uint32_t *error, cudaStream_t s);
+
 // scene.cu — the scene path (n3-n7) behind ptb_compute_frame / ptb_render_samples / ptb_wait
 void scene_destroy(ptb_context *ctx);
 bool scene_resident(const ptb_context *ctx);
@@ -108,4 +111,5 @@ struct ptb_context {
     float4 *slab_total = nullptr;
     uint32_t slab_first = 0, slab_count = 0;
     std::vector<void *> ipc_opened;
+    uint32_t *peer_flags = nullptr;   // 2 x PTB_MAX_PEERS epochs (arrive / done) + 1 error word, written by the peers
 };

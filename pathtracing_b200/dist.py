@@ -17,7 +17,7 @@ rendering; the only collective is the merge of the per-rank results:
            NCCL reduce: every rank owns a contiguous slab of pixels, loads the partials of that slab from
            all peers (CUDA IPC mappings of their accumulation buffers), adds them in rank order, resolves
            and stores the pixels into rank `dst`'s image (`ptb_peer_merge`).  Cross-rank ordering is a
-           1-element all-reduce before and after the kernel on the same stream.  Deterministic sum order;
+           one-warp rendezvous kernel over peer-memory flags (`ptb_peer_barrier`) before and after.  Deterministic sum order;
            8x less data over NVLink than reduce-to-one at 8 GPUs.
 
 The engine behind a rank is anything with the `LocalEngine` methods: `GpuEngine` (NativeTracer with
@@ -120,7 +120,7 @@ class GpuEngine:
         self.merger = NativeTracer(self.width, self.height, device=self.device.index, stream=self.merge_stream.cuda_stream)
         self.merger.accum_reset()
         self._bufs = [self.tracer.device_accum(), self.merger.device_accum()]
-        mine = (self.tracer.ipc_export(0), self.merger.ipc_export(0), self.tracer.ipc_export(1))
+        mine = (self.tracer.ipc_export(0), self.merger.ipc_export(0), self.tracer.ipc_export(1), self.merger.ipc_export(2))
         handles = [None] * world
         if world > 1:
             dist.all_gather_object(handles, mine, group=group)
@@ -130,6 +130,13 @@ class GpuEngine:
                       for b in range(2)]
         image_ptr = self.tracer.device_rgba8() if dst == rank else self.merger.ipc_open(handles[dst][2])
         self._peers = (accum_ptrs, image_ptr, slab_range(rank, world, self.width * self.height))
+        # rendezvous flag blocks (ptb_peer_barrier): one-warp kernels over peer memory instead of NCCL all-reduces
+        self._flag_ptrs = [self.merger.device_peer_flags() if r == rank else self.merger.ipc_open(handles[r][3])
+                           for r in range(world)]
+        self._rank = rank
+        self._epoch = [0, 0]
+        if world > 1:
+            dist.barrier(group=group)          # every flag block exists and is mapped before the first signal
         self._cur = 0
         self.torch_streams_synced = True
 
@@ -141,10 +148,17 @@ class GpuEngine:
                 self.tracer.device_accum()     # re-binds the context's own buffer
             self._cur = b
 
-    def peer_merge(self, b: int, spp_total: int) -> None:
-        """On the merge stream: this rank's slab of frame buffer b, summed over all peers, into dst's image."""
+    def peer_barrier(self, phase: int) -> None:
+        """On the merge stream: wait until every GPU has reached this point of the same frame."""
+        if len(self._flag_ptrs) > 1:
+            self._epoch[phase] += 1
+            self.merger.peer_barrier(self._flag_ptrs, self._rank, phase, self._epoch[phase])
+
+    def peer_merge(self, b: int, spp_total: int, background: bool = False) -> None:
+        """On the merge stream: this rank's slab of frame buffer b, summed over all peers, into dst's image.
+        background: small grid, for a merge that overlaps the next frame's render kernel."""
         accum_ptrs, image_ptr, (first, count) = self._peers
-        self.merger.peer_merge(accum_ptrs[b], image_ptr, first, count, spp_total)
+        self.merger.peer_merge(accum_ptrs[b], image_ptr, first, count, spp_total, background=background)
 
     def peer_clear(self, b: int) -> None:
         """On the merge stream: local memset of this rank's partial buffer b."""
@@ -242,9 +256,9 @@ class ShardedRenderer:
             rendered.record(e.stream)
             with torch.cuda.stream(e.merge_stream):
                 e.merge_stream.wait_event(rendered)
-                self._rendezvous()         # every rank has rendered this frame's samples (stream-ordered, no host sync)
-                e.peer_merge(b, self.spp_total)
-                self._rendezvous()         # every slab has landed in dst's image; nobody reads these partials any more
+                e.peer_barrier(0)          # every rank has rendered this frame's samples (stream-ordered, no host sync)
+                e.peer_merge(b, self.spp_total, background=pipelined)
+                e.peer_barrier(1)          # every slab has landed in dst's image; nobody reads these partials any more
                 e.peer_clear(b)            # local memset of this rank's partial buffer
                 done = torch.cuda.Event()
                 done.record(e.merge_stream)

@@ -211,6 +211,13 @@ class NativeTracer:
         return (prim, None) if any_hit else (prim, t)
 
     # -- fused multi-GPU merge over peer memory ---------------------------------------------------
+    def device_peer_flags(self) -> int:
+        return int(self._lib.ptb_device_peer_flags(self._ctx) or 0)
+
+    def peer_barrier(self, peer_flags, self_rank: int, phase: int, epoch: int) -> None:
+        arr = (C.c_void_p * len(peer_flags))(*peer_flags)
+        self._ck(self._lib.ptb_peer_barrier(self._ctx, len(peer_flags), arr, self_rank, phase, epoch))
+
     def accum_clear(self) -> None:
         self._ck(self._lib.ptb_accum_clear(self._ctx))
 
@@ -226,11 +233,12 @@ class NativeTracer:
         return int(ptr.value)
 
     def peer_merge(self, peer_accum, dst_image: int, slab_first: int, slab_count: int, spp_total: int,
-                   srgb: bool = False, bgra: bool = False) -> None:
+                   srgb: bool = False, bgra: bool = False, background: bool = False) -> None:
         """Sum the peers' partial accumulation buffers over this GPU's slab, resolve, store into dst_image."""
         arr = (C.c_void_p * len(peer_accum))(*peer_accum)
         self._ck(self._lib.ptb_peer_merge(self._ctx, len(peer_accum), arr, dst_image, slab_first, slab_count, spp_total,
-                                          (RESOLVE_SRGB if srgb else 0) | (RESOLVE_BGRA if bgra else 0)))
+                                          (RESOLVE_SRGB if srgb else 0) | (RESOLVE_BGRA if bgra else 0) |
+                                          (0x10 if background else 0)))
 
     # -- present-equivalent ----------------------------------------------------------------
     def present(self, dst_w: Optional[int] = None, dst_h: Optional[int] = None, srgb: bool = True) -> None:

@@ -464,6 +464,8 @@ def test_fused_peer_merge_kernel_single_process(oracle):
     ranks = [NativeTracer(w, h, seed=seed) for _ in range(world)]
     try:
         accum_ptrs = [t.device_accum() for t in ranks]
+        flag_ptrs = [t.device_peer_flags() for t in ranks]               # each context has its own stream
+        epoch = 0
         for t in ranks:
             t.accum_reset()
         total = np.zeros((h, w, 4), np.float32)
@@ -474,12 +476,15 @@ def test_fused_peer_merge_kernel_single_process(oracle):
                 st, n = sample_range(first, count, r, world)
                 t.render_samples(st, n)
                 parts.append(oracle.accumulate(p, st, n, seed, True))
-            for t in ranks:
-                t.wait()
             spp += count
+            epoch += 1
+            for r, t in enumerate(ranks):                                # rendezvous 0: everybody has rendered
+                t.peer_barrier(flag_ptrs, r, 0, epoch)
             for r, t in enumerate(ranks):
                 s0, sn = slab_range(r, world, w * h)
                 t.peer_merge(accum_ptrs, ranks[0].device_rgba8(), s0, sn, spp, srgb=True)
+            for r, t in enumerate(ranks):                                # rendezvous 1: everybody has merged
+                t.peer_barrier(flag_ptrs, r, 1, epoch)
             for t in ranks:
                 t.wait()
             total = total + ((parts[0] + parts[1]) + parts[2])          # rank order, then onto the running total
