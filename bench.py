@@ -538,10 +538,13 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="override the workload's samples per pixel per step")
     ap.add_argument("--cpu-spp", type=int, default=16, help="spp per step of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--shard", default="samples", choices=["samples", "tiles", "p2p"],
+    ap.add_argument("--shard", default=None, choices=["samples", "tiles", "p2p"],
                     help="multi-GPU partitioning: disjoint sample ranges merged by NCCL reduce (default), interleaved image "
                          "rows, or sample ranges merged by the fused peer-memory kernel (p2p)")
     args = ap.parse_args()
+    if args.shard is None:
+        # strong scaling merges every frame: the fused, pipelined peer-memory merge; otherwise sample ranges + NCCL reduce
+        args.shard = "p2p" if (args.workload == "c5" and max(args.gpus, int(os.environ.get("WORLD_SIZE", "1"))) > 1) else "samples"
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3           # timing rule: W >= 3
     if args.impl == "reference":
