@@ -399,7 +399,9 @@ struct WaveArgs {
     const uint32_t *n_in;     // paths in `in` (depth >= 1)
     uint32_t *n_out;          // compaction counter of `out`
     uint32_t *cursor;         // work cursor of this launch
-    uint32_t n0;              // depth 0: pixels in this context's row shard
+    uint32_t n0;              // depth 0: 32 x (number of 8x4 pixel tiles covering this context's row shard)
+    uint32_t n0_pixels;       // depth 0: pixels in this context's row shard
+    uint32_t tiles_x, rows;   // depth 0: tiles per tile row, rows in the shard
     uint32_t depth, sample;
     int jitter;
     int tail;                 // 1: finish every path of this launch in-kernel (bounce loop, no more queues)
@@ -423,11 +425,20 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
         if (base >= n_in) break;
         const uint32_t i = base + lane;
         bool alive = i < n_in;
+        uint32_t px = 0, py_shard = 0;
+        if (DEPTH0) {
+            // a warp takes one 8x4 pixel tile: primary rays of a warp stay close in BOTH image axes (32x1 strips were
+            // measurably less coherent on the 4K terrain), and the compacted queues inherit the locality
+            const uint32_t tile = i >> 5;
+            px = (tile % w.tiles_x) * 8u + (lane & 7u);
+            py_shard = (tile / w.tiles_x) * 4u + (lane >> 3);
+            alive = alive && px < k.width && py_shard < w.rows;
+        }
         uint32_t pix = 0;
         float ox = 0, oy = 0, oz = 0, dx = 0, dy = 0, dz = 1, tr = 1, tg = 1, tb = 1, uvx = 0, uvy = 0;
         if (alive) {
             if (DEPTH0) {
-                const uint32_t x = i % k.width, yy = i / k.width;
+                const uint32_t x = px, yy = py_shard;
                 const uint32_t y = k.row_offset + yy * k.row_stride;
                 pix = y * k.width + x;
                 float fx = (float)x, fy = (float)y;
@@ -545,7 +556,7 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
             atomicAdd(&w.stats->rays, v[2]);
             atomicAdd(&w.stats->scatters, v[3]);
             atomicMax(&w.stats->max_stack, (unsigned long long)ms);
-            if (DEPTH0 && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&w.stats->paths, (unsigned long long)w.n0);
+            if (DEPTH0 && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&w.stats->paths, (unsigned long long)w.n0_pixels);
         }
     }
 }
@@ -678,8 +689,10 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
                               cudaStream_t s, uint64_t *launches)
 {
     const uint32_t rows = k.row_offset < k.height ? (k.height - k.row_offset + k.row_stride - 1u) / k.row_stride : 0u;
-    const uint32_t n0 = rows * k.width;
-    if (n0 == 0) return cudaSuccess;
+    const uint32_t n0_pixels = rows * k.width;
+    if (n0_pixels == 0) return cudaSuccess;
+    const uint32_t tiles_x = (k.width + 7u) / 8u, tiles_y = (rows + 3u) / 4u;
+    const uint32_t n0 = tiles_x * tiles_y * 32u;
     const uint32_t depths = k.shade_mode == PTB_SHADE_NORMALS ? 1u : k.max_depth + 1u;
     // bounces >= tail_depth run inside ONE launch (0 disables); PTB200_TAIL_DEPTH overrides for A/B runs
     static const uint32_t tail_depth = [] {
@@ -697,6 +710,9 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
         w.n_out = st->counts + d + 1u;
         w.cursor = st->counts + (k.max_depth + 2u) + d;
         w.n0 = n0;
+        w.n0_pixels = n0_pixels;
+        w.tiles_x = tiles_x;
+        w.rows = rows;
         w.depth = d;
         w.sample = sample;
         w.jitter = jitter ? 1 : 0;
