@@ -251,7 +251,7 @@ def run_b200(args):
     W, H, spp = wl["width"], wl["height"], wl["spp"]
     scene = make_scene(wl)
     n_pix = W * H
-    strong = args.workload == "c5"
+    strong = args.workload in ("c5", "c4")     # c4 (BASELINE configs[3]) is ONE 256-spp 4K frame split over the GPUs
     literal = args.workload == "frame"
     # samples per pixel per STEP over all ranks: c2 scales with the world (weak), c5 is fixed (strong)
     spp_step = spp if (strong or literal) else spp * world
@@ -544,7 +544,12 @@ def main():
     args = ap.parse_args()
     if args.shard is None:
         # strong scaling merges every frame: the fused, pipelined peer-memory merge; otherwise sample ranges + NCCL reduce
-        args.shard = "p2p" if (args.workload == "c5" and max(args.gpus, int(os.environ.get("WORLD_SIZE", "1"))) > 1) else "samples"
+        n = max(args.gpus, int(os.environ.get("WORLD_SIZE", "1")))
+        args.shard = "samples"
+        if n > 1 and args.workload == "c5":
+            args.shard = "p2p"
+        elif n > 1 and args.workload == "c4":
+            args.shard = "tiles"                   # configs[3]: row-interleaved image tiles, bit-identical to one GPU
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3           # timing rule: W >= 3
     if args.impl == "reference":

@@ -141,6 +141,11 @@ int ptb_set_accum_buffer(ptb_context *ctx, void *device_ptr);
  * ptb_accum_reset), so the per-device results merge by a sum == gather of disjoint rows and the
  * merged image is bit-identical to a single-device render.  Default (0,1) = every row. */
 int ptb_set_row_shard(ptb_context *ctx, uint32_t row_offset, uint32_t row_stride);
+/* The same with bands of rows_per_band consecutive rows as the interleaving unit: this context renders the bands
+ * g = row_offset + i*row_stride, band g = rows [g*rows_per_band, (g+1)*rows_per_band) clipped to the image.
+ * The scene path traces primary rays in 8x4 pixel tiles, so bands of a multiple of 4 rows keep a warp's rays
+ * adjacent (single interleaved rows spread a tile over 4*row_stride image rows). rows_per_band = 1 == ptb_set_row_shard. */
+int ptb_set_row_shard_bands(ptb_context *ctx, uint32_t row_offset, uint32_t row_stride, uint32_t rows_per_band);
 /* Override the spp count used by ptb_resolve after an external merge of accum buffers. */
 int ptb_set_accum_spp(ptb_context *ctx, uint32_t spp_total);
 

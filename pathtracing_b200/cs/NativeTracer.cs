@@ -81,7 +81,7 @@ public sealed unsafe class NativeTracer : IDisposable
                                                               float tMax, int mode, int* outPrim, float* outT);
 
     // ---- multi-GPU: row shards, external accumulation buffers, fused merge over NVLink peer memory
-    [DllImport(Lib)] private static extern int ptb_set_row_shard(IntPtr ctx, uint rowOffset, uint rowStride);
+    [DllImport(Lib)] private static extern int ptb_set_row_shard_bands(IntPtr ctx, uint rowOffset, uint rowStride, uint rowsPerBand);
     [DllImport(Lib)] private static extern int ptb_set_accum_buffer(IntPtr ctx, void* devicePtr);
     [DllImport(Lib)] private static extern int ptb_set_accum_spp(IntPtr ctx, uint sppTotal);
     [DllImport(Lib)] private static extern int ptb_accum_clear(IntPtr ctx);
@@ -156,7 +156,8 @@ public sealed unsafe class NativeTracer : IDisposable
             Check(_ctx, ptb_trace_rays(_ctx, (ulong)prim.Length, o, d, tMin, tMax, anyHit ? 1 : 0, pp, anyHit ? null : tt));
     }
 
-    public void SetRowShard(uint rowOffset, uint rowStride) => Check(_ctx, ptb_set_row_shard(_ctx, rowOffset, rowStride));
+    public void SetRowShard(uint rowOffset, uint rowStride, uint rowsPerBand = 1) =>
+        Check(_ctx, ptb_set_row_shard_bands(_ctx, rowOffset, rowStride, rowsPerBand));
     public IntPtr DeviceAccum => (IntPtr)ptb_device_accum(_ctx);
     public IntPtr DeviceImage => (IntPtr)ptb_device_rgba8(_ctx);
     public void ClearPartials() => Check(_ctx, ptb_accum_clear(_ctx));

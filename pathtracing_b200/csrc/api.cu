@@ -168,6 +168,7 @@ int ptb_create(const ptb_config *cfg, ptb_context **out_ctx)
     c->k.height = cfg->height;
     c->k.row_offset = 0;
     c->k.row_stride = 1;
+    c->k.row_block = 1;
     c->k.div_x = cfg->uv_div_x;
     c->k.div_y = cfg->uv_div_y;
     for (int i = 0; i < 3; ++i) {
@@ -407,15 +408,21 @@ int ptb_set_accum_buffer(ptb_context *ctx, void *device_ptr)
     return PTB_OK;
 }
 
-int ptb_set_row_shard(ptb_context *ctx, uint32_t row_offset, uint32_t row_stride)
+int ptb_set_row_shard_bands(ptb_context *ctx, uint32_t row_offset, uint32_t row_stride, uint32_t rows_per_band)
 {
     PTB_ENTER(ctx);
-    if (row_stride == 0 || row_offset >= row_stride)
-        return fail(ctx, PTB_ERR_INVALID, "ptb_set_row_shard: need row_stride >= 1 and row_offset < row_stride (got %u, %u)",
-                    row_offset, row_stride);
+    if (row_stride == 0 || row_offset >= row_stride || rows_per_band == 0)
+        return fail(ctx, PTB_ERR_INVALID, "ptb_set_row_shard: need row_stride >= 1, row_offset < row_stride and rows_per_band >= 1 "
+                    "(got %u, %u, %u)", row_offset, row_stride, rows_per_band);
     ctx->k.row_offset = row_offset;
     ctx->k.row_stride = row_stride;
+    ctx->k.row_block = rows_per_band;
     return PTB_OK;
+}
+
+int ptb_set_row_shard(ptb_context *ctx, uint32_t row_offset, uint32_t row_stride)
+{
+    return ptb_set_row_shard_bands(ctx, row_offset, row_stride, 1u);
 }
 
 int ptb_set_accum_spp(ptb_context *ctx, uint32_t spp_total)

@@ -207,7 +207,7 @@ __global__ void __launch_bounds__(256) csmain_frame_vec4(const FrameK k, uint4 *
                                                          float4 *__restrict__ f32, int4 *__restrict__ hit)
 {
     const uint32_t xq = blockIdx.x * blockDim.x + threadIdx.x;   // quad index along x
-    const uint32_t y = k.row_offset + (blockIdx.y * blockDim.y + threadIdx.y) * k.row_stride;   // row shard (multi-GPU tiles)
+    const uint32_t y = shard_row(k.row_offset, k.row_stride, k.row_block, blockIdx.y * blockDim.y + threadIdx.y);   // row shard (multi-GPU tiles)
     const uint32_t wq = k.width >> 2;
     if (xq >= wq || y >= k.height) return;                       // the guard Test.hlsl:39 lacks
 
@@ -260,7 +260,7 @@ __global__ void __launch_bounds__(256) csmain_frame_scalar(const FrameK k, uint3
                                                            float4 *__restrict__ f32, int32_t *__restrict__ hit)
 {
     const uint32_t x = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t y = k.row_offset + (blockIdx.y * blockDim.y + threadIdx.y) * k.row_stride;   // row shard (multi-GPU tiles)
+    const uint32_t y = shard_row(k.row_offset, k.row_stride, k.row_block, blockIdx.y * blockDim.y + threadIdx.y);   // row shard (multi-GPU tiles)
     if (x >= k.width || y >= k.height) return;
     float r, g, b;
     const bool h = csmain_shade<MODE>(k, screen_uv<MODE>(__uint2float_rn(x), k.div_x, k.inv_div_x),
@@ -271,10 +271,10 @@ __global__ void __launch_bounds__(256) csmain_frame_scalar(const FrameK k, uint3
     if (hit) hit[i] = h ? 0 : -1;
 }
 
-// rows this context renders: y = row_offset + i*row_stride < height
+// rows this context renders (ptb_internal.h shard_row)
 static uint32_t shard_rows(const FrameK &k)
 {
-    return k.row_offset >= k.height ? 0u : (k.height - k.row_offset + k.row_stride - 1) / k.row_stride;
+    return shard_row_count(k.height, k.row_offset, k.row_stride, k.row_block);
 }
 
 static int pick_mode(const FrameK &k) { return k.fast ? (k.on_axis ? MODE_FAST_ON_AXIS : MODE_FAST) : MODE_GENERIC; }
@@ -316,7 +316,7 @@ __global__ void __launch_bounds__(256) csmain_accumulate(const FrameK k, float4 
                                                          uint32_t first_sample, uint32_t n_samples, uint32_t seed)
 {
     const uint32_t x = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t y = k.row_offset + (blockIdx.y * blockDim.y + threadIdx.y) * k.row_stride;   // row shard (multi-GPU tiles)
+    const uint32_t y = shard_row(k.row_offset, k.row_stride, k.row_block, blockIdx.y * blockDim.y + threadIdx.y);   // row shard (multi-GPU tiles)
     if (x >= k.width || y >= k.height) return;
     const uint32_t pix = y * k.width + x;
     const float fx = __uint2float_rn(x), fy = __uint2float_rn(y);

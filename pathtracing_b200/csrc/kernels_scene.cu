@@ -439,7 +439,7 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
         if (alive) {
             if (DEPTH0) {
                 const uint32_t x = px, yy = py_shard;
-                const uint32_t y = k.row_offset + yy * k.row_stride;
+                const uint32_t y = shard_row(k.row_offset, k.row_stride, k.row_block, yy);
                 pix = y * k.width + x;
                 float fx = (float)x, fy = (float)y;
                 if (w.jitter) {
@@ -688,7 +688,7 @@ cudaError_t launch_pack_tris(const float *verts9, const uint32_t *mat_in, const 
 cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, int32_t *hit_ids, uint32_t sample, bool jitter,
                               cudaStream_t s, uint64_t *launches)
 {
-    const uint32_t rows = k.row_offset < k.height ? (k.height - k.row_offset + k.row_stride - 1u) / k.row_stride : 0u;
+    const uint32_t rows = shard_row_count(k.height, k.row_offset, k.row_stride, k.row_block);
     const uint32_t n0_pixels = rows * k.width;
     if (n0_pixels == 0) return cudaSuccess;
     const uint32_t tiles_x = (k.width + 7u) / 8u, tiles_y = (rows + 3u) / 4u;

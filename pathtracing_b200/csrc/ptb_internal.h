@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 
 #include "../../include/ptb200.h"
+#include "row_shard.h"
 
 struct ptb_context;
 
@@ -18,7 +19,8 @@ namespace ptb {
 // (prepare_terms kernel, same *_rn intrinsics as the per-pixel code) when the context is created.
 struct FrameK {
     uint32_t width, height;
-    uint32_t row_offset, row_stride;   // this context renders rows row_offset + i*row_stride (default 0,1 = all)
+    uint32_t row_offset, row_stride;   // this context renders row BANDS row_offset + i*row_stride (default 0,1 = all)
+    uint32_t row_block;                // rows per band (default 1: single interleaved rows)
     float div_x, div_y;
     float cam[3];
     float centre[3];

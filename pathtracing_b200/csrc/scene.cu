@@ -67,6 +67,7 @@ ptb::SceneK make_k(const ptb_context *ctx, const SceneState *st)
     k.height = ctx->cfg.height;
     k.row_offset = ctx->k.row_offset;
     k.row_stride = ctx->k.row_stride;
+    k.row_block = ctx->k.row_block;
     k.div_x = ctx->cfg.uv_div_x;
     k.div_y = ctx->cfg.uv_div_y;
     for (int i = 0; i < 3; ++i) {
@@ -99,8 +100,7 @@ ptb::SceneK make_k(const ptb_context *ctx, const SceneState *st)
 
 uint32_t wave_paths(const ptb_context *ctx)
 {
-    const uint32_t h = ctx->cfg.height, off = ctx->k.row_offset, stride = ctx->k.row_stride;
-    return off < h ? ((h - off + stride - 1u) / stride) * ctx->cfg.width : 0u;
+    return ptb::shard_row_count(ctx->cfg.height, ctx->k.row_offset, ctx->k.row_stride, ctx->k.row_block) * ctx->cfg.width;
 }
 
 int check_error_flag(ptb_context *ctx, SceneState *st)

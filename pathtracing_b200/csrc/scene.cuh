@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 
 #include "../../include/ptb200.h"
+#include "row_shard.h"
 
 namespace ptb {
 
@@ -44,7 +45,7 @@ struct DeviceBvh {
 // Launch-uniform parameters of the scene kernels (kernel argument -> constant bank).
 struct SceneK {
     uint32_t width, height;
-    uint32_t row_offset, row_stride;
+    uint32_t row_offset, row_stride, row_block;
     float div_x, div_y;
     float cam_o[3], cam_u[3], cam_v[3], cam_w[3];
     float sky_h[3], sky_z[3];

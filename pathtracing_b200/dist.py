@@ -45,16 +45,24 @@ def slab_range(rank: int, world: int, n_pixels: int) -> Tuple[int, int]:
     return sample_range(0, n_pixels, rank, world)
 
 
-def row_shard(rank: int, world: int) -> Tuple[int, int]:
-    """Interleaved rows: (row_offset, row_stride) for ptb_set_row_shard."""
-    return rank, world
+BAND_ROWS = 4      # rows per interleaved band: the scene path traces primary rays in 8x4 pixel tiles
+
+
+def row_shard(rank: int, world: int, band_rows: int = 1) -> Tuple[int, int, int]:
+    """Interleaved row bands: (row_offset, row_stride, rows_per_band) for ptb_set_row_shard_bands."""
+    return rank, world, band_rows
+
+
+def shard_rows(row_offset: int, row_stride: int, rows_per_band: int, height: int):
+    """Image rows of a row shard, ascending (the host-side statement of csrc/ptb_internal.h shard_row)."""
+    return [y for y in range(height) if (y // rows_per_band) % row_stride == row_offset]
 
 
 class LocalEngine(Protocol):
     width: int
     height: int
 
-    def set_row_shard(self, row_offset: int, row_stride: int) -> None: ...
+    def set_row_shard(self, row_offset: int, row_stride: int, rows_per_band: int = 1) -> None: ...
     def accum_reset(self) -> None: ...
     def render_samples(self, first_sample: int, n_samples: int) -> None: ...
     def accum_tensor(self) -> torch.Tensor: ...          # (H, W, 4) float32, the live accumulation buffer
@@ -87,8 +95,8 @@ class GpuEngine:
             self.tracer.upload_scene(scene, count_stats=count_stats)
         self._image = None
 
-    def set_row_shard(self, row_offset, row_stride):
-        self.tracer.set_row_shard(row_offset, row_stride)
+    def set_row_shard(self, row_offset, row_stride, rows_per_band=1):
+        self.tracer.set_row_shard(row_offset, row_stride, rows_per_band)
 
     def _wrap(self, ptr, shape, typestr):
         class _Wrap:
@@ -195,7 +203,7 @@ class GpuEngine:
 class ShardedRenderer:
     """Drives one LocalEngine per rank; `mode` is "samples" or "tiles"."""
 
-    def __init__(self, engine: LocalEngine, mode: str = "samples", group=None, dst: int = 0):
+    def __init__(self, engine: LocalEngine, mode: str = "samples", group=None, dst: int = 0, band_rows: int = BAND_ROWS):
         if mode not in ("samples", "tiles", "p2p"):
             raise ValueError(f"unknown sharding mode {mode!r}")
         self.engine = engine
@@ -205,7 +213,7 @@ class ShardedRenderer:
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.spp_total = 0                 # samples per pixel in the merged image
         if mode == "tiles":
-            engine.set_row_shard(*row_shard(self.rank, self.world))
+            engine.set_row_shard(*row_shard(self.rank, self.world, band_rows))
         else:
             engine.set_row_shard(0, 1)
         engine.accum_reset()

@@ -127,8 +127,9 @@ class NativeTracer:
     def set_accum_spp(self, spp: int) -> None:
         self._ck(self._lib.ptb_set_accum_spp(self._ctx, spp))
 
-    def set_row_shard(self, row_offset: int, row_stride: int) -> None:
-        self._ck(self._lib.ptb_set_row_shard(self._ctx, row_offset, row_stride))
+    def set_row_shard(self, row_offset: int, row_stride: int, rows_per_band: int = 1) -> None:
+        """Render only the row bands row_offset + i*row_stride (bands of rows_per_band rows; 1 = single rows)."""
+        self._ck(self._lib.ptb_set_row_shard_bands(self._ctx, row_offset, row_stride, rows_per_band))
 
     def read_accum(self, out: Optional[np.ndarray] = None) -> np.ndarray:
         if out is None:

@@ -15,7 +15,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-from pathtracing_b200.dist import ShardedRenderer, row_shard, sample_range, slab_range  # noqa: E402
+from pathtracing_b200.dist import ShardedRenderer, row_shard, sample_range, shard_rows, slab_range  # noqa: E402
 
 W, H, SEED = 96, 54, 5
 
@@ -29,18 +29,17 @@ class OracleEngine:
         self.p = O.frame_params(width, height)
         self.acc = torch.zeros((height, width, 4), dtype=torch.float32)
         self.img = torch.zeros((height, width), dtype=torch.int32)
-        self.rows = (0, 1)
+        self.rows = list(range(height))
 
-    def set_row_shard(self, off, stride):
-        self.rows = (off, stride)
+    def set_row_shard(self, off, stride, band=1):
+        self.rows = shard_rows(off, stride, band, self.height)
 
     def accum_reset(self):
         self.acc.zero_()
 
     def render_samples(self, first, n):
         part = self.O.accumulate(self.p, first, n, self.seed, True)          # whole frame, then keep own rows
-        off, stride = self.rows
-        self.acc[off::stride] += torch.from_numpy(part)[off::stride]
+        self.acc[self.rows] += torch.from_numpy(part)[self.rows]
 
     def accum_tensor(self):
         return self.acc
@@ -71,8 +70,7 @@ class OracleSceneEngine(OracleEngine):
     def render_samples(self, first, n):
         # the scene path adds every sample straight into the accumulator (no per-launch partial sum)
         self.so.accumulate(first, n, seed=self.seed, jitter=True, accum=self.full)
-        off, stride = self.rows
-        self.acc[off::stride] = torch.from_numpy(self.full)[off::stride]
+        self.acc[self.rows] = torch.from_numpy(self.full)[self.rows]
 
 
 def _free_port():
@@ -129,7 +127,12 @@ def test_sample_range_partition():
         covered = [s for st, n in spans for s in range(st, st + n)]
         assert covered == list(range(first, first + count))          # disjoint, ordered, complete
         assert max(n for _, n in spans) - min(n for _, n in spans) <= 1
-    assert [row_shard(r, 4) for r in range(4)] == [(0, 4), (1, 4), (2, 4), (3, 4)]
+    assert [row_shard(r, 4) for r in range(4)] == [(0, 4, 1), (1, 4, 1), (2, 4, 1), (3, 4, 1)]
+    # row bands: every image row belongs to exactly one rank, bands of 4 rows interleaved, ragged last band
+    for h, world, band in [(54, 3, 4), (2160, 8, 4), (7, 2, 4), (9, 4, 1), (5, 8, 4)]:
+        rows = [shard_rows(*row_shard(r, world, band), h) for r in range(world)]
+        assert sorted(y for rr in rows for y in rr) == list(range(h))
+        assert all((y // band) % world == r for r, rr in enumerate(rows) for y in rr)
     # pixel slabs of the fused peer merge: contiguous, disjoint, complete
     for n, world in [(3840 * 2160, 8), (1920 * 1080, 3), (5, 8)]:
         slabs = [slab_range(r, world, n) for r in range(world)]

@@ -392,9 +392,9 @@ def test_async_readback_is_ordered_and_matches_sync(oracle):
 
 
 # ---- multi-GPU partitioning emulated on one device: one context per "rank" -------------------------
-@pytest.mark.parametrize("world", [2, 3, 8])
-def test_row_shards_merge_to_the_single_device_image(world):
-    w, h, spp, seed = 640, 360, 6, 4
+@pytest.mark.parametrize("world,band", [(2, 1), (3, 1), (8, 1), (2, 4), (3, 4), (8, 4), (8, 16), (7, 5)])
+def test_row_shards_merge_to_the_single_device_image(world, band):
+    w, h, spp, seed = 640, 358, 6, 4            # 358 rows: the last band is ragged for bands of 4, 5 and 16
     with NativeTracer(w, h, seed=seed, keep_f32=True) as t:
         t.compute_frame()
         full_frame = t.read_rgba8()
@@ -407,10 +407,11 @@ def test_row_shards_merge_to_the_single_device_image(world):
     merged_acc = np.zeros((h, w, 4), np.float32)
     for rank in range(world):
         with NativeTracer(w, h, seed=seed) as t:
-            t.set_row_shard(rank, world)
+            t.set_row_shard(rank, world, band)
             t.compute_frame()
             fr = t.read_rgba8()
-            assert not fr[(np.arange(h) % world) != rank].any()          # foreign rows untouched (zero)
+            assert not fr[(np.arange(h) // band % world) != rank].any()  # foreign rows untouched (zero)
+            assert fr[(np.arange(h) // band % world) == rank, :, 3].all()  # own rows all written (alpha 255)
             merged_frame += fr.view(np.uint32).reshape(h, w)
             t.render_samples(0, spp)
             merged_acc += t.read_accum()                                 # disjoint rows: sum == gather
@@ -423,9 +424,9 @@ def test_row_shards_merge_to_the_single_device_image(world):
 
 def test_row_shard_argument_errors():
     with NativeTracer(64, 36) as t:
-        for off, stride in ((0, 0), (2, 2), (5, 3)):
+        for off, stride, band in ((0, 0, 1), (2, 2, 1), (5, 3, 1), (0, 2, 0)):
             with pytest.raises(PtbError) as e:
-                t.set_row_shard(off, stride)
+                t.set_row_shard(off, stride, band)
             assert e.value.status == _lib.PTB_ERR_INVALID
         t.set_row_shard(40, 64)          # offset beyond the image: nothing to render, not an error
         t.compute_frame()

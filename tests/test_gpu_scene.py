@@ -265,7 +265,7 @@ def test_config4_full_size_million_triangles_4k(S):
         total = np.zeros_like(full)
         for r in range(8):
             t.accum_reset()
-            t.set_row_shard(r, 8)
+            t.set_row_shard(r, 8, 4)                       # bands of 4 rows, as bench.py --workload c4 --gpus 8 shards
             t.render_samples(0, 1)
             total += t.read_accum()
         assert_images_equal(total, full, "c4 8-way row-sharded merge")
@@ -307,8 +307,10 @@ def test_stats_build_gives_identical_images_and_sane_counters(S):
         assert t.scene_stats()["rays"] == 0
 
 
-def test_row_sharded_scene_render_merges_to_the_full_frame(S):
-    """n8 partitioning A on the scene path: interleaved row shards sum to the single-context result."""
+@pytest.mark.parametrize("band", [1, 4, 8])
+def test_row_sharded_scene_render_merges_to_the_full_frame(S, band):
+    """n8 partitioning A on the scene path: interleaved row shards (single rows / bands of rows, ragged last band)
+    sum to the single-context result."""
     w, h = 160, 90
     sc = scenes.mixed_small(width=w, height=h)
     with NativeTracer(w, h, seed=2, max_depth=5) as t:
@@ -319,10 +321,11 @@ def test_row_sharded_scene_render_merges_to_the_full_frame(S):
     for r in range(3):
         with NativeTracer(w, h, seed=2, max_depth=5) as t:
             t.upload_scene(sc)
-            t.set_row_shard(r, 3)
+            t.set_row_shard(r, 3, band)
             t.render_samples(0, 3)
             part = t.read_accum()
-            assert np.all(part[np.arange(h) % 3 != r] == 0)
+            assert np.all(part[np.arange(h) // band % 3 != r] == 0)
+            assert np.all(part[np.arange(h) // band % 3 == r, :, 3] == 3)
             total += part
     assert_images_equal(total, full, "row-sharded merge")
 
