@@ -148,6 +148,7 @@ SIGNATURES = {
     "ptb_set_accum_buffer": (C.c_int, [_CTX, C.c_void_p]),
     "ptb_set_accum_spp": (C.c_int, [_CTX, C.c_uint32]),
     "ptb_set_row_shard": (C.c_int, [_CTX, C.c_uint32, C.c_uint32]),
+    "ptb_scene_set_wave_samples": (C.c_int, [_CTX, C.c_uint32]),
     "ptb_set_row_shard_bands": (C.c_int, [_CTX, C.c_uint32, C.c_uint32, C.c_uint32]),
     "ptb_upload_scene": (C.c_int, [_CTX, _P(SceneDesc)]),
     "ptb_clear_scene": (C.c_int, [_CTX]),

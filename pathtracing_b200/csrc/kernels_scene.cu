@@ -402,7 +402,13 @@ struct WaveArgs {
     uint32_t n0;              // depth 0: 32 x (number of 8x4 pixel tiles covering this context's row shard)
     uint32_t n0_pixels;       // depth 0: pixels in this context's row shard
     uint32_t tiles_x, rows;   // depth 0: tiles per tile row, rows in the shard
-    uint32_t depth, sample;
+    uint32_t depth, sample;   // sample index of the wave's first sample
+    // samples of every pixel traced by this wave (>= 1).  A path's id word is its pixel's index within the row shard
+    // (shard row * width + x); batch > 1: | local sample << PIX_BITS, and its radiance goes to
+    // slices[local sample][shard index] (one plain store per path, summed in sample order by reduce_slices_kernel —
+    // the same additions in the same order as one wave per sample)
+    uint32_t batch, tiles;
+    float4 *slices;
     int jitter;
     int tail;                 // 1: finish every path of this launch in-kernel (bounce loop, no more queues)
     float4 *accum;
@@ -410,6 +416,8 @@ struct WaveArgs {
     SceneStatsDev *stats;
     uint32_t *error_flag;
 };
+
+constexpr uint32_t PIX_BITS = 26u, PIX_MASK = (1u << PIX_BITS) - 1u;
 
 template <bool DEPTH0, bool STATS>
 __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(const SceneK k, const WaveArgs w)
@@ -425,25 +433,30 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
         if (base >= n_in) break;
         const uint32_t i = base + lane;
         bool alive = i < n_in;
-        uint32_t px = 0, py_shard = 0;
+        uint32_t px = 0, py_shard = 0, s_local = 0;
         if (DEPTH0) {
             // a warp takes one 8x4 pixel tile: primary rays of a warp stay close in BOTH image axes (32x1 strips were
             // measurably less coherent on the 4K terrain), and the compacted queues inherit the locality
-            const uint32_t tile = i >> 5;
+            uint32_t tile = i >> 5;
+            if (w.batch > 1u) {                         // launch-uniform
+                s_local = tile / w.tiles;
+                tile -= s_local * w.tiles;
+            }
             px = (tile % w.tiles_x) * 8u + (lane & 7u);
             py_shard = (tile / w.tiles_x) * 4u + (lane >> 3);
             alive = alive && px < k.width && py_shard < w.rows;
         }
-        uint32_t pix = 0;
+        uint32_t pix = 0, loc = 0;
         float ox = 0, oy = 0, oz = 0, dx = 0, dy = 0, dz = 1, tr = 1, tg = 1, tb = 1, uvx = 0, uvy = 0;
         if (alive) {
             if (DEPTH0) {
                 const uint32_t x = px, yy = py_shard;
                 const uint32_t y = shard_row(k.row_offset, k.row_stride, k.row_block, yy);
                 pix = y * k.width + x;
+                loc = yy * k.width + x;
                 float fx = (float)x, fy = (float)y;
                 if (w.jitter) {
-                    const U3 v = pcg3d(pix, w.sample, k.seed);
+                    const U3 v = pcg3d(pix, w.sample + s_local, k.seed);
                     fx = fx + bits_to_unit(v.x);
                     fy = fy + bits_to_unit(v.y);
                 }
@@ -459,7 +472,14 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
                 // push the hierarchy out of L2
                 const float4 s0 = __ldcs(&w.in.s0[i]), s1 = __ldcs(&w.in.s1[i]);
                 const float2 s2 = __ldcs(&w.in.s2[i]);
-                ox = s0.x; oy = s0.y; oz = s0.z; pix = __float_as_uint(s0.w);
+                ox = s0.x; oy = s0.y; oz = s0.z;
+                loc = __float_as_uint(s0.w);
+                if (w.batch > 1u) {                     // launch-uniform
+                    s_local = loc >> PIX_BITS;
+                    loc &= PIX_MASK;
+                }
+                const uint32_t yy = loc / k.width;
+                pix = shard_row(k.row_offset, k.row_stride, k.row_block, yy) * k.width + (loc - yy * k.width);
                 dx = s1.x; dy = s1.y; dz = s1.z; tr = s1.w; tg = s2.x; tb = s2.y;
             }
         }
@@ -498,7 +518,7 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
                 alive = false;                      // bounce budget spent: contributes nothing
             } else {
                 const ptb_material m = k.materials[mat < k.n_materials ? mat : 0u];
-                const U3 v = pcg3d(pix, w.sample, k.seed + (depth + 1u) * 0x9E3779B9u);
+                const U3 v = pcg3d(pix, w.sample + s_local, k.seed + (depth + 1u) * 0x9E3779B9u);
                 if (STATS) ++n_scatter;
                 if (scatter(m, dx, dy, dz, nx, ny, nz, bits_to_unit(v.x), bits_to_unit(v.y), bits_to_unit(v.z))) {
                     tr = tr * m.albedo[0]; tg = tg * m.albedo[1]; tb = tb * m.albedo[2];
@@ -507,7 +527,10 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
                     alive = false;
                 }
             }
-            if (DEPTH0) {
+            if (w.slices) {                             // launch-uniform: batched wave
+                // every path stores its slot at depth 0 (zero radiance while it is still alive) and once more when it ends
+                if (DEPTH0 || add) __stcs(&w.slices[(size_t)s_local * w.n0_pixels + loc], make_float4(cr, cg, cb, 1.0f));
+            } else if (DEPTH0) {
                 float4 acc = w.accum[pix];
                 acc.x = acc.x + cr; acc.y = acc.y + cg; acc.z = acc.z + cb; acc.w = acc.w + 1.0f;
                 w.accum[pix] = acc;
@@ -535,7 +558,7 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
             obase = __shfl_sync(FULL, obase, 0);
             if (alive) {
                 const uint32_t o = obase + (uint32_t)__popc(live & ((1u << lane) - 1u));
-                __stcs(&w.out.s0[o], make_float4(ox, oy, oz, __uint_as_float(pix)));
+                __stcs(&w.out.s0[o], make_float4(ox, oy, oz, __uint_as_float(loc | (s_local << PIX_BITS))));
                 __stcs(&w.out.s1[o], make_float4(dx, dy, dz, tr));
                 __stcs(&w.out.s2[o], make_float2(tg, tb));
             }
@@ -556,7 +579,7 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
             atomicAdd(&w.stats->rays, v[2]);
             atomicAdd(&w.stats->scatters, v[3]);
             atomicMax(&w.stats->max_stack, (unsigned long long)ms);
-            if (DEPTH0 && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&w.stats->paths, (unsigned long long)w.n0_pixels);
+            if (DEPTH0 && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&w.stats->paths, (unsigned long long)w.n0_pixels * w.batch);
         }
     }
 }
@@ -601,6 +624,24 @@ __global__ void __launch_bounds__(256) pack_tris_kernel(const float *__restrict_
     out[3 * (size_t)i + 0] = make_float4(p[0], p[1], p[2], __int_as_float((int)(id_base + src)));
     out[3 * (size_t)i + 1] = make_float4(p[3] - p[0], p[4] - p[1], p[5] - p[2], __int_as_float((int)mat[src]));
     out[3 * (size_t)i + 2] = make_float4(p[6] - p[0], p[7] - p[1], p[8] - p[2], 0.0f);
+}
+
+// Batched waves: accum[pixel] += slices[0][pixel], then slices[1][pixel], ... in sample order — the additions one wave
+// per sample performs (depth 0 adds (0,0,0,1) or the radiance, a later bounce adds the radiance: x + 0 first, then + c).
+__global__ void __launch_bounds__(256) reduce_slices_kernel(const SceneK k, float4 *accum, const float4 *__restrict__ slices,
+                                                            uint32_t batch, uint32_t n_shard)
+{
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n_shard; j += gridDim.x * blockDim.x) {
+        const uint32_t yy = j / k.width, x = j - yy * k.width;
+        const uint32_t pix = shard_row(k.row_offset, k.row_stride, k.row_block, yy) * k.width + x;
+        float4 acc = accum[pix];
+        for (uint32_t s = 0; s < batch; ++s) {
+            const float4 c = __ldcs(&slices[(size_t)s * n_shard + j]);
+            acc.x = (acc.x + 0.0f) + c.x; acc.y = (acc.y + 0.0f) + c.y; acc.z = (acc.z + 0.0f) + c.z;
+            acc.w = acc.w + 1.0f;
+        }
+        accum[pix] = acc;
+    }
 }
 
 __global__ void __launch_bounds__(256) frame_finish_kernel(const float4 *__restrict__ accum, float4 *f32_out, uint32_t *rgba8_out,
@@ -685,14 +726,14 @@ cudaError_t launch_pack_tris(const float *verts9, const uint32_t *mat_in, const 
     return cudaGetLastError();
 }
 
-cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, int32_t *hit_ids, uint32_t sample, bool jitter,
-                              cudaStream_t s, uint64_t *launches)
+cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, int32_t *hit_ids, uint32_t sample, uint32_t batch,
+                              bool jitter, cudaStream_t s, uint64_t *launches)
 {
     const uint32_t rows = shard_row_count(k.height, k.row_offset, k.row_stride, k.row_block);
     const uint32_t n0_pixels = rows * k.width;
     if (n0_pixels == 0) return cudaSuccess;
     const uint32_t tiles_x = (k.width + 7u) / 8u, tiles_y = (rows + 3u) / 4u;
-    const uint32_t n0 = tiles_x * tiles_y * 32u;
+    const uint32_t n0 = tiles_x * tiles_y * 32u * batch;
     const uint32_t depths = k.shade_mode == PTB_SHADE_NORMALS ? 1u : k.max_depth + 1u;
     // bounces >= tail_depth run inside ONE launch (0 disables); PTB200_TAIL_DEPTH overrides for A/B runs
     static const uint32_t tail_depth = [] {
@@ -715,6 +756,9 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
         w.rows = rows;
         w.depth = d;
         w.sample = sample;
+        w.batch = batch;
+        w.tiles = tiles_x * tiles_y;
+        w.slices = batch > 1u ? st->slices : nullptr;
         w.jitter = jitter ? 1 : 0;
         w.tail = (tail_depth > 0 && d >= tail_depth && d + 1u < depths) ? 1 : 0;
         w.accum = accum;
@@ -730,6 +774,11 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
         }
         if (launches) ++*launches;
         if (w.tail) break;
+    }
+    if (batch > 1u) {
+        const unsigned blocks = min((n0_pixels + 255u) / 256u, 148u * 8u);
+        reduce_slices_kernel<<<blocks, 256, 0, s>>>(k, accum, st->slices, batch, n0_pixels);
+        if (launches) ++*launches;
     }
     return cudaGetLastError();
 }

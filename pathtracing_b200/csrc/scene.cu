@@ -4,6 +4,7 @@
 // there is no upload, hierarchy or material code to stand behind — SURVEY.md §0).
 // Only argument checking, ownership and stream plumbing live here; the work is in
 // scene_build.cu (GPU LBVH) and kernels_scene.cu (wavefront path tracer).
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -46,10 +47,14 @@ void free_state(SceneState *st)
     free_queue(st->q[1]);
     cudaFree(st->counts);
     cudaFree(st->frame_accum);
+    cudaFree(st->slices);
     cudaFree(st->stats);
     cudaFree(st->error_flag);
     delete st;
 }
+
+constexpr uint32_t MAX_WAVE_SAMPLES = 64u;                  // 6 bits of the path id word
+constexpr uint32_t WAVE_PATHS_TARGET = 32u << 20;            // paths per wave the queues are sized for (56 B per path)
 
 // Lockstep primitive tests when the hierarchy fits the SM's L1 (measured: profiles/r01_notes.md).
 // PTB200_LOCKSTEP=0/1 forces the choice (A/B experiments).
@@ -134,7 +139,7 @@ int scene_compute_frame(ptb_context *ctx)
     if (ctx->buf.hit) SC_CUDA(ctx, cudaMemsetAsync(ctx->buf.hit, 0xFF, n * sizeof(int32_t), ctx->stream));
     const SceneK k = make_k(ctx, st);
     st->last_n0 = wave_paths(ctx);
-    SC_CUDA(ctx, launch_scene_wave(k, st, st->frame_accum, ctx->buf.hit, 0u, false, ctx->stream, &ctx->launches));
+    SC_CUDA(ctx, launch_scene_wave(k, st, st->frame_accum, ctx->buf.hit, 0u, 1u, false, ctx->stream, &ctx->launches));
     SC_CUDA(ctx, launch_frame_finish(st->frame_accum, ctx->buf.f32, ctx->buf.rgba8, (uint32_t)n, ctx->stream));
     ctx->launches += 1;
     return PTB_OK;
@@ -144,9 +149,22 @@ int scene_render_samples(ptb_context *ctx, uint32_t first_sample, uint32_t n_sam
 {
     SceneState *st = state(ctx);
     const SceneK k = make_k(ctx, st);
-    st->last_n0 = wave_paths(ctx);
-    for (uint32_t s = 0; s < n_samples; ++s)
-        SC_CUDA(ctx, launch_scene_wave(k, st, ctx->buf.accum, nullptr, first_sample + s, jitter != 0, ctx->stream, &ctx->launches));
+    // One wave traces as many samples of every pixel of the shard as the path queues hold: small frames and 1/N row shards
+    // would otherwise run waves too small to fill the GPU at the deep bounces (profiles/r01_notes.md).  Same results bit
+    // for bit: the samples land in per-sample slices that are added to the accumulator in sample order.
+    const uint32_t shard = wave_paths(ctx);
+    if (shard == 0 || n_samples == 0) return PTB_OK;
+    uint32_t per_wave = std::min<uint32_t>(MAX_WAVE_SAMPLES, std::max<uint32_t>(1u, st->q_cap / shard));
+    if (st->wave_samples) per_wave = std::min(per_wave, st->wave_samples);
+    if (shard > (1u << 26)) per_wave = 1u;              // a batched wave keeps 26 bits of the path id word for the pixel
+    per_wave = std::min(per_wave, n_samples);
+    if (per_wave > 1u && !st->slices)                   // one radiance slot per path of a full wave
+        SC_CUDA(ctx, cudaMalloc(&st->slices, (size_t)st->q_cap * sizeof(float4)));
+    for (uint32_t s = 0; s < n_samples; s += per_wave) {
+        const uint32_t batch = std::min(per_wave, n_samples - s);
+        st->last_n0 = shard * batch;
+        SC_CUDA(ctx, launch_scene_wave(k, st, ctx->buf.accum, nullptr, first_sample + s, batch, jitter != 0, ctx->stream, &ctx->launches));
+    }
     return PTB_OK;
 }
 
@@ -272,7 +290,16 @@ int ptb_upload_scene(ptb_context *ctx, const ptb_scene_desc *d)
     ctx->launches += 12;     // bounds, Morton, sort passes, Karras, refit, survive, scan, emit, pack (per class; lower bound)
 
     // wavefront state
-    st->q_cap = ctx->cfg.width * ctx->cfg.height;
+    {
+        // wave capacity: at least one sample of every pixel; small frames get room for several samples per wave
+        // (PTB200_WAVE_PATHS overrides the target for A/B runs)
+        static const uint64_t target = [] {
+            const char *e = std::getenv("PTB200_WAVE_PATHS");
+            return e ? (uint64_t)std::strtoull(e, nullptr, 10) : (uint64_t)WAVE_PATHS_TARGET;
+        }();
+        const uint64_t n_pix = (uint64_t)ctx->cfg.width * ctx->cfg.height;
+        st->q_cap = (uint32_t)std::max<uint64_t>(n_pix, std::min<uint64_t>(target, n_pix * MAX_WAVE_SAMPLES));
+    }
     for (int i = 0; i < 2; ++i) {
         UP(cudaMalloc(&st->q[i].s0, sizeof(float4) * st->q_cap));
         UP(cudaMalloc(&st->q[i].s1, sizeof(float4) * st->q_cap));
@@ -335,6 +362,14 @@ int ptb_scene_stats_reset(ptb_context *ctx)
     if (!ctx->scene) return ptb::fail_msg(ctx, PTB_ERR_STATE, "ptb_scene_stats_reset: no scene resident");
     SC_CUDA(ctx, cudaSetDevice(ctx->cfg.device));
     SC_CUDA(ctx, cudaMemsetAsync(state(ctx)->stats, 0, sizeof(ptb::SceneStatsDev), ctx->stream));
+    return PTB_OK;
+}
+
+int ptb_scene_set_wave_samples(ptb_context *ctx, uint32_t samples_per_wave)
+{
+    if (!ctx) return ptb::fail_msg(nullptr, PTB_ERR_INVALID, "ptb_scene_set_wave_samples: ctx is NULL");
+    if (!ctx->scene) return ptb::fail_msg(ctx, PTB_ERR_STATE, "ptb_scene_set_wave_samples: no scene resident");
+    state(ctx)->wave_samples = samples_per_wave;
     return PTB_OK;
 }
 

@@ -69,7 +69,7 @@ struct SceneK {
 };
 
 // Wavefront path state, structure of arrays, ping-pong (in/out) per bounce:
-//   s0 = (o.x, o.y, o.z, pixel index bits), s1 = (d.x, d.y, d.z, thr.r), s2 = (thr.g, thr.b)
+//   s0 = (o.x, o.y, o.z, shard-local pixel index | sample of the wave << 26), s1 = (d.x, d.y, d.z, thr.r), s2 = (thr.g, thr.b)
 struct PathQueue {
     float4 *s0 = nullptr;
     float4 *s1 = nullptr;
@@ -89,7 +89,9 @@ struct SceneState {
     float4 *tri = nullptr;
     ptb_material *materials = nullptr;
     PathQueue q[2];
-    uint32_t q_cap = 0;             // paths per queue
+    uint32_t q_cap = 0;             // paths per queue = capacity of one wave
+    float4 *slices = nullptr;       // batched waves: q_cap radiance slots, [sample of the wave][pixel of the shard]
+    uint32_t wave_samples = 0;      // samples per wave: 0 = as many as fit the queues (ptb_scene_set_wave_samples)
     uint32_t *counts = nullptr;     // max_depth + 2 queue counters
     uint32_t counts_len = 0;
     float4 *frame_accum = nullptr;  // scratch accumulation for ptb_compute_frame
@@ -111,8 +113,9 @@ cudaError_t launch_pack_spheres(const float4 *sph_in, const uint32_t *mat_in, co
                                 float4 *sph_out, uint2 *meta_out, cudaStream_t s);
 cudaError_t launch_pack_tris(const float *verts9, const uint32_t *mat_in, const uint32_t *order, uint32_t n,
                              uint32_t id_base, float4 *tri_out, cudaStream_t s);
-// one wave: sample `sample` of every pixel of the row shard, all bounces; adds into accum
-cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, int32_t *hit_ids, uint32_t sample,
+// one wave: samples [sample, sample + batch) of every pixel of the row shard, all bounces; adds into accum
+// (batch > 1 needs st->slices to hold batch slices and batch * shard pixels <= st->q_cap)
+cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, int32_t *hit_ids, uint32_t sample, uint32_t batch,
                               bool jitter, cudaStream_t s, uint64_t *launches);
 cudaError_t launch_frame_finish(const float4 *accum, float4 *f32_out, uint32_t *rgba8_out, uint32_t n_pixels,
                                 cudaStream_t s);

@@ -183,6 +183,10 @@ class NativeTracer:
     def scene_stats_reset(self) -> None:
         self._ck(self._lib.ptb_scene_stats_reset(self._ctx))
 
+    def set_wave_samples(self, samples_per_wave: int) -> None:
+        """Samples of every pixel one wave traces (0 = as many as fit the path queues). Scheduling only."""
+        self._ck(self._lib.ptb_scene_set_wave_samples(self._ctx, samples_per_wave))
+
     def scene_queue_sizes(self):
         """Live paths entering each bounce of the last wave: [camera rays, after 1 scatter, ...]."""
         out = (C.c_uint32 * 256)()

@@ -241,7 +241,7 @@ def test_config3_full_size_500_spheres_1080p(S):
         t.render_samples(0, 2)
         assert_images_equal(t.read_accum(), so.accumulate(0, 2, seed=0), "c3 2-sample accumulation")
         q = t.scene_queue_sizes()
-        assert q[0] == w * h and all(a >= b for a, b in zip(q, q[1:]))       # paths only ever die
+        assert q[0] == 2 * w * h and all(a >= b for a, b in zip(q, q[1:]))   # one wave of both samples; paths only ever die
 
 
 def test_config4_full_size_million_triangles_4k(S):
@@ -328,6 +328,36 @@ def test_row_sharded_scene_render_merges_to_the_full_frame(S, band):
             assert np.all(part[np.arange(h) // band % 3 == r, :, 3] == 3)
             total += part
     assert_images_equal(total, full, "row-sharded merge")
+
+
+@pytest.mark.parametrize("make,w,h,depth", [
+    (lambda w, h: scenes.mixed_small(width=w, height=h), 160, 90, 6),
+    (lambda w, h: scenes.random_spheres(120, width=w, height=h), 133, 71, 8),          # ragged 8x4 tiles
+])
+def test_samples_per_wave_is_scheduling_only(S, make, w, h, depth):
+    """n7: a wave may carry 1, 3 or up to 64 samples of every pixel (ptb_scene_set_wave_samples) — the accumulation buffer
+    is the same bit for bit, also for ragged sample counts, progressive calls and row shards; and equal to the oracle."""
+    sc = make(w, h)
+    ref = S.SceneOracle(sc, w, h, max_depth=depth).accumulate(0, 11, seed=5)
+    got = {}
+    for per_wave in (1, 3, 0):
+        with NativeTracer(w, h, seed=5, max_depth=depth) as t:
+            t.upload_scene(sc)
+            t.set_wave_samples(per_wave)
+            t.render_samples(0, 7)               # 3 + 3 + 1 when per_wave = 3
+            assert t.scene_queue_sizes()[0] == w * h * {1: 1, 3: 1, 0: 7}[per_wave]
+            t.render_samples(7, 4)
+            got[per_wave] = t.read_accum()
+            t.accum_reset()
+            t.set_row_shard(1, 3, 4)
+            t.render_samples(0, 5)
+            part = t.read_accum()
+            rows = np.arange(h) // 4 % 3 == 1
+            assert np.all(part[~rows] == 0) and np.all(part[rows][..., 3] == 5)
+            got[per_wave, "shard"] = part
+    for per_wave in (1, 3, 0):
+        assert_images_equal(got[per_wave], ref, f"{per_wave} samples per wave vs oracle")
+        assert_images_equal(got[per_wave, "shard"], got[1, "shard"], f"{per_wave} samples per wave, row shard")
 
 
 def test_furnace_and_energy_bounds():
