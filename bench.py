@@ -440,17 +440,26 @@ def run_b200(args):
             prim_b = 16.0 if wl["scene"] == "spheres" else 48.0
             b_sample = (c["nodes_visited_per_sample"] * 64.0 + c["prims_tested_per_sample"] * prim_b +
                         c["segments_per_sample"] * 2.0 * STATE_BYTES_PER_PATH + ACCUM_BYTES_PER_PIXEL)
-            n_launch = wl["max_depth"] + 1
-            alg = b_sample * pix_rank                                    # one wave (all bounces of one sample)
+            n_launch = max(1.0, launches / K)                             # measured: kernels of this library per step
+            alg = b_sample * pix_rank                                    # one sample of every pixel of the rank, all bounces
             wave_ms = k_ms / max(1.0, spp_rank)
             achieved = alg / (wave_ms * 1e-3) / 1e9
+            # the part of those bytes that cannot be cache hits: path state streamed once per segment (evict-first, waves of
+            # up to 32 Mi paths x 40 B), the per-sample radiance slot (16 B written, 16 B read back) and the accumulator
+            stream_b = c["segments_per_sample"] * 2.0 * STATE_BYTES_PER_PATH + 32.0 + ACCUM_BYTES_PER_PIXEL / max(1.0, min(64.0, spp_rank))
+            stream_gbs = stream_b * pix_rank / (wave_ms * 1e-3) / 1e9
             roof = {"kernel": "bounce_kernel", "bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"],
                     "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None,
                     "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peaks['source']}); the scene ({c['scene_bytes'] / 1e6:.1f} MB) is "
-                                   "L2-resident, so node/primitive fetch is served by L1/L2 and the kernel is latency / "
-                                   "divergence bound rather than HBM bound (DESIGN.md 5)",
+                                   "L2-resident, so node/primitive fetch is served by L1/L2 (frac can exceed 1: it counts those cache hits "
+                                   "as bytes, as SURVEY.md 8d prescribes) and the kernel is latency / divergence bound rather than HBM "
+                                   "bound; hbm_stream_* is the share that must come from HBM (DESIGN.md 5)",
                     "algorithmic_bytes_per_sample": b_sample, "algorithmic_bytes_per_wave": alg,
-                    "launches_per_wave": n_launch, "wave_ms": wave_ms, "launch_ms": wave_ms / n_launch,
+                    "hbm_stream_bytes_per_sample": stream_b, "hbm_stream_gbs": stream_gbs, "hbm_stream_frac": stream_gbs / peaks["hbm_gbs"],
+                    "launches_per_step": n_launch, "wave_ms": wave_ms, "launch_ms": k_ms / n_launch,
+                    "note": "achieved = algorithmic bytes of ONE sample of every pixel / (render time per step / spp per step); "
+                            "a wave carries several samples of every pixel (ptb_scene_set_wave_samples), launches_per_step counts "
+                            "the bounce kernels and slice reductions actually launched",
                     "counters": c}
         else:
             fp32_peak = 148 * 128 * 2 * peaks["sm_max_mhz"] * 1e6 / 1e12     # TFLOP/s at max SM clock
