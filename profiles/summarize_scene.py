@@ -39,7 +39,7 @@ out = subprocess.run(["ncu", "-i", os.path.join(G, f"prof_bounce_{wl}.ncu-rep"),
 rows = list(csv.reader(io.StringIO(out)))
 hdr, units = rows[0], rows[1]
 with open(os.path.join(P, f"{tag}_{wl}_bounce_ncu.txt"), "w") as f:
-    f.write(f"# ncu --set full --clock-control none --import-source on -k regex:bounce_kernel -s 27 -c 3  (profiles/run_ncu_scene.sh {wl})\n")
+    f.write(f"# ncu --set full --clock-control none --import-source on -k regex:bounce_kernel -s 20 -c 5  (profiles/run_ncu_scene.sh {wl})\n")
     for row in rows[2:]:
         f.write(f"--- {row[hdr.index('Kernel Name')][:90]}\n")
         for k in KEYS:
