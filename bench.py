@@ -473,9 +473,10 @@ def run_b200(args):
                     "hbm_bytes_per_launch": ACCUM_BYTES_PER_PIXEL * pix_rank,
                     "hbm_frac": ACCUM_BYTES_PER_PIXEL * pix_rank / (k_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]}
         tr = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tr) and world == 1 and args.workload == "c2":
+        if os.path.exists(tr) and world == 1 and args.workload in ("c2", "c3", "c4"):
             try:
-                roof["traffic"] = json.load(open(tr)).get(roof["kernel"])
+                key = roof["kernel"] if args.workload == "c2" else f"{roof['kernel']}:{args.workload}"
+                roof["traffic"] = json.load(open(tr)).get(key)
             except Exception:
                 pass
 
