@@ -329,6 +329,36 @@ __global__ void __launch_bounds__(256) csmain_accumulate(const FrameK k, float4 
     float sr = 0.0f, sg = 0.0f, sb = 0.0f, sa = 0.0f;
     uint32_t i = 0;
     const bool lean = MODE != MODE_GENERIC && certain_miss(k, fx, fy);   // every sample of this pixel misses
+    if (MODE != MODE_GENERIC && JITTER && lean) {
+        // certain-miss pixels (most of the frame): their own loop, so that the per-pixel invariant `lean` is not tested
+        // per iteration; Test.hlsl:36 for both samples, nothing else to evaluate.  Same operations, same order.
+#pragma unroll 2
+        for (; i + 2 <= n_samples; i += 2) {
+            uint32_t ax = vx0, ay = (first_sample + i) * 1664525u + 1013904223u, az = vz0;
+            uint32_t bx = vx0, by = ay + 1664525u, bz = vz0;
+            ax += ay * az;
+            bx += by * bz;
+            ay += az * ax;
+            by += bz * bx;
+            az += ax * ay;
+            bz += bx * by;
+            ax ^= ax >> 16;
+            bx ^= bx >> 16;
+            ay ^= ay >> 16;
+            by ^= by >> 16;
+            az ^= az >> 16;
+            bz ^= bz >> 16;
+            ax += ay * az;
+            bx += by * bz;
+            ay += az * ax;
+            by += bz * bx;
+            const F2 px = fadd2(splat(fxm1), make_float2(bits_to_unit_plus_one(ax), bits_to_unit_plus_one(bx)));
+            const F2 py = fadd2(splat(fym1), make_float2(bits_to_unit_plus_one(ay), bits_to_unit_plus_one(by)));
+            const F2 uvx2 = screen_uv2(px, k.div_x, k.inv_div_x), uvy2 = screen_uv2(py, k.div_y, k.inv_div_y);
+            sr = fadd(fadd(sr, uvx2.x), uvx2.y);
+            sg = fadd(fadd(sg, uvy2.x), uvy2.y);
+        }
+    }
     if (MODE != MODE_GENERIC && JITTER) {
         // two samples per iteration in FP32x2 lanes; the sums stay sequential in sample order
         for (; i + 2 <= n_samples; i += 2) {
@@ -353,11 +383,6 @@ __global__ void __launch_bounds__(256) csmain_accumulate(const FrameK k, float4 
             const F2 px = fadd2(splat(fxm1), make_float2(bits_to_unit_plus_one(ax), bits_to_unit_plus_one(bx)));
             const F2 py = fadd2(splat(fym1), make_float2(bits_to_unit_plus_one(ay), bits_to_unit_plus_one(by)));
             const F2 uvx2 = screen_uv2(px, k.div_x, k.inv_div_x), uvy2 = screen_uv2(py, k.div_y, k.inv_div_y);
-            if (lean) {                      // Test.hlsl:36 for both samples, nothing else to evaluate
-                sr = fadd(fadd(sr, uvx2.x), uvx2.y);
-                sg = fadd(fadd(sg, uvy2.x), uvy2.y);
-                continue;
-            }
             F2 r, g, b;
             bool h0, h1;
             csmain_shade2<MODE>(k, uvx2, uvy2, r, g, b, h0, h1);
