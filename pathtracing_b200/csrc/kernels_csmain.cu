@@ -162,8 +162,14 @@ __device__ __forceinline__ void csmain_shade2(const FrameK &k, F2 uvx, F2 uvy, F
     g = uvy;
     bl = splat(0.0f);
     if (h0 || h1) {
-        // :27 — IEEE sqrt per lane (disc may be arbitrarily small); a missing lane gets a dummy argument
-        const F2 num = make_float2(fsub(-b.x, fsqrt(h0 ? disc.x : 1.0f)), fsub(-b.y, fsqrt(h1 ? disc.y : 1.0f)));
+        // :27 — sqrt(disc); a missing lane gets a dummy argument.  disc may be arbitrarily small next to the silhouette:
+        // the packed exactly-rounded sequence inside its proven domain, IEEE sqrt per lane outside it
+        const float d0 = h0 ? disc.x : 1.0f, d1 = h1 ? disc.y : 1.0f;
+        F2 num;
+        if (in_fast_range(d0) && in_fast_range(d1))
+            num = fadd2(neg2(b), neg_sqrt_rn_fast2(make_float2(-d0, -d1)));     // (-b) + (-sqrt) == (-b) - sqrt, one rounding
+        else
+            num = make_float2(fsub(-b.x, fsqrt(d0)), fsub(-b.y, fsqrt(d1)));
         const F2 denN = fmul2(splat(-2.0f), a);                  // -(2a), 2a in (1,4)
         const F2 t = div_rn_by_rcp2(num, denN, rcp_rn_fast2_neg(denN));
         // :28-29 — pc = (cam + t*d) - centre, with t*d.z = RN(t*(-yh))
