@@ -293,6 +293,8 @@ def run_b200(args):
         # ---- device-timed value ---------------------------------------------------------------------
         for s in range(Wm):
             step_device(s)
+        if not literal and not merge_every_step:
+            do_merge()                                 # progressive merge of the warm-up samples: the timed merge below is not NCCL's first call
         if pipelined:
             sr.finish()
         barrier()
