@@ -735,11 +735,14 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
     const uint32_t tiles_x = (k.width + 7u) / 8u, tiles_y = (rows + 3u) / 4u;
     const uint32_t n0 = tiles_x * tiles_y * 32u * batch;
     const uint32_t depths = k.shade_mode == PTB_SHADE_NORMALS ? 1u : k.max_depth + 1u;
-    // bounces >= tail_depth run inside ONE launch (0 disables); PTB200_TAIL_DEPTH overrides for A/B runs
-    static const uint32_t tail_depth = [] {
+    // bounces >= tail_depth run inside ONE launch (0 disables): queues that deep are too small to fill the GPU, unless the
+    // wave is a big batched one (>= 8 Mi camera rays), whose queues stay large two bounces longer (c3: tail at 4 costs 6 %
+    // there).  PTB200_TAIL_DEPTH overrides for A/B runs.
+    static const int tail_env = [] {
         const char *e = std::getenv("PTB200_TAIL_DEPTH");
-        return e ? (uint32_t)std::atoi(e) : 4u;
+        return e ? std::atoi(e) : -1;
     }();
+    const uint32_t tail_depth = tail_env >= 0 ? (uint32_t)tail_env : ((uint64_t)n0_pixels * batch >= (8u << 20) ? 6u : 4u);
     // counters: [0, depths] queue sizes, [depths+1, 2*depths+1] work cursors
     cudaError_t e = cudaMemsetAsync(st->counts, 0, sizeof(uint32_t) * st->counts_len, s);
     if (e != cudaSuccess) return e;
