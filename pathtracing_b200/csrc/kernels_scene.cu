@@ -179,15 +179,16 @@ __device__ __forceinline__ bool test_leaf(const SceneK &k, int leaf, const RayT 
     return false;
 }
 
-// Stack-based traversal of one hierarchy, warp-synchronous "while-while".  MUST be called by all 32
-// lanes of a warp (lanes without a ray pass active = false): the inner loop descends through nodes
-// (test both child boxes, go to the nearer, push the farther with its entry distance) until the lane
-// holds a leaf or has finished; __syncwarp() behind the inner loop makes the primitive tests — the
-// expensive, exactly rounded part — run with every lane that holds a leaf, and nobody leaves the outer
-// loop before the whole warp is done, so the caller continues converged.  Without the explicit
-// reconvergence, independent thread scheduling let every lane run its leaf tests AND the shading that
-// follows on its own: 2.6-3.0 active threads per instruction there (profiles/r01_notes.md).
-// CLS 0 = spheres, 1 = triangles.  ANY: stop at the first hit.
+// Stack-based traversal of one hierarchy, "while-while": the inner loop descends through nodes (test both child boxes,
+// go to the nearer, push the farther) until the lane holds a leaf or has finished, then the leaf's primitives are tested.
+// Lanes walk independently and the CALLER reconverges the warp (__syncwarp) before it shades: without that, independent
+// thread scheduling let every lane run the shading that follows on its own, 2.6-3.0 active threads per instruction
+// (profiles/r01_notes.md).  Two things an earlier version had were measured out again once waves carried millions of
+// paths (profiles/r01_notes.md): lockstep rounds (the warp reconverging before every round of primitive tests; c3 3,516 vs
+// 3,734 Msamples/s without) and entry distances stored next to the stacked references so that a pop could skip entries
+// the closest hit had ruled out since (2-4 % fewer node visits, but twice the stack's L1 footprint — 2 x 128 B lines per
+// warp and stack level; c4 929 -> 1,050 without).  A stale entry is culled one level later by the box tests of its children.
+// Lanes without a ray pass active = false.  CLS 0 = spheres, 1 = triangles.  ANY: stop at the first hit.
 template <int CLS, bool ANY, bool STATS, bool FMA_SLAB>
 __device__ __forceinline__ bool traverse(const SceneK &k, const RayT &r, float t_min, float t_max, bool active, Best &best,
                                          Counters &cn, uint32_t *error_flag)
@@ -195,23 +196,13 @@ __device__ __forceinline__ bool traverse(const SceneK &k, const RayT &r, float t
     const BvhNode *__restrict__ nodes = CLS == 0 ? k.sph_nodes : k.tri_nodes;
     const int root = CLS == 0 ? k.sph_root : k.tri_root;
     if (root == EMPTY_REF) return false;               // launch-uniform
-    const bool lockstep = (CLS == 0 ? k.sph_lockstep : k.tri_lockstep) != 0;
     int cur = active ? root : EMPTY_REF;               // node (>= 0), leaf (< 0) or EMPTY_REF = finished
     int stack[STACK_N];
-    float tstack[STACK_N];
     int sp = 0;
     uint32_t prims = 0;
     bool found = false;
 
-    // next entry of the stack that the current closest hit does not rule out, else EMPTY_REF
-#define PTB_POP()                                                                \
-    do {                                                                         \
-        cur = EMPTY_REF;                                                         \
-        while (sp > 0) {                                                         \
-            --sp;                                                                \
-            if (ANY || tstack[sp] <= best.t_cull) { cur = stack[sp]; break; }    \
-        }                                                                        \
-    } while (0)
+#define PTB_POP() (cur = sp > 0 ? stack[--sp] : EMPTY_REF)
 
     for (;;) {
         while (cur >= 0) {
@@ -226,9 +217,7 @@ __device__ __forceinline__ bool traverse(const SceneK &k, const RayT &r, float t
                 const bool swap = tn1 < tn0;
                 cur = swap ? nd.y : nd.x;
                 if (sp < STACK_N) {
-                    stack[sp] = swap ? nd.x : nd.y;
-                    tstack[sp] = swap ? tn0 : tn1;
-                    ++sp;
+                    stack[sp++] = swap ? nd.x : nd.y;
                     if (STATS) cn.max_stack = max(cn.max_stack, (uint32_t)sp);
                 } else {
                     atomicOr(error_flag, 1u);
@@ -241,28 +230,19 @@ __device__ __forceinline__ bool traverse(const SceneK &k, const RayT &r, float t
                 PTB_POP();
             }
         }
-        if (lockstep) {                                 // launch-uniform
-            __syncwarp();
-            if (!__any_sync(FULL, cur != EMPTY_REF)) break;
-        } else if (cur == EMPTY_REF) {
+        if (cur == EMPTY_REF) break;
+        if (test_leaf<CLS, ANY>(k, cur, r, t_min, t_max, best, prims)) {
+            found = true;
             break;
         }
-        if (cur != EMPTY_REF) {
-            if (test_leaf<CLS, ANY>(k, cur, r, t_min, t_max, best, prims)) {
-                found = true;
-                cur = EMPTY_REF;
-            } else {
-                PTB_POP();
-            }
-        }
-        if (lockstep) __syncwarp();
+        PTB_POP();
     }
 #undef PTB_POP
     if (STATS) cn.prims += prims;
     return ANY ? found : best.id >= 0;
 }
 
-// all 32 lanes of the warp must call this (active = false for lanes without a ray)
+// closest hit over both hierarchies (active = false for lanes without a ray)
 template <bool STATS, bool FMA_SLAB>
 __device__ __forceinline__ bool closest_hit(const SceneK &k, const RayT &r, float t_min, float t_max, bool active, Best &best,
                                             Counters &cn, uint32_t *error_flag)
@@ -487,7 +467,7 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
       bounce_again:
         float cr = 0.0f, cg = 0.0f, cb = 0.0f;     // radiance this path adds now
         bool add = false;
-        // closest hit: warp-synchronous, every lane takes part (lanes past the end of the queue idle)
+        // closest hit: every lane takes part (lanes past the end of the queue pass alive = false), the warp reconverges behind it
         RayT r;
         make_ray(r, ox, oy, oz, dx, dy, dz);
         Best best;
@@ -661,7 +641,7 @@ __global__ void __launch_bounds__(256) trace_rays_kernel(const SceneK k, uint64_
                                                          int32_t *out_prim, float *out_t, uint32_t *error_flag)
 {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const bool active = i < n;                          // no early return: the traversal is warp-synchronous
+    const bool active = i < n;                          // no early return: lanes without a ray just skip the walk
     const uint64_t j = active ? i : 0;
     RayT r;
     make_ray(r, o[3 * j], o[3 * j + 1], o[3 * j + 2], d[3 * j], d[3 * j + 1], d[3 * j + 2]);

@@ -56,15 +56,6 @@ void free_state(SceneState *st)
 constexpr uint32_t MAX_WAVE_SAMPLES = 64u;                  // 6 bits of the path id word
 constexpr uint32_t WAVE_PATHS_TARGET = 32u << 20;            // paths per wave the queues are sized for (56 B per path)
 
-// Lockstep primitive tests when the hierarchy fits the SM's L1 (measured: profiles/r01_notes.md).
-// PTB200_LOCKSTEP=0/1 forces the choice (A/B experiments).
-uint32_t lockstep_for(uint32_t n_nodes)
-{
-    static const char *env = std::getenv("PTB200_LOCKSTEP");
-    if (env && (env[0] == '0' || env[0] == '1')) return env[0] == '1';
-    return (uint64_t)n_nodes * 64u <= 128u * 1024u ? 1u : 0u;
-}
-
 ptb::SceneK make_k(const ptb_context *ctx, const SceneState *st)
 {
     ptb::SceneK k{};
@@ -98,8 +89,6 @@ ptb::SceneK make_k(const ptb_context *ctx, const SceneState *st)
     k.tri_nodes = st->tri_bvh.nodes;
     k.tri_root = st->tri_bvh.root_ref;
     k.materials = st->materials;
-    k.sph_lockstep = lockstep_for(st->sph_bvh.n_nodes);
-    k.tri_lockstep = lockstep_for(st->tri_bvh.n_nodes);
     return k;
 }
 

@@ -62,10 +62,6 @@ struct SceneK {
     const BvhNode *tri_nodes;
     int tri_root;
     const ptb_material *materials;
-    // 1: the warp reconverges before every round of primitive tests (pays when the hierarchy is cache resident
-    // and the kernel issue bound); 0: lanes traverse independently and only reconverge before shading (pays when
-    // node fetches miss L1 and diverged lanes hide each other's latency).  scene.cu picks by hierarchy size.
-    uint32_t sph_lockstep, tri_lockstep;
 };
 
 // Wavefront path state, structure of arrays, ping-pong (in/out) per bounce:
