@@ -27,7 +27,10 @@ namespace {
 
 constexpr int STACK_N = 64;
 #ifndef PTB_BOUNCE_MIN_BLOCKS
-#define PTB_BOUNCE_MIN_BLOCKS 4   // resident 256-thread blocks per SM the bounce kernel is compiled for (register cap)
+// resident 256-thread blocks per SM the bounce kernel is compiled for (register cap).  Measured with the lean traversal
+// stack (profiles/r01_notes.md): 3 / 4 / 5 / 6 blocks -> c4 1,064 / 1,051 / 1,109 / 1,083, c3 3,781 / 3,732 / 3,739 / 3,671
+// Msamples/s; 5 = 48 registers with ~100 B of spills, 40 warps per SM to hide the L2 latency of the node fetches.
+#define PTB_BOUNCE_MIN_BLOCKS 5
 #endif
 constexpr unsigned FULL = 0xFFFFFFFFu;
 

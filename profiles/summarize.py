@@ -58,6 +58,9 @@ with open(os.path.join(P, f"{tag}_accumulate_ncu.txt"), "w") as f:
             v, u = float(row[hdr.index(k)].replace(",", "")), units[hdr.index(k)]
             return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[u]
         traffic["csmain_accumulate"] = val("dram__bytes_read.sum") + val("dram__bytes_write.sum")
-json.dump(traffic, open(os.path.join(P, "traffic.json"), "w"), indent=1)
+tpath = os.path.join(P, "traffic.json")
+merged = json.load(open(tpath)) if os.path.exists(tpath) else {}      # keep the entries of the scene workloads
+merged.update(traffic)
+json.dump(merged, open(tpath, "w"), indent=1)
 print(open(os.path.join(P, f"{tag}_launches.txt")).read())
 print(open(os.path.join(P, f"{tag}_accumulate_ncu.txt")).read())

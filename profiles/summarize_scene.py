@@ -54,5 +54,20 @@ with open(os.path.join(P, f"{tag}_{wl}_bounce_ncu.txt"), "w") as f:
                     pass
         for v, k in sorted(stalls, reverse=True)[:6]:
             f.write(f"  {k} = {v:.3f}\n")
+# DRAM bytes of the captured wave (its five bounce launches: depth 0..3 + tail), per ONE sample of every pixel
+spw = int(sys.argv[3]) if len(sys.argv) > 3 else {"c3": 8, "c4": 4}[wl]      # samples per pixel of the profiled wave (run_ncu_scene.sh SPP)
+scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+tot_b = 0.0
+for row in rows[2:]:
+    for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+        tot_b += float(row[hdr.index(k)].replace(",", "")) * scale[units[hdr.index(k)]]
+tpath = os.path.join(P, "traffic.json")
+tr = json.load(open(tpath)) if os.path.exists(tpath) else {}
+tr[f"bounce_kernel:{wl}"] = round(tot_b / spw)
+tr["_note"] = ("dram__bytes_read.sum + dram__bytes_write.sum from ncu --set full. csmain_accumulate: per launch (profiles/r01_accumulate_ncu.txt). "
+               "bounce_kernel:<workload>: summed over the five bounce launches of ONE wave (depth 0..3 + tail) and divided by the wave's samples "
+               "per pixel (c3: 8, c4: 4), i.e. per one sample of every pixel = the unit of roofline.achieved "
+               "(profiles/r01_c3_bounce_ncu.txt, r01_c4_bounce_ncu.txt)")
+json.dump(tr, open(tpath, "w"), indent=1)
 print(open(os.path.join(P, f"{tag}_{wl}_launches.txt")).read())
 print(open(os.path.join(P, f"{tag}_{wl}_bounce_ncu.txt")).read())
