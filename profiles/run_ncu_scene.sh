@@ -8,6 +8,6 @@ $CMD > gpurun_out/plain_$WL.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv \
     --log-file gpurun_out/launches_$WL.csv $CMD > gpurun_out/ncu_launches_$WL.log 2>&1
 $CMD > gpurun_out/plain2_$WL.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:bounce_kernel -s 20 -c 5 \
+ncu --set full --clock-control none --import-source on -k regex:bounce_kernel -s 21 -c 7 \
     -f -o gpurun_out/prof_bounce_$WL $CMD > gpurun_out/ncu_full_$WL.log 2>&1
 tail -q -n 2 gpurun_out/ncu_launches_$WL.log gpurun_out/ncu_full_$WL.log

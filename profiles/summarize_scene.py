@@ -39,7 +39,7 @@ out = subprocess.run(["ncu", "-i", os.path.join(G, f"prof_bounce_{wl}.ncu-rep"),
 rows = list(csv.reader(io.StringIO(out)))
 hdr, units = rows[0], rows[1]
 with open(os.path.join(P, f"{tag}_{wl}_bounce_ncu.txt"), "w") as f:
-    f.write(f"# ncu --set full --clock-control none --import-source on -k regex:bounce_kernel -s 20 -c 5  (profiles/run_ncu_scene.sh {wl})\n")
+    f.write(f"# ncu --set full --clock-control none --import-source on -k regex:bounce_kernel -s 21 -c 7  (profiles/run_ncu_scene.sh {wl})\n")
     for row in rows[2:]:
         f.write(f"--- {row[hdr.index('Kernel Name')][:90]}\n")
         for k in KEYS:
@@ -54,7 +54,7 @@ with open(os.path.join(P, f"{tag}_{wl}_bounce_ncu.txt"), "w") as f:
                     pass
         for v, k in sorted(stalls, reverse=True)[:6]:
             f.write(f"  {k} = {v:.3f}\n")
-# DRAM bytes of the captured wave (its five bounce launches: depth 0..3 + tail), per ONE sample of every pixel
+# DRAM bytes of the captured wave (its bounce launches: depth 0..5 + tail), per ONE sample of every pixel
 spw = int(sys.argv[3]) if len(sys.argv) > 3 else {"c3": 8, "c4": 4}[wl]      # samples per pixel of the profiled wave (run_ncu_scene.sh SPP)
 scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 tot_b = 0.0
@@ -65,7 +65,7 @@ tpath = os.path.join(P, "traffic.json")
 tr = json.load(open(tpath)) if os.path.exists(tpath) else {}
 tr[f"bounce_kernel:{wl}"] = round(tot_b / spw)
 tr["_note"] = ("dram__bytes_read.sum + dram__bytes_write.sum from ncu --set full. csmain_accumulate: per launch (profiles/r01_accumulate_ncu.txt). "
-               "bounce_kernel:<workload>: summed over the five bounce launches of ONE wave (depth 0..3 + tail) and divided by the wave's samples "
+               "bounce_kernel:<workload>: summed over the bounce launches of ONE wave (depth 0..5 + tail) and divided by the wave's samples "
                "per pixel (c3: 8, c4: 4), i.e. per one sample of every pixel = the unit of roofline.achieved "
                "(profiles/r01_c3_bounce_ncu.txt, r01_c4_bounce_ncu.txt)")
 json.dump(tr, open(tpath, "w"), indent=1)
