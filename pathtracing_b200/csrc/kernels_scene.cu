@@ -9,13 +9,18 @@
 // sqrtf below is one IEEE binary32 round-to-nearest operation, never contracted, which is what
 // makes the results bit-identical to the CPU oracle.  FMAs appear only where written as fmaf().
 //
-// Wavefront organisation: one wave = one sample of every pixel of this context's row shard.
+// Wavefront organisation: one wave = `batch` samples of every pixel of this context's row shard
+// (scene.cu packs as many as fit the path queues), camera rays generated in 8x4 pixel tiles.
 // Per bounce ONE fused kernel (closest hit over both hierarchies + scatter), run by a persistent
 // grid whose warps pull 32-path chunks from an atomic cursor.  Paths that continue are repacked
 // into the next queue with warp ballot + prefix popcount + one atomicAdd per warp, so every
-// bounce starts from a dense array (structure of arrays, 40 B per path).  A pixel owns at most
-// one live path per wave, so terminated paths add their radiance to the float4 accumulation
-// buffer with a plain read-modify-write.
+// bounce starts from a dense array (structure of arrays, 40 B per path); from a certain depth on
+// the few paths left finish inside one launch (tail mode).  With batch = 1 a pixel owns at most
+// one live path per wave and terminated paths add their radiance to the float4 accumulation
+// buffer with a plain read-modify-write; with batch > 1 every path stores its radiance into its
+// own slot of slices[sample of the wave][pixel of the shard] and reduce_slices_kernel adds the
+// slices in sample order — the same additions in the same order, so the results do not depend
+// on the wave size.
 #include <cfloat>
 #include <cstdlib>
 
@@ -47,7 +52,7 @@ struct RayT {
 
 struct Best {
     float t;
-    float t_cull;  // t * (1 + 2^-19): what node culling and stack pruning compare against
+    float t_cull;  // t * (1 + 2^-19): what node culling compares against
     int id;        // unified original primitive id (spheres 0..ns-1, triangles ns..)
     int pos;       // leaf-order position inside its class
     int cls;       // 0 sphere, 1 triangle
