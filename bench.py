@@ -83,6 +83,13 @@ def cpu_scene_sample(wl, scene, spp_sample, steps, warmup):
     return W * H * spp_sample * len(times) / total / 1e6, 1e3 * total / len(times), O.max_threads()
 
 
+def use_host_cores():
+    """torchrun exports OMP_NUM_THREADS=1 to its workers; the timed CPU legs run on every core this process may use."""
+    from oracle import pt_oracle as O
+    if "TORCHELASTIC_RUN_ID" in os.environ or int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        O.set_threads(len(os.sched_getaffinity(0)))
+
+
 def load_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -194,6 +201,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
+    use_host_cores()
     wl = dict(WORKLOADS[args.workload])
     if args.spp:
         wl["spp"] = args.spp
@@ -484,6 +492,8 @@ def run_b200(args):
 
         # ---- CPU baseline on this box's host cores (bounded sample) ------------------------------------------
         cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            use_host_cores()
         if world == 1 and not args.no_cpu_baseline and scene is not None:
             ms, _, threads = cpu_scene_sample(wl, scene, 1, 2, 1)
             cpu = {"value": ms, "unit": "Msamples/s", "cores": threads, "kind": "port",

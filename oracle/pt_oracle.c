@@ -17,6 +17,17 @@
 #include <omp.h>
 #endif
 
+/* Threads of the following parallel regions (torchrun exports OMP_NUM_THREADS=1 to its workers; the timed CPU
+ * baseline asks for the host's cores explicitly instead of inheriting that). */
+void pto_set_threads(int n)
+{
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int pto_max_threads(void)
 {
 #ifdef _OPENMP

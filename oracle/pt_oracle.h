@@ -92,6 +92,7 @@ void pto_present(const uint8_t *src_rgba8, uint32_t sw, uint32_t sh,
                  uint8_t *dst_bgra8, uint32_t dw, uint32_t dh, uint32_t flags);
 
 int pto_max_threads(void);
+void pto_set_threads(int n);
 
 #ifdef __cplusplus
 }

@@ -70,6 +70,8 @@ def lib() -> C.CDLL:
         L.pto_present.restype = None
         L.pto_max_threads.argtypes = []
         L.pto_max_threads.restype = C.c_int
+        L.pto_set_threads.argtypes = [C.c_int]
+        L.pto_set_threads.restype = None
         _lib = L
     return _lib
 
@@ -147,3 +149,8 @@ def bits_to_unit(w: int) -> np.float32:
 
 def max_threads() -> int:
     return int(lib().pto_max_threads())
+
+
+def set_threads(n: int) -> None:
+    """OpenMP threads of the following calls (both oracles share the OpenMP runtime)."""
+    lib().pto_set_threads(int(n))
