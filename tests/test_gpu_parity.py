@@ -431,6 +431,12 @@ def test_row_shard_argument_errors():
         t.set_row_shard(40, 64)          # offset beyond the image: nothing to render, not an error
         t.compute_frame()
         assert not t.read_rgba8().any()
+        t.set_row_shard(0, 2, 100)       # one band taller than the image: rank 0 of 2 owns every row, rank 1 none
+        t.compute_frame()
+        assert t.read_rgba8()[..., 3].all()
+        t.set_row_shard(1, 2, 100)
+        t.render_samples(0, 2)
+        assert not t.read_accum().any()
 
 
 def test_sharded_renderer_single_rank_paths(oracle):

@@ -340,12 +340,12 @@ def test_samples_per_wave_is_scheduling_only(S, make, w, h, depth):
     sc = make(w, h)
     ref = S.SceneOracle(sc, w, h, max_depth=depth).accumulate(0, 11, seed=5)
     got = {}
-    for per_wave in (1, 3, 0):
+    for per_wave in (1, 3, 0, 1000):             # 1000: clipped to what fits (<= 64 samples per wave)
         with NativeTracer(w, h, seed=5, max_depth=depth) as t:
             t.upload_scene(sc)
             t.set_wave_samples(per_wave)
             t.render_samples(0, 7)               # 3 + 3 + 1 when per_wave = 3
-            assert t.scene_queue_sizes()[0] == w * h * {1: 1, 3: 1, 0: 7}[per_wave]
+            assert t.scene_queue_sizes()[0] == w * h * {1: 1, 3: 1, 0: 7, 1000: 7}[per_wave]
             t.render_samples(7, 4)
             got[per_wave] = t.read_accum()
             t.accum_reset()
@@ -355,7 +355,7 @@ def test_samples_per_wave_is_scheduling_only(S, make, w, h, depth):
             rows = np.arange(h) // 4 % 3 == 1
             assert np.all(part[~rows] == 0) and np.all(part[rows][..., 3] == 5)
             got[per_wave, "shard"] = part
-    for per_wave in (1, 3, 0):
+    for per_wave in (1, 3, 0, 1000):
         assert_images_equal(got[per_wave], ref, f"{per_wave} samples per wave vs oracle")
         assert_images_equal(got[per_wave, "shard"], got[1, "shard"], f"{per_wave} samples per wave, row shard")
 
