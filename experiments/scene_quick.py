@@ -43,3 +43,6 @@ if which in ("c4", "all"):
     sc = scenes.triangle_terrain(512, 2, width=3840, height=2160)
     for ml in (1, 4, 8):
         run("c4", sc, 3840, 2160, 4, 8, ml)
+if which == "leaf8":
+    run("c3", scenes.random_spheres(500, width=1920, height=1080), 1920, 1080, 8, 8, 8)
+    run("c4", scenes.triangle_terrain(512, 2, width=3840, height=2160), 3840, 2160, 4, 8, 8)

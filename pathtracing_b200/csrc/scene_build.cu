@@ -14,6 +14,7 @@
 // Culling in the traversal kernels is conservative (padded boxes, padded slab interval), so the
 // closest hit a ray finds does not depend on the shape of this tree (oracle/pt_scene_oracle.h).
 #include <cfloat>
+#include <cstdlib>
 #include <cub/cub.cuh>
 
 #include "scene.cuh"
@@ -21,7 +22,6 @@
 namespace ptb {
 namespace {
 
-constexpr float SAH_C_TRAVERSE = 1.0f;   // one node visit = two box tests + one 64 B fetch
 constexpr float SAH_C_PRIM = 1.0f;       // one primitive test (+ its 16/48 B fetch)
 
 __device__ __forceinline__ uint32_t f2ord(float f)
@@ -164,7 +164,8 @@ __device__ __forceinline__ float box_area(float4 lo, float4 hi)
 __device__ __forceinline__ float4 ldcg4(const float4 *p) { return __ldcg(p); }
 
 __global__ void __launch_bounds__(256) refit_kernel(const float4 *__restrict__ prim_lo, const float4 *__restrict__ prim_hi,
-                                                    const uint32_t *__restrict__ vals, int n, uint32_t max_leaf, BuildTmp t)
+                                                    const uint32_t *__restrict__ vals, int n, uint32_t max_leaf,
+                                                    float SAH_C_TRAVERSE, BuildTmp t)
 {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
@@ -267,6 +268,19 @@ __global__ void single_leaf_kernel(const float4 *__restrict__ prim_lo, const flo
     nodes[0] = nd;
 }
 
+// Cost of one node visit (two box tests + one 64 B fetch) in units of one primitive test.  The primitive tests are
+// exactly rounded (IEEE division and square root), a node visit is 12 FMAs and a handful of min/max: measured
+// (profiles/r01_notes.md) 0.5 / 1 / 1.5 / 2 / 3 -> c3 3,831 / 3,739 / 3,689 / 3,606 / 3,342, c4 1,110 / 1,107 / 1,070 /
+// 1,007 / 864 Msamples/s.  PTB200_SAH_CTRAV overrides.
+float sah_c_traverse()
+{
+    static const float v = [] {
+        const char *e = std::getenv("PTB200_SAH_CTRAV");
+        return e ? (float)std::atof(e) : 0.5f;
+    }();
+    return v;
+}
+
 template <typename T>
 cudaError_t dmalloc(T **p, size_t count)
 {
@@ -356,7 +370,7 @@ cudaError_t build_lbvh(const float4 *prim_lo, const float4 *prim_hi, uint32_t n,
     BK(cudaMemsetAsync(t.arrive, 0, sizeof(uint32_t) * ni, s));
 
     karras_kernel<<<blocks_i, 256, 0, s>>>(keys_b, (int)n, t);
-    refit_kernel<<<blocks_n, 256, 0, s>>>(prim_lo, prim_hi, vals_b, (int)n, max_leaf, t);
+    refit_kernel<<<blocks_n, 256, 0, s>>>(prim_lo, prim_hi, vals_b, (int)n, max_leaf, sah_c_traverse(), t);
     survive_kernel<<<blocks_i, 256, 0, s>>>(ni, max_leaf, t);
     BK(cudaGetLastError());
     BK(cub::DeviceScan::ExclusiveSum(cub_tmp, scan_bytes, t.flags, t.compact, ni, s));
