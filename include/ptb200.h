@@ -223,7 +223,7 @@ int ptb_scene_info_get(ptb_context *ctx, ptb_scene_info *out);
 int ptb_scene_stats_get(ptb_context *ctx, ptb_scene_stats *out);
 int ptb_scene_stats_reset(ptb_context *ctx);
 /* ptb_render_samples on a scene traces WAVES: one wave = `samples_per_wave` samples of every pixel of the row shard
- * carried through all bounces.  0 (default) = as many as fit the path queues (sized for 32 Mi paths, at most 64 samples),
+ * carried through all bounces.  0 (default) = as many as fit the path queues (sized for 64 Mi paths, at most 64 samples),
  * so that small frames and 1/N row shards still fill the GPU at deep bounces; n >= 1 caps it.  Scheduling only: the
  * accumulation buffer receives the samples' radiance in sample order whatever the wave size — results do not change
  * by a bit (tests/test_gpu_scene.py). */

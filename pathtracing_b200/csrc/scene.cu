@@ -54,7 +54,9 @@ void free_state(SceneState *st)
 }
 
 constexpr uint32_t MAX_WAVE_SAMPLES = 64u;                  // 6 bits of the path id word
-constexpr uint32_t WAVE_PATHS_TARGET = 32u << 20;            // paths per wave the queues are sized for (56 B per path)
+// paths per wave the queues are sized for (2 x 40 B of path state + a 16 B radiance slot each = 6 GB at 64 Mi; measured
+// 8 / 16 / 32 / 64 Mi-path waves: c3 3,326 / 3,425 / 3,919 / 3,966, c4 full frame 33 / 66 Mi: 1,112 / 1,130 Msamples/s)
+constexpr uint32_t WAVE_PATHS_TARGET = 64u << 20;
 
 ptb::SceneK make_k(const ptb_context *ctx, const SceneState *st)
 {
