@@ -15,6 +15,7 @@
 // proven (exhaustively, selftest.cu) or provable (Markstein) to round identically on the domain
 // the launch-uniform checks in api.cu guarantee; MODE_GENERIC is the literal intrinsic form and
 // is used whenever those checks fail.  No dense contraction anywhere => no tensor cores.
+#include <cstdlib>
 #include "ptb_internal.h"
 #include "ptb_math.cuh"
 
@@ -313,8 +314,8 @@ cudaError_t launch_csmain_frame(const FrameK &k, const Buffers &b, cudaStream_t 
 // ---- multi-sample accumulation -------------------------------------------------------------
 // One thread per pixel, samples looped in-kernel: the float4 read-modify-write of the
 // accumulation buffer (32 B/pixel/launch) is amortised over n_samples, leaving the kernel
-// FP32-issue bound.  Block (32,8) keeps a warp on one row (coalesced 512 B accum access) and a
-// block on a 32x8 tile (hit/miss is spatially coherent, so few warps diverge).
+// FP32-issue bound.  Block (32,4) keeps a warp on one row (coalesced 512 B accum access) and a
+// block on a 32x4 tile (hit/miss is spatially coherent, so few warps diverge).
 // RNG: pcg3d keyed (pixel, sample, seed); the pixel and seed lanes of its first LCG step are
 // loop-invariant and hoisted.
 template <int MODE, bool JITTER>
@@ -496,8 +497,15 @@ static cudaError_t launch_acc_t(const FrameK &k, float4 *accum, uint32_t first, 
                                 bool jitter, cudaStream_t s)
 {
     if (shard_rows(k) == 0) return cudaSuccess;
-    const dim3 block(32, 8);
-    const dim3 grid((k.width + 31) / 32, (shard_rows(k) + 7) / 8);
+    // block height: 32x4 pixels measured best at 1080p (rows 8 / 4 / 2 / 1 -> 0.1711 / 0.1693 / 0.1729 / 0.1796 ms per
+    // 64-spp launch: smaller blocks even out the expensive silhouette tiles); PTB200_ACC_BLOCK_Y overrides for A/B runs
+    static const unsigned by = [] {
+        const char *e = std::getenv("PTB200_ACC_BLOCK_Y");
+        const int v = e ? std::atoi(e) : 4;
+        return (unsigned)(v >= 1 && v <= 8 ? v : 4);
+    }();
+    const dim3 block(32, by);
+    const dim3 grid((k.width + 31) / 32, (shard_rows(k) + by - 1) / by);
     if (jitter) csmain_accumulate<MODE, true><<<grid, block, 0, s>>>(k, accum, first, n, seed);
     else csmain_accumulate<MODE, false><<<grid, block, 0, s>>>(k, accum, first, n, seed);
     return cudaGetLastError();
