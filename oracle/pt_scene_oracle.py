@@ -6,7 +6,6 @@ legs).  Takes the same host arrays (`pathtracing_b200.scenes.Scene`) the CUDA ba
 from __future__ import annotations
 
 import ctypes as C
-import math
 
 import numpy as np
 

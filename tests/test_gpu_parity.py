@@ -368,7 +368,6 @@ def test_generic_kernel_handles_degenerate_parameters(oracle):
 
 
 def test_async_readback_is_ordered_and_matches_sync(oracle):
-    import ctypes
     w, h = 640, 360
     bufs = [np.zeros((h, w, 4), np.uint8) for _ in range(3)]
     with NativeTracer(w, h, seed=2) as t:
