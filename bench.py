@@ -289,9 +289,15 @@ def run_b200(args):
             else:
                 sr.merge(0)
 
+        # one GPU, literal scene: accumulate + resolve are ONE launch (ptb_render_resolve; PTB200_NO_FUSED_RESOLVE=1 for A/B)
+        fused = world == 1 and scene is None and not literal and not os.environ.get("PTB200_NO_FUSED_RESOLVE")
+
         def step_device(step):
             if literal:
                 t.compute_frame()
+                return
+            if fused:
+                t.render_resolve(step * spp_step, spp_step)
                 return
             sr.render(step * spp_step, spp_step)
             if merge_every_step:
@@ -322,10 +328,12 @@ def run_b200(args):
             kern_ev[s][0].record(stream)
             if literal:
                 t.compute_frame()
+            elif fused:
+                t.render_resolve((Wm + s) * spp_step, spp_step)
             else:
                 sr.render((Wm + s) * spp_step, spp_step)
             kern_ev[s][1].record(stream)
-            if not literal and merge_every_step:
+            if not literal and not fused and merge_every_step:
                 do_merge()
             ev[s][1].record(stream)
         ev[K][0].record(stream)
@@ -350,6 +358,8 @@ def run_b200(args):
         def step_e2e(step):
             if literal:
                 t.compute_frame()
+            elif fused:
+                t.render_resolve(step * spp_step, spp_step)
             else:
                 sr.render(step * spp_step, spp_step)
                 sr.merge(0)
@@ -521,6 +531,8 @@ def run_b200(args):
             "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl["name"], "width": W, "height": H, "spp_per_step_total": spp_step,
                        "spp_per_step_per_rank": spp_rank, "seed": 0, "jitter": not literal, "sharding": sharding,
+                       "step": ("ptb_render_resolve: accumulate + resolve in one launch" if fused else
+                                "ptb_compute_frame" if literal else "ptb_render_samples + merge/resolve"),
                        "max_depth": wl.get("max_depth", 0), "scene": scene.name if scene is not None else "default (Test.hlsl literals)",
                        "l2": ("no flush: each step streams two 16 B/pixel partial buffers (> 126 MB L2) plus the peers' slabs"
                               if (pipelined and 2 * n_pix * 16 > 126 * 1024 * 1024) else
@@ -531,7 +543,8 @@ def run_b200(args):
             "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": 128, "d2h_bytes_per_step": n_pix * 4,
                     "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps,
-                    "note": "C-ABI calls with host buffers (ptb_render_samples, ptb_resolve, ptb_read_rgba8_async into "
+                    "note": "C-ABI calls with host buffers (" + ("ptb_render_resolve = accumulate + resolve in one launch" if fused else
+                                                                 "ptb_render_samples, ptb_resolve") + ", ptb_read_rgba8_async into "
                             "double-buffered pinned memory; merge over NCCL every step when N>1). The path's only input is "
                             "the parameter block (Test.hlsl reads nothing); output = the RGBA8 frame, every step"},
             "gpu_launches": int(launches),

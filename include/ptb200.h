@@ -128,6 +128,13 @@ void *ptb_device_peer_flags(ptb_context *ctx);   /* this context's rendezvous fl
 int ptb_accum_reset(ptb_context *ctx);
 int ptb_render_samples(ptb_context *ctx, uint32_t first_sample, uint32_t n_samples, int jitter);
 int ptb_resolve(ptb_context *ctx, uint32_t flags);
+/* ptb_render_samples followed by ptb_resolve, as ONE kernel launch where that is possible (literal scene, no row shard,
+ * no PTB_RESOLVE_SRGB): the accumulate kernel resolves each pixel while its sum is still in registers, which saves the
+ * resolve pass's read of the accumulation buffer and a launch per frame.  Same results as the two calls, bit for bit.
+ * The fused form writes a SECOND image buffer and makes it the current one, so that an asynchronous read-back of the
+ * previous frame (ptb_read_rgba8_async) keeps overlapping the next frame's rendering: re-query ptb_device_rgba8 after
+ * every call, and do not combine it with an image exported through ptb_ipc_export. */
+int ptb_render_resolve(ptb_context *ctx, uint32_t first_sample, uint32_t n_samples, int jitter, uint32_t flags);
 uint32_t ptb_accum_spp(const ptb_context *ctx);
 /* Checkpoint / restore of the progressive state (float4 accumulation + spp). */
 int ptb_read_accum(ptb_context *ctx, float *host_dst, size_t pitch_bytes);

@@ -147,6 +147,7 @@ SIGNATURES = {
     "ptb_write_accum": (C.c_int, [_CTX, C.c_void_p, C.c_size_t, C.c_uint32]),
     "ptb_set_accum_buffer": (C.c_int, [_CTX, C.c_void_p]),
     "ptb_set_accum_spp": (C.c_int, [_CTX, C.c_uint32]),
+    "ptb_render_resolve": (C.c_int, [_CTX, C.c_uint32, C.c_uint32, C.c_int, C.c_uint32]),
     "ptb_set_row_shard": (C.c_int, [_CTX, C.c_uint32, C.c_uint32]),
     "ptb_scene_set_wave_samples": (C.c_int, [_CTX, C.c_uint32]),
     "ptb_set_row_shard_bands": (C.c_int, [_CTX, C.c_uint32, C.c_uint32, C.c_uint32]),

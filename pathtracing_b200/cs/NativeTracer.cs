@@ -41,6 +41,7 @@ public sealed unsafe class NativeTracer : IDisposable
     [DllImport(Lib)] private static extern int ptb_accum_reset(IntPtr ctx);
     [DllImport(Lib)] private static extern int ptb_render_samples(IntPtr ctx, uint firstSample, uint nSamples, int jitter);
     [DllImport(Lib)] private static extern int ptb_resolve(IntPtr ctx, uint flags);
+    [DllImport(Lib)] private static extern int ptb_render_resolve(IntPtr ctx, uint firstSample, uint nSamples, int jitter, uint flags);
     [DllImport(Lib)] private static extern uint ptb_accum_spp(IntPtr ctx);
     [DllImport(Lib)] private static extern int ptb_present(IntPtr ctx, uint dstW, uint dstH, uint flags);
     [DllImport(Lib)] private static extern int ptb_read_present(IntPtr ctx, void* hostDst, nuint pitchBytes);
@@ -124,6 +125,9 @@ public sealed unsafe class NativeTracer : IDisposable
     public void RenderSamples(uint first, uint count, bool jitter = true) =>
         Check(_ctx, ptb_render_samples(_ctx, first, count, jitter ? 1 : 0));
     public void Resolve(uint flags = 0) => Check(_ctx, ptb_resolve(_ctx, flags));
+    /// RenderSamples + Resolve as one kernel launch where possible (literal scene, no row shard, no sRGB); same results.
+    public void RenderResolve(uint first, uint count, bool jitter = true, uint flags = 0) =>
+        Check(_ctx, ptb_render_resolve(_ctx, first, count, jitter ? 1 : 0, flags));
     public uint AccumulatedSamples => ptb_accum_spp(_ctx);
 
     public void ReadImage(Span<byte> rgba8)                                              // W*H*4 bytes

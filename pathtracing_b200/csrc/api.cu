@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <utility>
 #include <new>
 
 #include "ptb_internal.h"
@@ -51,6 +52,7 @@ size_t n_pixels(const ptb_context *c) { return (size_t)c->cfg.width * c->cfg.hei
 void free_buffers(ptb_context *c)
 {
     cudaFree(c->buf.rgba8);
+    cudaFree(c->buf.rgba8_alt);
     cudaFree(c->buf.f32);
     cudaFree(c->buf.hit);
     cudaFree(c->buf.accum_owned);
@@ -229,6 +231,7 @@ int ptb_destroy(ptb_context *ctx)
     }
     if (ctx->ev_img_ready) cudaEventDestroy(ctx->ev_img_ready);
     if (ctx->ev_copy_done) cudaEventDestroy(ctx->ev_copy_done);
+    if (ctx->ev_copy_done_alt) cudaEventDestroy(ctx->ev_copy_done_alt);
     if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
     return PTB_OK;
@@ -250,9 +253,9 @@ int ptb_wait(ptb_context *ctx)
 {
     PTB_ENTER(ctx);
     PTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    if (ctx->copy_pending) {
+    if (ctx->copy_pending || ctx->copy_pending_alt) {
         PTB_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
-        ctx->copy_pending = false;
+        ctx->copy_pending = ctx->copy_pending_alt = false;
     }
     if (ctx->peer_flags) {
         uint32_t err = 0;
@@ -348,6 +351,42 @@ int ptb_render_samples(ptb_context *ctx, uint32_t first_sample, uint32_t n_sampl
     }
     PTB_CUDA(ctx, ptb::launch_csmain_accumulate(ctx->k, ctx->buf.accum, first_sample, n_samples, ctx->cfg.seed,
                                                 jitter != 0, ctx->stream));
+    ctx->launches += 1;
+    ctx->accum_spp += n_samples;
+    return PTB_OK;
+}
+
+int ptb_render_resolve(ptb_context *ctx, uint32_t first_sample, uint32_t n_samples, int jitter, uint32_t flags)
+{
+    PTB_ENTER(ctx);
+    if (flags & ~(PTB_RESOLVE_SRGB | PTB_RESOLVE_BGRA))
+        return fail(ctx, PTB_ERR_INVALID, "ptb_render_resolve: unknown flags 0x%x", flags);
+    if (n_samples == 0) return fail(ctx, PTB_ERR_INVALID, "ptb_render_resolve: n_samples is 0");
+    // One launch only where the accumulate kernel touches every pixel the resolve would: the literal scene, no row shard,
+    // no sRGB table.  Everything else takes the two calls this one stands for.
+    const bool fused = !ptb::scene_resident(ctx) && !(flags & PTB_RESOLVE_SRGB) && ctx->k.row_offset == 0 &&
+                       ctx->k.row_stride == 1;
+    if (!fused) {
+        const int rc = ptb_render_samples(ctx, first_sample, n_samples, jitter);
+        return rc != PTB_OK ? rc : ptb_resolve(ctx, flags);
+    }
+    if ((uint64_t)ctx->accum_spp + n_samples > 0xFFFFFFFFull)
+        return fail(ctx, PTB_ERR_INVALID, "ptb_render_resolve: spp counter would overflow");
+    int rc = ensure_accum(ctx);
+    if (rc != PTB_OK) return rc;
+    if (!ctx->buf.rgba8_alt) {
+        PTB_CUDA(ctx, cudaMalloc(&ctx->buf.rgba8_alt, n_pixels(ctx) * sizeof(uint32_t)));
+        PTB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_copy_done_alt, cudaEventDisableTiming));
+    }
+    // the image this launch writes is the one that was current two calls ago: a read-back of it may still be running
+    if (ctx->copy_pending_alt) PTB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_copy_done_alt, 0));
+    PTB_CUDA(ctx, ptb::launch_csmain_accumulate(ctx->k, ctx->buf.accum, first_sample, n_samples, ctx->cfg.seed, jitter != 0,
+                                                ctx->stream, ctx->buf.rgba8_alt, (float)(ctx->accum_spp + n_samples),
+                                                (flags & PTB_RESOLVE_BGRA) != 0));
+    std::swap(ctx->buf.rgba8, ctx->buf.rgba8_alt);
+    std::swap(ctx->ev_copy_done, ctx->ev_copy_done_alt);
+    ctx->copy_pending_alt = ctx->copy_pending;      // a read-back of the image that was current until now
+    ctx->copy_pending = false;                      // the new current image: its old read-back is ordered before this launch
     ctx->launches += 1;
     ctx->accum_spp += n_samples;
     return PTB_OK;

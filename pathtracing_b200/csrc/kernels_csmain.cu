@@ -320,7 +320,8 @@ cudaError_t launch_csmain_frame(const FrameK &k, const Buffers &b, cudaStream_t 
 // loop-invariant and hoisted.
 template <int MODE, bool JITTER>
 __global__ void __launch_bounds__(256) csmain_accumulate(const FrameK k, float4 *__restrict__ accum,
-                                                         uint32_t first_sample, uint32_t n_samples, uint32_t seed)
+                                                         uint32_t first_sample, uint32_t n_samples, uint32_t seed,
+                                                         uint32_t *__restrict__ out8, float spp_total, int bgra)
 {
     const uint32_t x = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t y = shard_row(k.row_offset, k.row_stride, k.row_block, blockIdx.y * blockDim.y + threadIdx.y);   // row shard (multi-GPU tiles)
@@ -437,6 +438,11 @@ __global__ void __launch_bounds__(256) csmain_accumulate(const FrameK k, float4 
     acc.z = fadd(acc.z, sb);
     acc.w = fadd(acc.w, sa);
     accum[pix] = acc;
+    if (out8) {   // launch-uniform: fused resolve (ptb_render_resolve) — the operations of resolve_kernel<false, BGRA>
+        const uint32_t r8 = unorm8(fdiv(acc.x, spp_total)), g8 = unorm8(fdiv(acc.y, spp_total));
+        const uint32_t b8 = unorm8(fdiv(acc.z, spp_total)), a8 = unorm8(fdiv(acc.w, spp_total));
+        out8[pix] = bgra ? (b8 | (g8 << 8) | (r8 << 16) | (a8 << 24)) : (r8 | (g8 << 8) | (b8 << 16) | (a8 << 24));
+    }
 }
 
 // ptb_selftest_exact_math which = 3: brute-force check of certain_miss for this context's parameters.
@@ -494,7 +500,7 @@ cudaError_t selftest_certain_miss(const FrameK &k, unsigned long long *mismatche
 
 template <int MODE>
 static cudaError_t launch_acc_t(const FrameK &k, float4 *accum, uint32_t first, uint32_t n, uint32_t seed,
-                                bool jitter, cudaStream_t s)
+                                bool jitter, cudaStream_t s, uint32_t *out8, float spp_total, bool bgra)
 {
     if (shard_rows(k) == 0) return cudaSuccess;
     // block height: 32x4 pixels measured best at 1080p (rows 8 / 4 / 2 / 1 -> 0.1711 / 0.1693 / 0.1729 / 0.1796 ms per
@@ -506,20 +512,21 @@ static cudaError_t launch_acc_t(const FrameK &k, float4 *accum, uint32_t first, 
     }();
     const dim3 block(32, by);
     const dim3 grid((k.width + 31) / 32, (shard_rows(k) + by - 1) / by);
-    if (jitter) csmain_accumulate<MODE, true><<<grid, block, 0, s>>>(k, accum, first, n, seed);
-    else csmain_accumulate<MODE, false><<<grid, block, 0, s>>>(k, accum, first, n, seed);
+    if (jitter) csmain_accumulate<MODE, true><<<grid, block, 0, s>>>(k, accum, first, n, seed, out8, spp_total, bgra ? 1 : 0);
+    else csmain_accumulate<MODE, false><<<grid, block, 0, s>>>(k, accum, first, n, seed, out8, spp_total, bgra ? 1 : 0);
     return cudaGetLastError();
 }
 
 cudaError_t launch_csmain_accumulate(const FrameK &k, float4 *accum, uint32_t first_sample,
-                                     uint32_t n_samples, uint32_t seed, bool jitter, cudaStream_t s)
+                                     uint32_t n_samples, uint32_t seed, bool jitter, cudaStream_t s,
+                                     uint32_t *out8, float spp_total, bool bgra)
 {
     int mode = pick_mode(k);
     if (n_samples > (1u << 24)) mode = MODE_GENERIC;
     switch (mode) {
-    case MODE_FAST_ON_AXIS: return launch_acc_t<MODE_FAST_ON_AXIS>(k, accum, first_sample, n_samples, seed, jitter, s);
-    case MODE_FAST: return launch_acc_t<MODE_FAST>(k, accum, first_sample, n_samples, seed, jitter, s);
-    default: return launch_acc_t<MODE_GENERIC>(k, accum, first_sample, n_samples, seed, jitter, s);
+    case MODE_FAST_ON_AXIS: return launch_acc_t<MODE_FAST_ON_AXIS>(k, accum, first_sample, n_samples, seed, jitter, s, out8, spp_total, bgra);
+    case MODE_FAST: return launch_acc_t<MODE_FAST>(k, accum, first_sample, n_samples, seed, jitter, s, out8, spp_total, bgra);
+    default: return launch_acc_t<MODE_GENERIC>(k, accum, first_sample, n_samples, seed, jitter, s, out8, spp_total, bgra);
     }
 }
 

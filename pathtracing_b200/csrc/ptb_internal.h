@@ -42,7 +42,8 @@ struct FrameK {
 };
 
 struct Buffers {
-    uint32_t *rgba8 = nullptr;   // W*H packed R8G8B8A8 (Renderer.cs:124)
+    uint32_t *rgba8 = nullptr;   // W*H packed R8G8B8A8 (Renderer.cs:124): the CURRENT image
+    uint32_t *rgba8_alt = nullptr; // second image, allocated by the first ptb_render_resolve (which writes it and swaps)
     float4 *f32 = nullptr;       // W*H float4 (Test.hlsl:1), optional
     int32_t *hit = nullptr;      // W*H hit ids, optional
     float4 *accum = nullptr;     // W*H float4 accumulation (n2)
@@ -58,8 +59,11 @@ cudaError_t launch_csmain_frame(const FrameK &k, const Buffers &b, cudaStream_t 
 // counts, over every pixel classified "certain miss", the jitter positions (8x8 grid incl. both extremes) whose exact
 // discriminant says HIT — must be 0; tested = positions evaluated (ptb_selftest_exact_math which = 3)
 cudaError_t selftest_certain_miss(const FrameK &k, unsigned long long *mismatches, unsigned long long *tested, cudaStream_t s);
+// out8 != nullptr: the launch also resolves every pixel it accumulates (accum / spp_total -> UNORM8, the arithmetic of
+// resolve_kernel without the sRGB table) into out8; bgra selects the byte order
 cudaError_t launch_csmain_accumulate(const FrameK &k, float4 *accum, uint32_t first_sample,
-                                     uint32_t n_samples, uint32_t seed, bool jitter, cudaStream_t s);
+                                     uint32_t n_samples, uint32_t seed, bool jitter, cudaStream_t s,
+                                     uint32_t *out8 = nullptr, float spp_total = 1.0f, bool bgra = false);
 // selftest.cu — exhaustive proofs of the short exact sequences in ptb_math.cuh
 //   which: 0 = sqrt_rn_fast over [2^-20,2^24), 1 = rcp_rn_fast over [2^-12,2^12),
 //          2 = div_rn_uniform(v, D) for v in {0} U [2^-24, 2^17)
@@ -104,6 +108,9 @@ struct ptb_context {
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev_img_ready = nullptr, ev_copy_done = nullptr;
     bool copy_pending = false;
+    // the same pair for buf.rgba8_alt (ptb_render_resolve swaps image, event and flag together)
+    cudaEvent_t ev_copy_done_alt = nullptr;
+    bool copy_pending_alt = false;
     bool timer_open = false;
     uint32_t accum_spp = 0;
     uint64_t launches = 0;

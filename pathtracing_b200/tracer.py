@@ -117,6 +117,12 @@ class NativeTracer:
     def render_samples(self, first_sample: int, n_samples: int, jitter: bool = True) -> None:
         self._ck(self._lib.ptb_render_samples(self._ctx, first_sample, n_samples, int(jitter)))
 
+    def render_resolve(self, first_sample: int, n_samples: int, jitter: bool = True, srgb: bool = False,
+                       bgra: bool = False) -> None:
+        """render_samples + resolve as one launch where possible (literal scene, no row shard, no sRGB); same results."""
+        self._ck(self._lib.ptb_render_resolve(self._ctx, first_sample, n_samples, int(jitter),
+                                              (RESOLVE_SRGB if srgb else 0) | (RESOLVE_BGRA if bgra else 0)))
+
     def resolve(self, srgb: bool = False, bgra: bool = False) -> None:
         self._ck(self._lib.ptb_resolve(self._ctx, (RESOLVE_SRGB if srgb else 0) | (RESOLVE_BGRA if bgra else 0)))
 

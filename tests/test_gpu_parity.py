@@ -390,6 +390,49 @@ def test_async_readback_is_ordered_and_matches_sync(oracle):
     assert np.array_equal(sync, bufs[2])
 
 
+@pytest.mark.parametrize("size", [(640, 360), (333, 77), (1920, 1080)])
+@pytest.mark.parametrize("jitter", [True, False])
+def test_fused_render_resolve_equals_the_two_calls(oracle, size, jitter):
+    """ptb_render_resolve = ptb_render_samples + ptb_resolve in one launch: same accumulation, same image, progressive
+    calls, asynchronous read-backs of consecutive frames (two image buffers), and the unfused fall-backs."""
+    w, h = size
+    p = oracle.frame_params(w, h)
+    spans = [(0, 5), (5, 2), (7, 4), (11, 1)]
+    bufs = [np.zeros((h, w, 4), np.uint8) for _ in spans]
+    with NativeTracer(w, h, seed=6) as t:
+        ptrs = set()
+        for (first, n), buf in zip(spans, bufs):
+            t.render_resolve(first, n, jitter=jitter)
+            ptrs.add(t.device_rgba8())
+            t.read_rgba8_async(buf.ctypes.data)            # overlaps the next call, which writes the OTHER image
+        t.wait()
+        assert len(ptrs) == 2 and t.accum_spp == 12
+        last_sync, acc_gpu = t.read_rgba8(), t.read_accum()
+        t.render_resolve(12, 3, jitter=jitter, bgra=True)
+        bgra = t.read_rgba8()
+        t.render_resolve(15, 2, jitter=jitter, srgb=True)  # sRGB: falls back to the two launches
+        srgb = t.read_rgba8()
+        t.set_row_shard(1, 2)
+        t.render_resolve(17, 1, jitter=jitter)             # row shard: falls back as well
+        shard_img, shard_acc = t.read_rgba8(), t.read_accum()
+    acc = None
+    for (first, n), buf in zip(spans, bufs):
+        acc = oracle.accumulate(p, first, n, 6, jitter, accum=acc)
+        assert np.array_equal(buf, oracle.resolve(acc, first + n)), (first, n)
+    assert np.array_equal(last_sync, bufs[-1]) and eq_bits(acc_gpu, acc)
+    acc = oracle.accumulate(p, 12, 3, 6, jitter, accum=acc)
+    assert np.array_equal(bgra, oracle.resolve(acc, 15, bgra=True))
+    acc = oracle.accumulate(p, 15, 2, 6, jitter, accum=acc)
+    assert np.array_equal(srgb, oracle.resolve(acc, 17, srgb=True))
+    with NativeTracer(w, h, seed=6) as t:                  # the same sequence through the two calls
+        for first, n in spans + [(12, 3), (15, 2)]:
+            t.render_samples(first, n, jitter=jitter)
+        t.set_row_shard(1, 2)
+        t.render_samples(17, 1, jitter=jitter)
+        t.resolve()
+        assert np.array_equal(t.read_rgba8(), shard_img) and eq_bits(t.read_accum(), shard_acc)
+
+
 # ---- multi-GPU partitioning emulated on one device: one context per "rank" -------------------------
 @pytest.mark.parametrize("world,band", [(2, 1), (3, 1), (8, 1), (2, 4), (3, 4), (8, 4), (8, 16), (7, 5)])
 def test_row_shards_merge_to_the_single_device_image(world, band):
