@@ -36,7 +36,7 @@ int main(int argc, char **argv)
                 r.Render(1.0f / 60.0f);                     // the reference's per-frame path
             } else {                                        // progressive: spp jittered samples, resolve
                 ptb_context *c = r.Handle();
-                if (ptb_render_samples(c, f * spp, spp, 1) || ptb_resolve(c, 0) || ptb_wait(c))
+                if (ptb_render_resolve(c, f * spp, spp, 1, 0) || ptb_wait(c))      // accumulate + resolve, one launch
                     throw std::runtime_error(ptb_last_error(c));
             }
         }
