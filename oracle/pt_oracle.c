@@ -217,6 +217,10 @@ void pto_resolve(const float *accum, uint32_t width, uint32_t height, uint32_t s
     const float spp = (float)spp_total;
     const int bgra = (flags & PTO_RESOLVE_BGRA) != 0;
     const int srgb = (flags & PTO_RESOLVE_SRGB) != 0;
+    /* the same Parallel.For analogue as the tracing loops: every pixel is independent */
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static)
+#endif
     for (int64_t i = 0; i < n; ++i) {
         float r = accum[4 * i + 0] / spp, g = accum[4 * i + 1] / spp;
         float b = accum[4 * i + 2] / spp, a = accum[4 * i + 3] / spp;
@@ -237,7 +241,11 @@ void pto_resolve(const float *accum, uint32_t width, uint32_t height, uint32_t s
 void pto_present(const uint8_t *src_rgba8, uint32_t sw, uint32_t sh,
                  uint8_t *dst_bgra8, uint32_t dw, uint32_t dh, uint32_t flags)
 {
-    for (uint32_t j = 0; j < dh; ++j) {
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static)
+#endif
+    for (int64_t jj = 0; jj < (int64_t)dh; ++jj) {
+        const uint32_t j = (uint32_t)jj;
         for (uint32_t i = 0; i < dw; ++i) {
             /* nearest texel of the pixel-centre uv; exact integer form of
              * floor(((i+0.5)/dw) * sw) = floor((2i+1)*sw / (2dw)) */

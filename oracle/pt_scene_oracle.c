@@ -498,13 +498,25 @@ int64_t pto_scene_frame(const pto_scene *s, const pto_accel *a, uint32_t seed, f
 void pto_scene_accumulate(const pto_scene *s, const pto_accel *a, uint32_t first_sample,
                           uint32_t n_samples, uint32_t seed, int jitter, float *accum, int nthreads)
 {
+    pto_scene_accumulate_rows(s, a, first_sample, n_samples, seed, jitter, accum, 0, 1, 1, nthreads);
+}
+
+/* The same for one interleaved row shard only (the rows ptb_set_row_shard_bands selects: bands of row_block rows,
+ * band g = y / row_block belongs to the shard when g % row_stride == row_offset); other rows of accum are untouched. */
+void pto_scene_accumulate_rows(const pto_scene *s, const pto_accel *a, uint32_t first_sample,
+                               uint32_t n_samples, uint32_t seed, int jitter, float *accum,
+                               uint32_t row_offset, uint32_t row_stride, uint32_t row_block, int nthreads)
+{
     const int64_t W = s->width, H = s->height;
+    if (row_stride == 0) row_stride = 1;
+    if (row_block == 0) row_block = 1;
 #ifdef _OPENMP
     if (nthreads <= 0) nthreads = omp_get_max_threads();
 #pragma omp parallel for schedule(dynamic, 1) num_threads(nthreads)
 #endif
     for (int64_t y = 0; y < H; ++y)
         for (int64_t x = 0; x < W; ++x) {
+            if (((uint32_t)y / row_block) % row_stride != row_offset) break;
             float *acc = accum + 4 * (y * W + x);
             for (uint32_t k = 0; k < n_samples; ++k) {
                 float c[3];

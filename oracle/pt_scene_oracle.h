@@ -106,6 +106,10 @@ int64_t pto_scene_frame(const pto_scene *s, const pto_accel *a, uint32_t seed, f
 /* accum[pixel] += (rgb,1) for samples first..first+n-1, in sample order. */
 void pto_scene_accumulate(const pto_scene *s, const pto_accel *a, uint32_t first_sample,
                           uint32_t n_samples, uint32_t seed, int jitter, float *accum, int nthreads);
+/* One interleaved row shard only (ptb_set_row_shard_bands semantics); other rows of accum are untouched. */
+void pto_scene_accumulate_rows(const pto_scene *s, const pto_accel *a, uint32_t first_sample,
+                               uint32_t n_samples, uint32_t seed, int jitter, float *accum,
+                               uint32_t row_offset, uint32_t row_stride, uint32_t row_block, int nthreads);
 
 /* Exposed pieces of the spec (unit-tested on their own, restated by the CUDA path). */
 void pto_sincos2pi(float u, float *sn, float *cs);

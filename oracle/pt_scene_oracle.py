@@ -50,6 +50,9 @@ def lib() -> C.CDLL:
         L.pto_scene_accumulate.argtypes = [P(SceneC), C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int,
                                            C.c_void_p, C.c_int]
         L.pto_scene_accumulate.restype = None
+        L.pto_scene_accumulate_rows.argtypes = [P(SceneC), C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int,
+                                                C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int]
+        L.pto_scene_accumulate_rows.restype = None
         L.pto_sincos2pi.argtypes = [C.c_float, P(C.c_float), P(C.c_float)]
         L.pto_sincos2pi.restype = None
         L.pto_unit_vector.argtypes = [C.c_float, C.c_float, P(C.c_float)]
@@ -118,12 +121,14 @@ class SceneOracle:
         return {"f32": f32, "rgba8": rgba8, "hit": hit, "hits": int(n)}
 
     def accumulate(self, first_sample: int, n_samples: int, seed: int = 0, jitter: bool = True, accum=None,
-                   brute: bool = False, nthreads: int = 0):
+                   brute: bool = False, nthreads: int = 0, rows=None):
+        """rows = (row_offset, row_stride, rows_per_band): only that interleaved row shard (ptb_set_row_shard_bands)."""
         if accum is None:
             accum = np.zeros((self.height, self.width, 4), np.float32)
         assert accum.dtype == np.float32 and accum.flags.c_contiguous
-        lib().pto_scene_accumulate(C.byref(self.c), None if brute else self._accel, first_sample, n_samples, seed,
-                                   int(jitter), accum.ctypes.data, nthreads)
+        off, stride, block = rows if rows is not None else (0, 1, 1)
+        lib().pto_scene_accumulate_rows(C.byref(self.c), None if brute else self._accel, first_sample, n_samples, seed,
+                                        int(jitter), accum.ctypes.data, off, stride, block, nthreads)
         return accum
 
 
