@@ -48,6 +48,14 @@ typedef struct ptb_context ptb_context;   /* opaque; owns all device memory and 
 #define PTB_CFG_FORCE_IEEE    0x8u  /* always run the literal IEEE-intrinsic kernels (never the shortened, proven-equal
                                        FMA sequences); results are bit-identical either way — for tests / A-B timing */
 
+#define PTB_CFG_SPIRV_ARITH   0x10u /* evaluate the operation list of the reference's CHECKED-IN compiled module
+                                       Assets/Shaders/Compiled/Ray/Test.spirv (what Renderer.cs:356-357 loads) instead of
+                                       the source order of Test.hlsl: uv by the folded reciprocal fl(1/1080) [general:
+                                       fl(1/div)], disc = Fma(b, b, a*-3), -b-s = Fma(d.z, -2, -s).  Literal scene only
+                                       (camera / sphere are folded into the module).  Same hit mask as the default
+                                       arithmetic, radiance within 3.4e-5 relative at 1080p; bit-identical to the numpy
+                                       evaluation of the module's words (tests/test_spirv_pin.py, test_gpu_spirv.py) */
+
 /* Parameters that are literals in the reference (Test.hlsl:6,8,12,13; App.cs:27).
  * ptb_default_config fills them so that width=1920,height=1080 reproduces the reference. */
 typedef struct ptb_config {
@@ -290,7 +298,8 @@ int ptb_timer_end(ptb_context *ctx, float *elapsed_ms);     /* synchronises */
 /* Kernels launched by this context since creation (for bench.py's gpu_launches). */
 uint64_t ptb_launch_count(const ptb_context *ctx);
 /* Which CSMain kernel variant this context runs: 0 = literal IEEE intrinsics, 1 = shortened exact
- * sequences, 2 = shortened + camera-on-axis specialisation.  All three produce identical bits. */
+ * sequences, 2 = shortened + camera-on-axis specialisation — all three produce identical bits; 3 = the as-compiled
+ * operation list of Test.spirv (PTB_CFG_SPIRV_ARITH). */
 int ptb_kernel_mode(const ptb_context *ctx);
 /* Proof by exhaustion, on the device, that a shortened sequence equals the IEEE intrinsic on its
  * whole domain: which = 0 sqrt over [2^-20,2^24), 1 reciprocal over [2^-12,2^12), 2 division of

@@ -115,6 +115,79 @@ int pto_csmain_sample(const pto_frame_params *p, float px, float py,
     return 0;
 }
 
+/* ---- the "as-compiled" variant: Assets/Shaders/Compiled/Ray/Test.spirv, instruction by instruction ----
+ * The reference checks in the DXC output of Test.hlsl (the module Renderer.cs:356-357 actually loads).  Its
+ * operation list differs from the source in four places (asserted word by word against the
+ * file in tests/test_spirv_pin.py):
+ *   [34]      id * fl(1/1080)          (constant 0x3A72B9D6) instead of id / 1080
+ *   [43]      b = 2.0 * d.z            (oc . d folded for oc = (0,0,1); exact, same value as the source form)
+ *   [44],[45] disc = Fma(b, b, a * -3) instead of b*b - (4a)*0.75   (ONE rounding less)
+ *   [52]      -b - s = Fma(d.z, -2, -s)                             (2*d.z is exact: same value as the source form)
+ *   [56]      P = (0,0,1) + t*d, centre subtraction folded away     (centre = 0: same value)
+ * Implementation-defined precisions (Normalize, Sqrt, FDiv, Dot order) are fixed as in the frozen spec above.
+ * Only defined for the literal scene (cam (0,0,1), centre 0, r 0.5); the divisor generalises to fl(1/div). */
+int pto_csmain_sample_spirv(const pto_frame_params *p, float px, float py,
+                            float colour[4], float *disc_out, float *t_out)
+{
+    const float kx = 1.0f / p->uv_div_x, ky = 1.0f / p->uv_div_y;    /* [26] fl(1/1080) = 0x3A72B9D6 */
+    float uvx = (px * kx) * 2.0f - 1.0f;                             /* [34] [35] [36] */
+    float uvy = (py * ky) * 2.0f - 1.0f;
+    float raw[3] = { uvx, uvy, -1.0f };
+    float d[3];
+    normalize3(raw, d);                                              /* [40] */
+    float a = dot3(d, d);                                            /* [41] */
+    float b = 2.0f * d[2];                                           /* [43] */
+    float m3a = a * -3.0f;                                           /* [44] */
+    float disc = fmaf(b, b, m3a);                                    /* [45] */
+    if (disc_out) *disc_out = disc;
+    if (disc > 0.0f) {                                               /* [46] */
+        float s = sqrtf(disc);                                       /* [50] */
+        float num = fmaf(d[2], -2.0f, -s);                           /* [51] [52] */
+        float t = num / (2.0f * a);                                  /* [53] [54] */
+        if (t_out) *t_out = t;
+        float P[3] = { 0.0f + d[0] * t, 0.0f + d[1] * t, 1.0f + d[2] * t };   /* [55] [56] */
+        float n[3];
+        normalize3(P, n);                                            /* [57] */
+        colour[0] = n[0] * 0.5f + 0.5f;                              /* [58] [59] */
+        colour[1] = n[1] * 0.5f + 0.5f;
+        colour[2] = n[2] * 0.5f + 0.5f;
+        colour[3] = 1.0f;                                            /* [63] */
+        return 1;
+    }
+    if (t_out) *t_out = 0.0f;
+    colour[0] = uvx; colour[1] = uvy; colour[2] = 0.0f; colour[3] = 1.0f;   /* [64] */
+    return 0;
+}
+
+/* Whole frame of the as-compiled variant (same outputs as pto_csmain_frame). */
+int64_t pto_csmain_frame_spirv(const pto_frame_params *p, float *out_f32, uint8_t *out_rgba8,
+                               int32_t *out_hit, int nthreads)
+{
+    const int64_t W = p->width, H = p->height;
+    int64_t hits = 0;
+#ifdef _OPENMP
+    if (nthreads <= 0) nthreads = omp_get_max_threads();
+#pragma omp parallel for schedule(dynamic, 4) num_threads(nthreads) reduction(+ : hits)
+#endif
+    for (int64_t y = 0; y < H; ++y) {
+        for (int64_t x = 0; x < W; ++x) {
+            float col[4];
+            int hit = pto_csmain_sample_spirv(p, (float)x, (float)y, col, NULL, NULL);
+            int64_t i = y * W + x;
+            hits += hit;
+            if (out_f32) memcpy(out_f32 + 4 * i, col, sizeof col);
+            if (out_rgba8) {
+                out_rgba8[4 * i + 0] = pto_unorm8(col[0]);
+                out_rgba8[4 * i + 1] = pto_unorm8(col[1]);
+                out_rgba8[4 * i + 2] = pto_unorm8(col[2]);
+                out_rgba8[4 * i + 3] = pto_unorm8(col[3]);
+            }
+            if (out_hit) out_hit[i] = hit ? 0 : -1;
+        }
+    }
+    return hits;
+}
+
 /* Effective image store of Test.hlsl:39 into an R8G8B8A8Unorm image
  * (Graphics/Renderer.cs:124,167): NaN->0, clamp [0,1], scale 255, round-nearest-even. */
 uint8_t pto_unorm8(float v)
@@ -183,6 +256,13 @@ float pto_bits_to_unit(uint32_t w)
 void pto_accumulate(const pto_frame_params *p, uint32_t first_sample, uint32_t n_samples,
                     uint32_t seed, int jitter, float *accum, int nthreads)
 {
+    pto_accumulate_v(p, 0, first_sample, n_samples, seed, jitter, accum, nthreads);
+}
+
+/* variant 0 = the frozen source-order spec (pto_csmain_sample), 1 = the as-compiled one (pto_csmain_sample_spirv). */
+void pto_accumulate_v(const pto_frame_params *p, int variant, uint32_t first_sample, uint32_t n_samples,
+                      uint32_t seed, int jitter, float *accum, int nthreads)
+{
     const int64_t W = p->width, H = p->height;
 #ifdef _OPENMP
     if (nthreads <= 0) nthreads = omp_get_max_threads();
@@ -201,7 +281,8 @@ void pto_accumulate(const pto_frame_params *p, uint32_t first_sample, uint32_t n
                     jy = pto_bits_to_unit(v[1]);
                 }
                 float col[4];
-                pto_csmain_sample(p, (float)x + jx, (float)y + jy, col, NULL, NULL);
+                if (variant) pto_csmain_sample_spirv(p, (float)x + jx, (float)y + jy, col, NULL, NULL);
+                else pto_csmain_sample(p, (float)x + jx, (float)y + jy, col, NULL, NULL);
                 sum[0] += col[0]; sum[1] += col[1]; sum[2] += col[2]; sum[3] += col[3];
             }
             float *a = accum + 4 * (int64_t)pix;

@@ -10,12 +10,21 @@
  * present path per Assets/Shaders/Source/Basic/PixelShader.hlsl:8-19 and
  * Graphics/SwapChain.cs:154-165 (B8G8R8A8Srgb).
  *
- * PARITY PIN STATUS: the reference ships no tests, golden vectors or CPU
- * implementation and its HLSL/Vulkan path cannot run on this
- * box, so with respect to the reference's own fixtures this oracle is
- * "parity unpinned".  It IS pinned to the survey-derived known answers of
- * SURVEY.md Appendix B (hit counts, hit bbox, per-pixel float bit patterns), which
- * were derived from the shader source with the rounding spec frozen below.
+ * PARITY PIN STATUS: the reference ships no tests, golden vectors or CPU implementation
+ *  and its HLSL/Vulkan path cannot run on this box.  What it DOES hold is
+ * the compiled module it loads, Assets/Shaders/Compiled/Ray/Test.spirv (sha256 051e3943...c9f0f).
+ * The oracle is pinned to that file (tests/test_spirv_pin.py, oracle/spirv_eval.py): the
+ * module's words are decoded, its constants (fl(1/1080) = 0x3A72B9D6, -3.0, -2.0, 0.5) and
+ * operation order asserted, and its operation list evaluated instruction by instruction in
+ * numpy float32.  Result: pto_csmain_frame_spirv (the "as-compiled" variant below) equals that
+ * evaluation bit for bit; pto_csmain_frame (the frozen source-order spec the CUDA kernels
+ * reproduce) has the IDENTICAL hit mask at 320x180, 1920x1080, 1920x1088 and 3840x2160 and
+ * radiance within 3.44e-5 relative at 1080p (north_star bar: 1e-4).  The precision of
+ * Normalize / Sqrt / FDiv / Dot is implementation-defined in SPIR-V and fixed here by the
+ * rounding spec, so the pin is "same operation list, stated roundings", not a run of a Vulkan
+ * driver.  Additionally pinned to the survey-derived known answers of SURVEY.md Appendix B
+ * (hit counts, hit bbox, per-pixel float bit patterns).  Stages n1-n8 (jitter, accumulation,
+ * scenes) have no reference counterpart at all and stay "parity unpinned".
  *
  * Rounding spec (frozen): IEEE-754 binary32, round-to-nearest-even on every single
  * operation, NO fused multiply-add unless fmaf() is written explicitly, left-to-right
@@ -58,6 +67,15 @@ int pto_csmain_sample(const pto_frame_params *p, float px, float py,
 int64_t pto_csmain_frame(const pto_frame_params *p, float *out_f32, uint8_t *out_rgba8,
                          int32_t *out_hit, int nthreads);
 
+/* The "as-compiled" variant: the operation list of the reference's checked-in
+ * Assets/Shaders/Compiled/Ray/Test.spirv (reciprocal multiply for the uv division, the two Fma's, folded
+ * constants), literal scene only.  Same hit mask as the frozen source-order spec at every size tested,
+ * radiance within 3.4e-5 relative at 1080p (tests/test_spirv_pin.py). */
+int pto_csmain_sample_spirv(const pto_frame_params *p, float px, float py,
+                            float colour[4], float *disc_out, float *t_out);
+int64_t pto_csmain_frame_spirv(const pto_frame_params *p, float *out_f32, uint8_t *out_rgba8,
+                               int32_t *out_hit, int nthreads);
+
 /* f32 -> UNORM8 store conversion: NaN -> 0, clamp to [0,1], *255, RNE. */
 uint8_t pto_unorm8(float v);
 /* sRGB OETF then UNORM8 (what a B8G8R8A8Srgb attachment does on write). */
@@ -77,6 +95,9 @@ float pto_bits_to_unit(uint32_t w);
  * jitter == 0 -> jx = jy = 0 (reduces to a1-a5 exactly). */
 void pto_accumulate(const pto_frame_params *p, uint32_t first_sample, uint32_t n_samples,
                     uint32_t seed, int jitter, float *accum, int nthreads);
+/* variant 0 = pto_accumulate; 1 = the same loop over the as-compiled sample (pto_csmain_sample_spirv). */
+void pto_accumulate_v(const pto_frame_params *p, int variant, uint32_t first_sample, uint32_t n_samples,
+                      uint32_t seed, int jitter, float *accum, int nthreads);
 
 /* resolve: out = accum * (1/spp) via division accum/ (float)spp, then UNORM8 (flags&1: sRGB
  * OETF first), channel order RGBA (flags&2: BGRA). */

@@ -52,6 +52,10 @@ def lib() -> C.CDLL:
         L.pto_csmain_sample.restype = C.c_int
         L.pto_csmain_frame.argtypes = [P(FrameParams), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.pto_csmain_frame.restype = C.c_int64
+        L.pto_csmain_sample_spirv.argtypes = L.pto_csmain_sample.argtypes
+        L.pto_csmain_sample_spirv.restype = C.c_int
+        L.pto_csmain_frame_spirv.argtypes = L.pto_csmain_frame.argtypes
+        L.pto_csmain_frame_spirv.restype = C.c_int64
         L.pto_unorm8.argtypes = [C.c_float]
         L.pto_unorm8.restype = C.c_uint8
         L.pto_srgb8.argtypes = [C.c_float]
@@ -63,6 +67,9 @@ def lib() -> C.CDLL:
         L.pto_accumulate.argtypes = [P(FrameParams), C.c_uint32, C.c_uint32, C.c_uint32, C.c_int,
                                      C.c_void_p, C.c_int]
         L.pto_accumulate.restype = None
+        L.pto_accumulate_v.argtypes = [P(FrameParams), C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int,
+                                       C.c_void_p, C.c_int]
+        L.pto_accumulate_v.restype = None
         L.pto_resolve.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
         L.pto_resolve.restype = None
         L.pto_present.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint32,
@@ -90,21 +97,22 @@ def frame_params(width: int, height: int, uv_div=None, cam=None, centre=None, ra
     return p
 
 
-def csmain_sample(p: FrameParams, px: float, py: float):
-    """-> (hit, colour float32[4], disc, t)"""
+def csmain_sample(p: FrameParams, px: float, py: float, spirv: bool = False):
+    """-> (hit, colour float32[4], disc, t).  spirv: the as-compiled variant (Compiled/Ray/Test.spirv op list)."""
     col = (C.c_float * 4)()
     disc, t = C.c_float(), C.c_float()
-    hit = lib().pto_csmain_sample(C.byref(p), px, py, col, C.byref(disc), C.byref(t))
+    fn = lib().pto_csmain_sample_spirv if spirv else lib().pto_csmain_sample
+    hit = fn(C.byref(p), px, py, col, C.byref(disc), C.byref(t))
     return hit, np.array(col[:], dtype=np.float32), np.float32(disc.value), np.float32(t.value)
 
 
-def csmain_frame(p: FrameParams, want_f32=True, want_rgba8=True, want_hit=True, nthreads=0):
-    """-> dict(hits, f32 (H,W,4), rgba8 (H,W,4), hit (H,W))"""
+def csmain_frame(p: FrameParams, want_f32=True, want_rgba8=True, want_hit=True, nthreads=0, spirv: bool = False):
+    """-> dict(hits, f32 (H,W,4), rgba8 (H,W,4), hit (H,W)).  spirv: the as-compiled variant."""
     W, H = p.width, p.height
     f32 = np.empty((H, W, 4), np.float32) if want_f32 else None
     u8 = np.empty((H, W, 4), np.uint8) if want_rgba8 else None
     hit = np.empty((H, W), np.int32) if want_hit else None
-    n = lib().pto_csmain_frame(C.byref(p),
+    n = (lib().pto_csmain_frame_spirv if spirv else lib().pto_csmain_frame)(C.byref(p),
                                f32.ctypes.data if want_f32 else None,
                                u8.ctypes.data if want_rgba8 else None,
                                hit.ctypes.data if want_hit else None, nthreads)
@@ -112,11 +120,12 @@ def csmain_frame(p: FrameParams, want_f32=True, want_rgba8=True, want_hit=True, 
 
 
 def accumulate(p: FrameParams, first_sample: int, n_samples: int, seed: int, jitter: bool,
-               accum: np.ndarray | None = None, nthreads=0) -> np.ndarray:
+               accum: np.ndarray | None = None, nthreads=0, spirv: bool = False) -> np.ndarray:
     if accum is None:
         accum = np.zeros((p.height, p.width, 4), np.float32)
     assert accum.dtype == np.float32 and accum.flags.c_contiguous
-    lib().pto_accumulate(C.byref(p), first_sample, n_samples, seed, int(jitter), accum.ctypes.data, nthreads)
+    lib().pto_accumulate_v(C.byref(p), 1 if spirv else 0, first_sample, n_samples, seed, int(jitter),
+                           accum.ctypes.data, nthreads)
     return accum
 
 

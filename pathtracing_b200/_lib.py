@@ -25,6 +25,7 @@ CFG_KEEP_F32 = 0x1
 CFG_KEEP_HIT_IDS = 0x2
 CFG_EXTERNAL_STREAM = 0x4
 CFG_FORCE_IEEE = 0x8
+CFG_SPIRV_ARITH = 0x10
 RESOLVE_SRGB = 0x1
 RESOLVE_BGRA = 0x2
 

@@ -83,7 +83,8 @@ void derive_fast_flags(ptb_context *c)
     k.on_axis = 0;
     k.cm_on = 0;
     k.cm_sx = k.cm_sy = k.cm_K = 0.0f;
-    if (c->cfg.flags & PTB_CFG_FORCE_IEEE) return;
+    k.spirv = (c->cfg.flags & PTB_CFG_SPIRV_ARITH) ? 1u : 0u;
+    if (c->cfg.flags & (PTB_CFG_FORCE_IEEE | PTB_CFG_SPIRV_ARITH)) return;
     const float vals[] = {k.cam[0], k.cam[1], k.cam[2], k.centre[0], k.centre[1], k.centre[2], k.radius,
                           k.oc[0], k.oc[1], k.oc[2], k.c, k.c4, k.inv_div_x, k.inv_div_y};
     for (float v : vals)
@@ -152,8 +153,15 @@ int ptb_create(const ptb_config *cfg, ptb_context **out_ctx)
         return fail(nullptr, PTB_ERR_UNSUPPORTED, "ptb_create: %ux%u exceeds 2^30 pixels", cfg->width, cfg->height);
     if (!(cfg->uv_div_x != 0.0f) || !(cfg->uv_div_y != 0.0f))
         return fail(nullptr, PTB_ERR_INVALID, "ptb_create: uv divisor must be non-zero");
-    if (cfg->flags & ~(PTB_CFG_KEEP_F32 | PTB_CFG_KEEP_HIT_IDS | PTB_CFG_EXTERNAL_STREAM | PTB_CFG_FORCE_IEEE))
+    if (cfg->flags & ~(PTB_CFG_KEEP_F32 | PTB_CFG_KEEP_HIT_IDS | PTB_CFG_EXTERNAL_STREAM | PTB_CFG_FORCE_IEEE | PTB_CFG_SPIRV_ARITH))
         return fail(nullptr, PTB_ERR_INVALID, "ptb_create: unknown flags 0x%x", cfg->flags);
+    if ((cfg->flags & PTB_CFG_SPIRV_ARITH) &&
+        !(cfg->cam[0] == 0.0f && cfg->cam[1] == 0.0f && cfg->cam[2] == 1.0f && cfg->centre[0] == 0.0f && cfg->centre[1] == 0.0f &&
+          cfg->centre[2] == 0.0f && cfg->radius == 0.5f))
+        return fail(nullptr, PTB_ERR_UNSUPPORTED, "ptb_create: PTB_CFG_SPIRV_ARITH follows the compiled module, which has the "
+                    "literal camera (0,0,1) and sphere (0,0,0; 0.5) of Test.hlsl:8,12-13 folded in");
+    if (cfg->max_depth > 1024u)
+        return fail(nullptr, PTB_ERR_INVALID, "ptb_create: max_depth %u exceeds the limit of 1024", cfg->max_depth);
 
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
@@ -632,6 +640,7 @@ uint64_t ptb_launch_count(const ptb_context *ctx) { return ctx ? ctx->launches :
 int ptb_kernel_mode(const ptb_context *ctx)
 {
     if (!ctx) return fail(nullptr, PTB_ERR_INVALID, "ptb_kernel_mode: ctx is NULL");
+    if (ctx->k.spirv) return 3;
     return ctx->k.fast ? (ctx->k.on_axis ? 2 : 1) : 0;
 }
 

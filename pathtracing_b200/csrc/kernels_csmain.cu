@@ -21,7 +21,12 @@
 
 namespace ptb {
 
-enum Mode { MODE_GENERIC = 0, MODE_FAST = 1, MODE_FAST_ON_AXIS = 2 };
+// MODE_SPIRV: the operation list of the reference's checked-in compiled module Assets/Shaders/Compiled/Ray/Test.spirv
+// (reciprocal multiply for the uv division, disc = Fma(b, b, a * -3), -b - s = Fma(d.z, -2, -s), folded constants;
+// PTB_CFG_SPIRV_ARITH, literal scene only) with literal IEEE intrinsics — bit-identical to the numpy evaluation of the
+// module's words (tests/test_spirv_pin.py, tests/test_gpu_spirv.py).
+enum Mode { MODE_GENERIC = 0, MODE_FAST = 1, MODE_FAST_ON_AXIS = 2, MODE_SPIRV = 3 };
+template <int MODE> struct ModeTraits { static constexpr bool fast = MODE == MODE_FAST || MODE == MODE_FAST_ON_AXIS; };
 
 // Launch-uniform subexpressions, evaluated once on the device with the same intrinsics.
 __global__ void prepare_terms_kernel(FrameK *k)
@@ -59,6 +64,7 @@ template <int MODE>
 __device__ __forceinline__ float screen_uv(float p, float div, float inv_div)
 {
     if (MODE == MODE_GENERIC) return fsub(fmul(fdiv(p, div), 2.0f), 1.0f);
+    if (MODE == MODE_SPIRV) return fsub(fmul(fmul(p, inv_div), 2.0f), 1.0f);   // Test.spirv [34]-[36]: id * fl(1/1080)
     // q*2 is exact, so one FMA rounds exactly like (q*2) - 1.
     return ffma(div_rn_uniform(p, div, inv_div), 2.0f, -1.0f);
 }
@@ -69,7 +75,26 @@ __device__ __forceinline__ bool csmain_shade(const FrameK &k, float uvx, float u
 {
     V3 d;
     float a, b, disc;
-    if (MODE == MODE_GENERIC) {
+    if (MODE == MODE_SPIRV) {
+        // Test.spirv, result ids in brackets; cam (0,0,1), centre 0, r 0.5 are folded into the module
+        d = normalize3(V3{uvx, uvy, -1.0f});                                   // [40]
+        a = dot3(d, d);                                                        // [41]
+        b = fmul(2.0f, d.z);                                                   // [43]
+        disc = ffma(b, b, fmul(a, -3.0f));                                     // [44] [45]
+        if (disc > 0.0f) {                                                     // [46]
+            const float s = fsqrt(disc);                                       // [50]
+            const float t = fdiv(ffma(d.z, -2.0f, -s), fmul(2.0f, a));         // [51]-[54]
+            const V3 n = normalize3(V3{fadd(0.0f, fmul(d.x, t)), fadd(0.0f, fmul(d.y, t)), fadd(1.0f, fmul(d.z, t))});   // [55]-[57]
+            r = fadd(fmul(n.x, 0.5f), 0.5f);                                   // [58] [59]
+            g = fadd(fmul(n.y, 0.5f), 0.5f);
+            bl = fadd(fmul(n.z, 0.5f), 0.5f);
+            return true;
+        }
+        r = uvx;                                                               // [64]
+        g = uvy;
+        bl = 0.0f;
+        return false;
+    } else if (MODE == MODE_GENERIC) {
         d = normalize3(V3{uvx, uvy, -1.0f});                                   // :10
         a = dot3(d, d);                                                        // :17
         b = fmul(2.0f, dot3(V3{k.oc[0], k.oc[1], k.oc[2]}, d));                // :18
@@ -223,7 +248,7 @@ __global__ void __launch_bounds__(256) csmain_frame_vec4(const FrameK k, uint4 *
     uint32_t px8[4];
     int32_t hid[4];
     const size_t q = (size_t)y * wq + xq;
-    if (MODE == MODE_GENERIC) {
+    if (!ModeTraits<MODE>::fast) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const float uvx = screen_uv<MODE>(__uint2float_rn(xq * 4u + i), k.div_x, k.inv_div_x);
@@ -284,7 +309,11 @@ static uint32_t shard_rows(const FrameK &k)
     return shard_row_count(k.height, k.row_offset, k.row_stride, k.row_block);
 }
 
-static int pick_mode(const FrameK &k) { return k.fast ? (k.on_axis ? MODE_FAST_ON_AXIS : MODE_FAST) : MODE_GENERIC; }
+static int pick_mode(const FrameK &k)
+{
+    if (k.spirv) return MODE_SPIRV;
+    return k.fast ? (k.on_axis ? MODE_FAST_ON_AXIS : MODE_FAST) : MODE_GENERIC;
+}
 
 template <int MODE>
 static cudaError_t launch_frame_t(const FrameK &k, const Buffers &b, cudaStream_t s)
@@ -307,6 +336,7 @@ cudaError_t launch_csmain_frame(const FrameK &k, const Buffers &b, cudaStream_t 
     switch (pick_mode(k)) {
     case MODE_FAST_ON_AXIS: return launch_frame_t<MODE_FAST_ON_AXIS>(k, b, s);
     case MODE_FAST: return launch_frame_t<MODE_FAST>(k, b, s);
+    case MODE_SPIRV: return launch_frame_t<MODE_SPIRV>(k, b, s);
     default: return launch_frame_t<MODE_GENERIC>(k, b, s);
     }
 }
@@ -336,8 +366,9 @@ __global__ void __launch_bounds__(256) csmain_accumulate(const FrameK k, float4 
 
     float sr = 0.0f, sg = 0.0f, sb = 0.0f, sa = 0.0f;
     uint32_t i = 0;
-    const bool lean = MODE != MODE_GENERIC && certain_miss(k, fx, fy);   // every sample of this pixel misses
-    if (MODE != MODE_GENERIC && JITTER && lean) {
+    constexpr bool FAST = ModeTraits<MODE>::fast;
+    const bool lean = FAST && certain_miss(k, fx, fy);   // every sample of this pixel misses
+    if (FAST && JITTER && lean) {
         // certain-miss pixels (most of the frame): their own loop, so that the per-pixel invariant `lean` is not tested
         // per iteration; Test.hlsl:36 for both samples, nothing else to evaluate.  Same operations, same order.
 #pragma unroll 2
@@ -367,7 +398,7 @@ __global__ void __launch_bounds__(256) csmain_accumulate(const FrameK k, float4 
             sg = fadd(fadd(sg, uvy2.x), uvy2.y);
         }
     }
-    if (MODE != MODE_GENERIC && JITTER) {
+    if (FAST && JITTER) {
         // two samples per iteration in FP32x2 lanes; the sums stay sequential in sample order
         for (; i + 2 <= n_samples; i += 2) {
             uint32_t ax = vx0, ay = (first_sample + i) * 1664525u + 1013904223u, az = vz0;
@@ -423,7 +454,7 @@ __global__ void __launch_bounds__(256) csmain_accumulate(const FrameK k, float4 
         const bool h = csmain_shade<MODE>(k, uvx, uvy, r, g, b);
         sr = fadd(sr, r);
         sg = fadd(sg, g);
-        if (MODE == MODE_GENERIC) {
+        if (!FAST) {
             sb = fadd(sb, b);
             sa = fadd(sa, 1.0f);
         } else if (h) {
@@ -431,7 +462,7 @@ __global__ void __launch_bounds__(256) csmain_accumulate(const FrameK k, float4 
         }
     }
     // alpha: n_samples sequential additions of 1.0 are exact up to 2^24 (checked by the launcher)
-    if (MODE != MODE_GENERIC) sa = __uint2float_rn(n_samples);
+    if (FAST) sa = __uint2float_rn(n_samples);
     float4 acc = accum[pix];
     acc.x = fadd(acc.x, sr);
     acc.y = fadd(acc.y, sg);
@@ -522,10 +553,11 @@ cudaError_t launch_csmain_accumulate(const FrameK &k, float4 *accum, uint32_t fi
                                      uint32_t *out8, float spp_total, bool bgra)
 {
     int mode = pick_mode(k);
-    if (n_samples > (1u << 24)) mode = MODE_GENERIC;
+    if (n_samples > (1u << 24) && mode != MODE_SPIRV) mode = MODE_GENERIC;
     switch (mode) {
     case MODE_FAST_ON_AXIS: return launch_acc_t<MODE_FAST_ON_AXIS>(k, accum, first_sample, n_samples, seed, jitter, s, out8, spp_total, bgra);
     case MODE_FAST: return launch_acc_t<MODE_FAST>(k, accum, first_sample, n_samples, seed, jitter, s, out8, spp_total, bgra);
+    case MODE_SPIRV: return launch_acc_t<MODE_SPIRV>(k, accum, first_sample, n_samples, seed, jitter, s, out8, spp_total, bgra);
     default: return launch_acc_t<MODE_GENERIC>(k, accum, first_sample, n_samples, seed, jitter, s, out8, spp_total, bgra);
     }
 }

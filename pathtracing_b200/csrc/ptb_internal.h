@@ -35,6 +35,7 @@ struct FrameK {
     // launch-uniform validity of the short exact sequences (api.cu: derive_fast_flags)
     uint32_t fast;                // 1: uv division / sqrt / rcp domains verified for these parameters
     uint32_t on_axis;             // 1: oc.x == oc.y == 0 and oc.z is a moderate normal number
+    uint32_t spirv;               // 1: PTB_CFG_SPIRV_ARITH — the as-compiled operation list of Compiled/Ray/Test.spirv
     // conservative per-pixel "every sample of this pixel misses" classification (kernels_csmain.cu: certain_miss)
     uint32_t cm_on;               // 1: enabled (fast mode, finite terms)
     float cm_sx, cm_sy;           // 2/div: uv per pixel

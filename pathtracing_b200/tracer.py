@@ -13,7 +13,7 @@ from typing import Optional, Sequence
 import numpy as np
 
 from . import _lib
-from ._lib import (CFG_EXTERNAL_STREAM, CFG_FORCE_IEEE, CFG_KEEP_F32, CFG_KEEP_HIT_IDS, RESOLVE_BGRA, RESOLVE_SRGB,
+from ._lib import (CFG_EXTERNAL_STREAM, CFG_FORCE_IEEE, CFG_KEEP_F32, CFG_KEEP_HIT_IDS, CFG_SPIRV_ARITH, RESOLVE_BGRA, RESOLVE_SRGB,
                    Config, PtbError, check)
 
 
@@ -27,7 +27,7 @@ class NativeTracer:
                  radius: Optional[float] = None,
                  seed: int = 0, max_depth: int = 0,
                  keep_f32: bool = False, keep_hit_ids: bool = False,
-                 stream: Optional[int] = None, force_ieee: bool = False):
+                 stream: Optional[int] = None, force_ieee: bool = False, spirv_arith: bool = False):
         self._lib = _lib.load()
         self._ctx = C.c_void_p()
         cfg = Config()
@@ -46,6 +46,8 @@ class NativeTracer:
         cfg.flags = (CFG_KEEP_F32 if keep_f32 else 0) | (CFG_KEEP_HIT_IDS if keep_hit_ids else 0)
         if force_ieee:
             cfg.flags |= CFG_FORCE_IEEE
+        if spirv_arith:
+            cfg.flags |= CFG_SPIRV_ARITH
         if stream is not None:
             cfg.flags |= CFG_EXTERNAL_STREAM
             cfg.stream = stream
@@ -283,7 +285,7 @@ class NativeTracer:
 
     @property
     def kernel_mode(self) -> int:
-        """0 = literal IEEE intrinsics, 1 = shortened exact sequences, 2 = + on-axis camera."""
+        """0 = literal IEEE intrinsics, 1 = shortened exact sequences, 2 = + on-axis camera, 3 = Test.spirv op list."""
         return int(self._lib.ptb_kernel_mode(self._ctx))
 
     def selftest_exact_math(self, which: int, divisor: float = 1.0):
