@@ -104,6 +104,12 @@ const char *ptb_last_error(const ptb_context *ctx);
  * ptb_wait    replaces WaitForFences(ComputeFence, inf) (Renderer.cs:972). */
 int ptb_compute_frame(ptb_context *ctx);
 int ptb_wait(ptb_context *ctx);
+/* n_frames consecutive ptb_compute_frame's as ONE persistent launch (literal scene, RGBA8 output only, width % 4 == 0, no
+ * row shard; anything else falls back to n_frames launches).  The reference's render loop (Renderer.cs:933-1004) calls
+ * ComputeFrame once per displayed frame and each frame is ~2 us of GPU work, so a launch per frame is bound by launch
+ * latency; here one resident wave of blocks walks the row chunks of every frame back to back.  Every frame is computed
+ * and stored in full; all frames write the same image, exactly as the reference's frames overwrite TestImage. */
+int ptb_compute_frames(ptb_context *ctx, uint32_t n_frames);
 
 /* Headless consumers of the image (replace the fragment-stage sampling of ComputeImage,
  * Renderer.cs:1086-1089).  pitch_bytes = host row stride; 0 means tightly packed.
@@ -173,9 +179,9 @@ int ptb_set_accum_spp(ptb_context *ctx, uint32_t spp_total);
  * 64 B two-child nodes.  One hierarchy per primitive class (spheres / triangles).
  * While a scene is resident, ptb_compute_frame renders sample 0 of every pixel without jitter
  * (RGBA8 + optional float4 + primary-ray primitive ids: spheres 0..ns-1, triangles ns..ns+nt-1,
- * -1 = miss) and ptb_render_samples runs the wavefront path tracer (one wave = one sample of
- * every pixel; per bounce one fused closest-hit + scatter kernel; live paths are repacked with
- * warp ballot + prefix sum).  ptb_clear_scene returns the context to the literal CSMain path.
+ * -1 = miss) and ptb_render_samples runs the wavefront path tracer (one wave = up to 64 samples of
+ * every pixel of the row shard, see ptb_scene_set_wave_samples; per bounce one fused closest-hit +
+ * scatter kernel; live paths are repacked with warp ballot + prefix sum).  ptb_clear_scene returns the context to the literal CSMain path.
  * The arithmetic spec (ray generation = Test.hlsl:7-10 generalised to a camera basis, sphere
  * quadratic = Test.hlsl:16-27 + far root, Moeller-Trumbore triangles, Lambert / metal /
  * dielectric scattering, RNG keys) is frozen in oracle/pt_scene_oracle.h. */
@@ -265,9 +271,10 @@ int ptb_trace_rays(ptb_context *ctx, uint64_t n_rays, const float *origins, cons
  * merges have finished), resolves (total / spp_total -> UNORM8, PTB_RESOLVE_*) and stores the
  * pixels into dst_image (the RGBA8 image of the destination GPU, also peer memory).  One kernel, no staging buffer.
  * The caller provides the cross-GPU ordering: every peer's samples are rendered before, and nobody renders again until
- * every GPU's merge has finished (pathtracing_b200/dist.py uses a 1-element all-reduce on the same stream).
+ * every GPU's merge has finished (ptb_peer_barrier before and after; ptb_peer_frame does all of it).
  * ptb_ipc_export / ptb_ipc_open move the pointers between processes (cudaIpcMemHandle_t, 64 bytes);
- * which = 0 this context's accumulation buffer, 1 its RGBA8 image, 2 its rendezvous flag block.  Mappings are closed by ptb_destroy. */
+ * which = 0 this context's accumulation buffer, 1 its RGBA8 image, 2 its rendezvous flag block (3, 4: the second partial
+ * buffer / image of a peer group).  Mappings are closed by ptb_destroy. */
 #define PTB_MERGE_BACKGROUND 0x10u  /* ptb_peer_merge flag: small grid (one block per SM) for a merge that overlaps a render */
 #define PTB_MAX_PEERS 16
 #define PTB_IPC_HANDLE_BYTES 64
@@ -277,12 +284,46 @@ int ptb_ipc_open(ptb_context *ctx, const void *handle, void **device_ptr_out);
  * stores `epoch` into this GPU's slot of every peer's flag block (ptb_ipc_export which = 2; peer_flags in rank order,
  * own block included) and waits until every peer has stored `epoch` into this GPU's block.  phase 0 / 1 are two
  * independent sets of slots (e.g. "rendered" and "merged").  Epochs must increase by one per use of a phase.
- * Gives up after ~10 s (PTB_ERR_STATE from the next ptb_wait). */
+ * The flag store is a system-scope release, the wait a system-scope acquire.  Gives up after ~10 s
+ * (PTB200_BARRIER_TIMEOUT_MS): ptb_peer_merge / ptb_accum_clear queued behind it then do nothing and the next ptb_wait
+ * returns PTB_ERR_STATE. */
 int ptb_peer_barrier(ptb_context *ctx, uint32_t n_peers, void *const *peer_flags, uint32_t self_rank, uint32_t phase,
                      uint32_t epoch);
-int ptb_accum_clear(ptb_context *ctx);   /* zero the accumulation buffer only (keeps the slab total and the spp count) */
+int ptb_accum_clear(ptb_context *ctx);   /* zero the accumulation buffer only (keeps the slab total and the spp count);
+                                            a no-op on the device when a rendezvous before it timed out */
 int ptb_peer_merge(ptb_context *ctx, uint32_t n_peers, void *const *peer_accum, void *dst_image, uint32_t slab_first,
                    uint32_t slab_count, uint32_t spp_total, uint32_t flags);
+
+/* ---- native multi-GPU frame loop: the calls above composed inside the library (one call per frame and rank) ----------
+ * Sample-range sharding with the fused merge, pipelined: frame k renders into partial buffer k & 1 on the context's stream
+ * while a second, highest-priority stream merges frame k-1 (rendezvous, ptb_peer_merge into image k & 1 of the
+ * destination rank, rendezvous, clear of the partial).  No host synchronisation and no NCCL on the data path.
+ *   ptb_peer_group_create   allocates the second partial buffer, the second image, the flag block and the merge stream;
+ *   ptb_ipc_export          which = 0 partial[0], 1 image[0], 2 flag block, 3 partial[1], 4 image[1] (after create);
+ *   ptb_peer_group_local    the same five pointers for peers living in the SAME process (CUDA IPC cannot map a
+ *                           process's own allocations);
+ *   ptb_peer_group_bind     rank-ordered pointer tables (own entries included) + the destination rank's two images;
+ *                           this rank merges the pixel slab [rank*P/n ...) of every frame (split as dist.py sample_range).
+ *                           Restarts the rendezvous epochs: after every rank has bound, synchronise the ranks once on
+ *                           the host before the first ptb_peer_frame (also the way to recover from a timed-out peer);
+ *   ptb_peer_frame          renders THIS rank's samples [first_sample, first_sample + n_samples) of the frame (literal or
+ *                           uploaded scene, row shards honoured) and queues its merge; spp_total = samples per pixel in
+ *                           the merged image after this frame, over all ranks; flags = PTB_RESOLVE_*.  On the
+ *                           destination rank the merged frame becomes the current image: ptb_read_rgba8_async delivers
+ *                           it once its merge has finished, overlapping the next frame's rendering;
+ *   ptb_peer_finish         makes the context's stream wait for every merge queued so far;
+ *   ptb_peer_read_total     this rank's slab of the merged float4 accumulation (host copy; parity checks).
+ * A rendezvous that times out (PTB200_BARRIER_TIMEOUT_MS, default 10 s) raises a device-side error word: the merge and
+ * clear kernels behind it do nothing, ptb_wait returns PTB_ERR_STATE, ptb_accum_reset clears the condition. */
+#define PTB_PEER_RENDER_ONLY 0x20u   /* ptb_peer_frame flag: render into the frame's partial buffer, do not merge yet (a frame
+                                        built from several sample ranges; the last call, possibly with n_samples = 0, merges) */
+int ptb_peer_group_create(ptb_context *ctx);
+void *ptb_peer_group_local(ptb_context *ctx, int which);
+int ptb_peer_group_bind(ptb_context *ctx, uint32_t n_peers, uint32_t self_rank, uint32_t dst_rank, void *const *partial0,
+                        void *const *partial1, void *const *flags, void *dst_image0, void *dst_image1);
+int ptb_peer_frame(ptb_context *ctx, uint32_t first_sample, uint32_t n_samples, int jitter, uint32_t spp_total, uint32_t flags);
+int ptb_peer_finish(ptb_context *ctx);
+int ptb_peer_read_total(ptb_context *ctx, float *host_dst, uint32_t *slab_first, uint32_t *slab_count);
 
 /* ---- present-equivalent -----------------------------------------------
  * ptb_present replaces the full-screen-quad draw (Renderer.cs:1079-1091) + PSMain
@@ -305,7 +346,8 @@ int ptb_kernel_mode(const ptb_context *ctx);
  * whole domain: which = 0 sqrt over [2^-20,2^24), 1 reciprocal over [2^-12,2^12), 2 division of
  * every float in [2^-24,2^17) by `divisor`, 3 = the per-pixel "every sample of this pixel misses" classification of THIS
  * context's parameters against the exact discriminant at an 8x8 grid of jitter positions (both extremes included) of
- * every pixel so classified.  Writes the number of disagreeing inputs (must be 0
+ * every pixel so classified; 4 = the per-row span table of the 1 spp frame kernels (quads of four pixels that skip the
+ * intersection): every pixel of every skipped quad against the exact discriminant.  Writes the number of disagreeing inputs (must be 0
  * for the fast kernels to be selected) and the number of inputs tested. */
 int ptb_selftest_exact_math(ptb_context *ctx, int which, float divisor, uint64_t *mismatches, uint64_t *tested);
 

@@ -168,6 +168,14 @@ SIGNATURES = {
     "ptb_ipc_export": (C.c_int, [_CTX, C.c_int, C.c_void_p]),
     "ptb_ipc_open": (C.c_int, [_CTX, C.c_void_p, _P(C.c_void_p)]),
     "ptb_peer_merge": (C.c_int, [_CTX, C.c_uint32, _P(C.c_void_p), C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]),
+    "ptb_compute_frames": (C.c_int, [_CTX, C.c_uint32]),
+    "ptb_peer_group_create": (C.c_int, [_CTX]),
+    "ptb_peer_group_local": (C.c_void_p, [_CTX, C.c_int]),
+    "ptb_peer_group_bind": (C.c_int, [_CTX, C.c_uint32, C.c_uint32, C.c_uint32, _P(C.c_void_p), _P(C.c_void_p), _P(C.c_void_p),
+                                     C.c_void_p, C.c_void_p]),
+    "ptb_peer_frame": (C.c_int, [_CTX, C.c_uint32, C.c_uint32, C.c_int, C.c_uint32, C.c_uint32]),
+    "ptb_peer_finish": (C.c_int, [_CTX]),
+    "ptb_peer_read_total": (C.c_int, [_CTX, C.c_void_p, _P(C.c_uint32), _P(C.c_uint32)]),
     "ptb_present": (C.c_int, [_CTX, C.c_uint32, C.c_uint32, C.c_uint32]),
     "ptb_read_present": (C.c_int, [_CTX, C.c_void_p, C.c_size_t]),
     "ptb_timer_begin": (C.c_int, [_CTX]),

@@ -57,6 +57,7 @@ void free_buffers(ptb_context *c)
     cudaFree(c->buf.hit);
     cudaFree(c->buf.accum_owned);
     cudaFree(c->buf.present);
+    cudaFree(c->buf.row_span);
     c->buf = ptb::Buffers{};
 }
 
@@ -212,6 +213,11 @@ int ptb_create(const ptb_config *cfg, ptb_context **out_ctx)
     // ≙ CreateResources (Renderer.cs:120-179): the W x H RGBA8 storage image.
     if ((e = cudaMalloc(&c->buf.rgba8, n * 4)) != cudaSuccess) return bail(e, "cudaMalloc(rgba8)");
     if ((e = cudaMemsetAsync(c->buf.rgba8, 0, n * 4, c->stream)) != cudaSuccess) return bail(e, "cudaMemset(rgba8)");
+    if (c->k.fast && c->k.cm_on && (cfg->width & 3u) == 0) {
+        // which quads of every row can skip the intersection altogether: evaluated once, the parameters never change
+        if ((e = cudaMalloc(&c->buf.row_span, (size_t)cfg->height * sizeof(uint2))) != cudaSuccess) return bail(e, "cudaMalloc(row_span)");
+        if ((e = ptb::launch_row_span(c->k, c->buf.row_span, c->stream)) != cudaSuccess) return bail(e, "row_span_kernel");
+    }
     if (cfg->flags & PTB_CFG_KEEP_F32)
         if ((e = cudaMalloc(&c->buf.f32, n * sizeof(float4))) != cudaSuccess) return bail(e, "cudaMalloc(f32)");
     if (cfg->flags & PTB_CFG_KEEP_HIT_IDS)
@@ -228,6 +234,21 @@ int ptb_destroy(ptb_context *ctx)
     ptb::scene_destroy(ctx);
     for (void *p : ctx->ipc_opened) cudaIpcCloseMemHandle(p);
     ctx->ipc_opened.clear();
+    if (ctx->peer) {
+        ptb::PeerGroup *pg = ctx->peer;
+        if (pg->merge_stream) {
+            cudaStreamSynchronize(pg->merge_stream);
+            cudaStreamDestroy(pg->merge_stream);
+        }
+        if (pg->partial[1] && pg->partial[1] != ctx->buf.accum_owned) cudaFree(pg->partial[1]);
+        if (pg->ev_rendered) cudaEventDestroy(pg->ev_rendered);
+        for (int b = 0; b < 2; ++b) {
+            if (pg->ev_released[b]) cudaEventDestroy(pg->ev_released[b]);
+            if (pg->ev_merged[b]) cudaEventDestroy(pg->ev_merged[b]);
+        }
+        delete pg;
+        ctx->peer = nullptr;
+    }
     cudaFree(ctx->slab_total);
     cudaFree(ctx->peer_flags);
     free_buffers(ctx);
@@ -257,10 +278,34 @@ int ptb_compute_frame(ptb_context *ctx)
     return PTB_OK;
 }
 
+int ptb_compute_frames(ptb_context *ctx, uint32_t n_frames)
+{
+    PTB_ENTER(ctx);
+    if (n_frames == 0) return PTB_OK;
+    if (ctx->copy_pending) PTB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_copy_done, 0));
+    if (!ptb::scene_resident(ctx)) {
+        const cudaError_t e = ptb::launch_csmain_frames(ctx->k, ctx->buf, n_frames, ctx->stream);
+        if (e == cudaSuccess) {
+            ctx->launches += 1;
+            return PTB_OK;
+        }
+        if (e != cudaErrorNotSupported) return cuda_fail(ctx, e, "launch_csmain_frames");
+    }
+    for (uint32_t f = 0; f < n_frames; ++f) {      // configurations the persistent kernel does not cover: one launch per frame
+        const int rc = ptb_compute_frame(ctx);
+        if (rc != PTB_OK) return rc;
+    }
+    return PTB_OK;
+}
+
 int ptb_wait(ptb_context *ctx)
 {
     PTB_ENTER(ctx);
     PTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->peer && ctx->peer->merge_stream) {
+        PTB_CUDA(ctx, cudaStreamSynchronize(ctx->peer->merge_stream));
+        ctx->peer->released_pending[0] = ctx->peer->released_pending[1] = false;
+    }
     if (ctx->copy_pending || ctx->copy_pending_alt) {
         PTB_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
         ctx->copy_pending = ctx->copy_pending_alt = false;
@@ -268,7 +313,9 @@ int ptb_wait(ptb_context *ctx)
     if (ctx->peer_flags) {
         uint32_t err = 0;
         PTB_CUDA(ctx, cudaMemcpy(&err, ctx->peer_flags + 2 * PTB_MAX_PEERS, sizeof err, cudaMemcpyDeviceToHost));
-        if (err) return fail(ctx, PTB_ERR_STATE, "ptb_peer_barrier timed out waiting for a peer GPU (10 s)");
+        if (err)
+            return fail(ctx, PTB_ERR_STATE, "a cross-GPU rendezvous (ptb_peer_barrier / ptb_peer_frame) timed out waiting for a peer: "
+                        "the merges behind it were skipped, the image is incomplete (ptb_accum_reset clears the condition)");
     }
     if (ptb::scene_resident(ctx)) return ptb::scene_wait_check(ctx);
     return PTB_OK;
@@ -281,8 +328,16 @@ int ptb_read_rgba8_async(ptb_context *ctx, void *host_dst, size_t pitch_bytes)
     const size_t row = (size_t)ctx->cfg.width * 4;
     if (pitch_bytes == 0) pitch_bytes = row;
     if (pitch_bytes < row) return fail(ctx, PTB_ERR_INVALID, "ptb_read_rgba8_async: pitch %zu < row size %zu", pitch_bytes, row);
-    PTB_CUDA(ctx, cudaEventRecord(ctx->ev_img_ready, ctx->stream));
-    PTB_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_img_ready, 0));
+    ptb::PeerGroup *pg = ctx->peer;
+    const int cur = (pg && pg->bound && ctx->buf.rgba8 == pg->image[1]) ? 1 : 0;
+    if (pg && pg->bound && pg->merged_valid[cur]) {
+        // the current image was produced on the merge stream (ptb_peer_frame): order the copy after ITS completion, not
+        // after the render stream, which is already busy with the next frame
+        PTB_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, pg->ev_merged[cur], 0));
+    } else {
+        PTB_CUDA(ctx, cudaEventRecord(ctx->ev_img_ready, ctx->stream));
+        PTB_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_img_ready, 0));
+    }
     PTB_CUDA(ctx, cudaMemcpy2DAsync(host_dst, pitch_bytes, ctx->buf.rgba8, row, row, ctx->cfg.height,
                                     cudaMemcpyDeviceToHost, ctx->copy_stream));
     PTB_CUDA(ctx, cudaEventRecord(ctx->ev_copy_done, ctx->copy_stream));
@@ -293,6 +348,10 @@ int ptb_read_rgba8_async(ptb_context *ctx, void *host_dst, size_t pitch_bytes)
 int ptb_read_rgba8(ptb_context *ctx, void *host_dst, size_t pitch_bytes)
 {
     PTB_ENTER(ctx);
+    if (ctx->peer && ctx->peer->bound) {
+        const int rc = ptb_peer_finish(ctx);
+        if (rc != PTB_OK) return rc;
+    }
     return read_rows(ctx, host_dst, pitch_bytes, ctx->buf.rgba8, (size_t)ctx->cfg.width * 4, ctx->cfg.height);
 }
 
@@ -335,11 +394,22 @@ void *ptb_device_accum(ptb_context *ctx)
 int ptb_accum_reset(ptb_context *ctx)
 {
     PTB_ENTER(ctx);
+    if (ctx->peer && ctx->peer->merge_stream) PTB_CUDA(ctx, cudaStreamSynchronize(ctx->peer->merge_stream));   // merges in flight use these buffers
     int rc = ensure_accum(ctx);
     if (rc != PTB_OK) return rc;
     PTB_CUDA(ctx, cudaMemsetAsync(ctx->buf.accum, 0, n_pixels(ctx) * sizeof(float4), ctx->stream));
     if (ctx->slab_total)
         PTB_CUDA(ctx, cudaMemsetAsync(ctx->slab_total, 0, (size_t)ctx->slab_count * sizeof(float4), ctx->stream));
+    if (ctx->peer_flags)     // a timed-out rendezvous is sticky until the progressive state is reset
+        PTB_CUDA(ctx, cudaMemsetAsync(ctx->peer_flags + 2 * PTB_MAX_PEERS, 0, sizeof(uint32_t), ctx->stream));
+    if (ctx->peer) {
+        ptb::PeerGroup *pg = ctx->peer;
+        for (int b = 0; b < 2; ++b)
+            if (pg->partial[b] && pg->partial[b] != ctx->buf.accum)
+                PTB_CUDA(ctx, cudaMemsetAsync(pg->partial[b], 0, n_pixels(ctx) * sizeof(float4), ctx->stream));
+        PTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        pg->released_pending[0] = pg->released_pending[1] = false;
+    }
     ctx->accum_spp = 0;
     return PTB_OK;
 }
@@ -517,14 +587,18 @@ int ptb_accum_clear(ptb_context *ctx)
     PTB_ENTER(ctx);
     int rc = ensure_accum(ctx);
     if (rc != PTB_OK) return rc;
-    PTB_CUDA(ctx, cudaMemsetAsync(ctx->buf.accum, 0, n_pixels(ctx) * sizeof(float4), ctx->stream));
+    // a kernel rather than a memset: it does nothing when the rendezvous before it timed out (the partials then survive)
+    PTB_CUDA(ctx, ptb::launch_accum_clear(ctx->buf.accum, (uint32_t)n_pixels(ctx),
+                                          ctx->peer_flags ? ctx->peer_flags + 2 * PTB_MAX_PEERS : nullptr, ctx->stream));
+    ctx->launches += 1;
     return PTB_OK;
 }
 
 int ptb_ipc_export(ptb_context *ctx, int which, void *handle_out)
 {
     PTB_ENTER(ctx);
-    if (!handle_out || which < 0 || which > 2) return fail(ctx, PTB_ERR_INVALID, "ptb_ipc_export: bad argument");
+    if (!handle_out || which < 0 || which > 4) return fail(ctx, PTB_ERR_INVALID, "ptb_ipc_export: bad argument");
+    if (which >= 3 && !ctx->peer) return fail(ctx, PTB_ERR_STATE, "ptb_ipc_export: which = 3 / 4 need ptb_peer_group_create");
     static_assert(sizeof(cudaIpcMemHandle_t) == PTB_IPC_HANDLE_BYTES, "IPC handle size");
     void *ptr = nullptr;
     if (which == 0) {
@@ -534,11 +608,15 @@ int ptb_ipc_export(ptb_context *ctx, int which, void *handle_out)
             return fail(ctx, PTB_ERR_STATE, "ptb_ipc_export: the accumulation buffer is caller-owned (ptb_set_accum_buffer)");
         ptr = ctx->buf.accum_owned;
     } else if (which == 1) {
-        ptr = ctx->buf.rgba8;
-    } else {
+        ptr = ctx->peer ? ctx->peer->image[0] : ctx->buf.rgba8;
+    } else if (which == 2) {
         int rc = ensure_peer_flags(ctx);
         if (rc != PTB_OK) return rc;
         ptr = ctx->peer_flags;
+    } else if (which == 3) {
+        ptr = ctx->peer->partial[1];
+    } else {
+        ptr = ctx->peer->image[1];
     }
     cudaIpcMemHandle_t h;
     PTB_CUDA(ctx, cudaIpcGetMemHandle(&h, ptr));
@@ -581,8 +659,195 @@ int ptb_peer_merge(ptb_context *ctx, uint32_t n_peers, void *const *peer_accum, 
         ctx->slab_count = slab_count;
     }
     PTB_CUDA(ctx, ptb::launch_peer_merge(peer_accum, n_peers, ctx->slab_total, static_cast<uint32_t *>(dst_image), slab_first,
-                                         slab_count, spp_total, flags, ctx->stream));
+                                         slab_count, spp_total, flags, ctx->stream,
+                                         ctx->peer_flags ? ctx->peer_flags + 2 * PTB_MAX_PEERS : nullptr));
     ctx->launches += 1;
+    return PTB_OK;
+}
+
+// ---- native multi-GPU frame loop ---------------------------------------------------------------------------------
+static void slab_of(uint32_t rank, uint32_t world, uint64_t n, uint32_t *first, uint32_t *count)
+{
+    const uint64_t base = n / world, extra = n % world;        // the split of pathtracing_b200/dist.py sample_range
+    *count = (uint32_t)(base + (rank < extra ? 1u : 0u));
+    *first = (uint32_t)(rank * base + (rank < extra ? rank : extra));
+}
+
+int ptb_peer_group_create(ptb_context *ctx)
+{
+    PTB_ENTER(ctx);
+    if (ctx->peer) return PTB_OK;
+    int rc = ensure_accum(ctx);
+    if (rc != PTB_OK) return rc;
+    if (ctx->buf.accum != ctx->buf.accum_owned)
+        return fail(ctx, PTB_ERR_STATE, "ptb_peer_group_create: the accumulation buffer is caller-owned (ptb_set_accum_buffer)");
+    rc = ensure_peer_flags(ctx);
+    if (rc != PTB_OK) return rc;
+    if (!ctx->buf.rgba8_alt) {
+        PTB_CUDA(ctx, cudaMalloc(&ctx->buf.rgba8_alt, n_pixels(ctx) * sizeof(uint32_t)));
+        PTB_CUDA(ctx, cudaMemsetAsync(ctx->buf.rgba8_alt, 0, n_pixels(ctx) * sizeof(uint32_t), ctx->stream));
+        PTB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_copy_done_alt, cudaEventDisableTiming));
+    }
+    ptb::PeerGroup *pg = new (std::nothrow) ptb::PeerGroup();
+    if (!pg) return fail(ctx, PTB_ERR_NOMEM, "ptb_peer_group_create: host allocation failed");
+    ctx->peer = pg;                                  // from here on ptb_destroy releases whatever was created
+    int lo = 0, hi = 0;
+    PTB_CUDA(ctx, cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    PTB_CUDA(ctx, cudaStreamCreateWithPriority(&pg->merge_stream, cudaStreamNonBlocking, hi));
+    pg->partial[0] = ctx->buf.accum_owned;
+    PTB_CUDA(ctx, cudaMalloc(&pg->partial[1], n_pixels(ctx) * sizeof(float4)));
+    PTB_CUDA(ctx, cudaMemsetAsync(pg->partial[1], 0, n_pixels(ctx) * sizeof(float4), ctx->stream));
+    pg->image[0] = ctx->buf.rgba8;
+    pg->image[1] = ctx->buf.rgba8_alt;
+    PTB_CUDA(ctx, cudaEventCreateWithFlags(&pg->ev_rendered, cudaEventDisableTiming));
+    for (int b = 0; b < 2; ++b) {
+        PTB_CUDA(ctx, cudaEventCreateWithFlags(&pg->ev_released[b], cudaEventDisableTiming));
+        PTB_CUDA(ctx, cudaEventCreateWithFlags(&pg->ev_merged[b], cudaEventDisableTiming));
+    }
+    PTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return PTB_OK;
+}
+
+void *ptb_peer_group_local(ptb_context *ctx, int which)
+{
+    if (!ctx || !ctx->peer) return nullptr;
+    switch (which) {
+    case 0: return ctx->peer->partial[0];
+    case 1: return ctx->peer->image[0];
+    case 2: return ctx->peer_flags;
+    case 3: return ctx->peer->partial[1];
+    case 4: return ctx->peer->image[1];
+    default: return nullptr;
+    }
+}
+
+int ptb_peer_group_bind(ptb_context *ctx, uint32_t n_peers, uint32_t self_rank, uint32_t dst_rank, void *const *partial0,
+                        void *const *partial1, void *const *flags, void *dst_image0, void *dst_image1)
+{
+    PTB_ENTER(ctx);
+    if (!ctx->peer) return fail(ctx, PTB_ERR_STATE, "ptb_peer_group_bind: call ptb_peer_group_create first");
+    if (n_peers == 0 || n_peers > PTB_MAX_PEERS || self_rank >= n_peers || dst_rank >= n_peers || !partial0 || !partial1 || !flags ||
+        !dst_image0 || !dst_image1)
+        return fail(ctx, PTB_ERR_INVALID, "ptb_peer_group_bind: bad argument");
+    ptb::PeerGroup *pg = ctx->peer;
+    for (uint32_t q = 0; q < n_peers; ++q) {
+        if (!partial0[q] || !partial1[q] || !flags[q] || ((uintptr_t)partial0[q] & 15u) || ((uintptr_t)partial1[q] & 15u))
+            return fail(ctx, PTB_ERR_INVALID, "ptb_peer_group_bind: peer %u pointer is NULL or misaligned", q);
+        pg->peer_partial[0][q] = partial0[q];
+        pg->peer_partial[1][q] = partial1[q];
+        pg->peer_flags[q] = flags[q];
+    }
+    if (partial0[self_rank] != pg->partial[0] || partial1[self_rank] != pg->partial[1] || flags[self_rank] != ctx->peer_flags)
+        return fail(ctx, PTB_ERR_INVALID, "ptb_peer_group_bind: entry self_rank of every array must be this context's own buffer");
+    if (dst_rank == self_rank && (dst_image0 != pg->image[0] || dst_image1 != pg->image[1]))
+        return fail(ctx, PTB_ERR_INVALID, "ptb_peer_group_bind: the destination images of the destination rank must be its own");
+    pg->dst_image[0] = dst_image0;
+    pg->dst_image[1] = dst_image1;
+    pg->n_peers = n_peers;
+    pg->self = self_rank;
+    pg->dst = dst_rank;
+    uint32_t first = 0, count = 0;
+    slab_of(self_rank, n_peers, n_pixels(ctx), &first, &count);
+    if (!ctx->slab_total || ctx->slab_first != first || ctx->slab_count != count) {
+        cudaFree(ctx->slab_total);
+        ctx->slab_total = nullptr;
+        PTB_CUDA(ctx, cudaMalloc(&ctx->slab_total, (size_t)(count ? count : 1) * sizeof(float4)));
+        ctx->slab_first = first;
+        ctx->slab_count = count;
+    }
+    PTB_CUDA(ctx, cudaMemsetAsync(ctx->slab_total, 0, (size_t)(count ? count : 1) * sizeof(float4), ctx->stream));
+    // a (re-)bind restarts the rendezvous epochs: own flag block and error word back to zero.  Every rank binds, then the
+    // host synchronises the ranks once (dist.py: barrier) before the first frame, so no signal can precede this reset.
+    PTB_CUDA(ctx, cudaStreamSynchronize(pg->merge_stream));
+    PTB_CUDA(ctx, cudaMemsetAsync(ctx->peer_flags, 0, (2 * PTB_MAX_PEERS + 1) * sizeof(uint32_t), ctx->stream));
+    PTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    pg->epoch[0] = pg->epoch[1] = 0;
+    pg->frame = 0;
+    pg->released_pending[0] = pg->released_pending[1] = false;
+    pg->merged_valid[0] = pg->merged_valid[1] = false;
+    pg->bound = true;
+    return PTB_OK;
+}
+
+int ptb_peer_frame(ptb_context *ctx, uint32_t first_sample, uint32_t n_samples, int jitter, uint32_t spp_total, uint32_t flags)
+{
+    PTB_ENTER(ctx);
+    ptb::PeerGroup *pg = ctx->peer;
+    if (!pg || !pg->bound) return fail(ctx, PTB_ERR_STATE, "ptb_peer_frame: no peer group bound (ptb_peer_group_bind)");
+    if (flags & ~(PTB_RESOLVE_SRGB | PTB_RESOLVE_BGRA | PTB_PEER_RENDER_ONLY))
+        return fail(ctx, PTB_ERR_INVALID, "ptb_peer_frame: unknown flags 0x%x", flags);
+    const bool render_only = (flags & PTB_PEER_RENDER_ONLY) != 0;
+    flags &= ~PTB_PEER_RENDER_ONLY;
+    if (spp_total == 0 && !render_only) return fail(ctx, PTB_ERR_INVALID, "ptb_peer_frame: spp_total is 0");
+    const int b = (int)(pg->frame & 1u);
+    uint32_t *const err = ctx->peer_flags + 2 * PTB_MAX_PEERS;
+    // ---- render stream: this rank's samples into partial[b], once the merge of frame k-2 has released it
+    if (pg->released_pending[b]) {
+        PTB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, pg->ev_released[b], 0));
+        pg->released_pending[b] = false;
+    }
+    ctx->buf.accum = pg->partial[b];
+    if (n_samples) {
+        const uint32_t spp_before = ctx->accum_spp;
+        ctx->accum_spp = 0;                               // the partial holds this frame's samples only
+        const int rc = ptb_render_samples(ctx, first_sample, n_samples, jitter);
+        ctx->accum_spp = spp_before;
+        if (rc != PTB_OK) return rc;
+    }
+    if (render_only) return PTB_OK;                       // more samples of this frame follow; a later call merges
+    PTB_CUDA(ctx, cudaEventRecord(pg->ev_rendered, ctx->stream));
+    // ---- merge stream: rendezvous, fused merge + resolve of this rank's slab into dst's image[b], rendezvous, clear
+    cudaStream_t ms = pg->merge_stream;
+    PTB_CUDA(ctx, cudaStreamWaitEvent(ms, pg->ev_rendered, 0));
+    if (pg->self == pg->dst) {
+        // image[b] is about to be overwritten by every rank: a read-back of it (frame k-2) must have finished first
+        const bool is_cur = ctx->buf.rgba8 == pg->image[b];
+        const bool pending = is_cur ? ctx->copy_pending : ctx->copy_pending_alt;
+        if (pending) PTB_CUDA(ctx, cudaStreamWaitEvent(ms, is_cur ? ctx->ev_copy_done : ctx->ev_copy_done_alt, 0));
+    }
+    PTB_CUDA(ctx, ptb::launch_peer_barrier(pg->peer_flags, pg->n_peers, pg->self, 0, ++pg->epoch[0], err, ms));
+    PTB_CUDA(ctx, ptb::launch_peer_merge(pg->peer_partial[b], pg->n_peers, ctx->slab_total, static_cast<uint32_t *>(pg->dst_image[b]),
+                                         ctx->slab_first, ctx->slab_count, spp_total,
+                                         flags | (pg->n_peers > 1 ? PTB_MERGE_BACKGROUND : 0u), ms, err));
+    PTB_CUDA(ctx, ptb::launch_peer_barrier(pg->peer_flags, pg->n_peers, pg->self, 1, ++pg->epoch[1], err, ms));
+    PTB_CUDA(ctx, cudaEventRecord(pg->ev_merged[b], ms));
+    pg->merged_valid[b] = true;
+    PTB_CUDA(ctx, ptb::launch_accum_clear(pg->partial[b], (uint32_t)n_pixels(ctx), err, ms));
+    PTB_CUDA(ctx, cudaEventRecord(pg->ev_released[b], ms));
+    pg->released_pending[b] = true;
+    ctx->launches += 4;
+    // image[b] becomes the current image (ptb_read_rgba8*, ptb_device_rgba8), with its own read-back bookkeeping
+    if (ctx->buf.rgba8 != pg->image[b]) {
+        std::swap(ctx->buf.rgba8, ctx->buf.rgba8_alt);
+        std::swap(ctx->ev_copy_done, ctx->ev_copy_done_alt);
+        std::swap(ctx->copy_pending, ctx->copy_pending_alt);
+    }
+    if (pg->self == pg->dst) ctx->copy_pending = false;   // its last read-back is ordered before the merge that refills it
+    pg->frame += 1;
+    return PTB_OK;
+}
+
+int ptb_peer_finish(ptb_context *ctx)
+{
+    PTB_ENTER(ctx);
+    ptb::PeerGroup *pg = ctx->peer;
+    if (!pg) return fail(ctx, PTB_ERR_STATE, "ptb_peer_finish: no peer group");
+    for (int b = 0; b < 2; ++b)
+        if (pg->released_pending[b]) PTB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, pg->ev_released[b], 0));
+    return PTB_OK;
+}
+
+int ptb_peer_read_total(ptb_context *ctx, float *host_dst, uint32_t *slab_first, uint32_t *slab_count)
+{
+    PTB_ENTER(ctx);
+    if (!ctx->slab_total) return fail(ctx, PTB_ERR_STATE, "ptb_peer_read_total: no merge has run on this context");
+    if (slab_first) *slab_first = ctx->slab_first;
+    if (slab_count) *slab_count = ctx->slab_count;
+    if (!host_dst) return PTB_OK;
+    if (ctx->peer && ctx->peer->merge_stream) PTB_CUDA(ctx, cudaStreamSynchronize(ctx->peer->merge_stream));
+    PTB_CUDA(ctx, cudaMemcpyAsync(host_dst, ctx->slab_total, (size_t)ctx->slab_count * sizeof(float4), cudaMemcpyDeviceToHost,
+                                  ctx->stream));
+    PTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return PTB_OK;
 }
 
@@ -647,8 +912,16 @@ int ptb_kernel_mode(const ptb_context *ctx)
 int ptb_selftest_exact_math(ptb_context *ctx, int which, float divisor, uint64_t *mismatches, uint64_t *tested)
 {
     PTB_ENTER(ctx);
-    if (which < 0 || which > 3 || !mismatches || !tested)
+    if (which < 0 || which > 4 || !mismatches || !tested)
         return fail(ctx, PTB_ERR_INVALID, "ptb_selftest_exact_math: bad argument");
+    if (which == 4) {
+        unsigned long long bad4 = 0, n4 = 0;
+        PTB_CUDA(ctx, ptb::selftest_row_span(ctx->k, ctx->buf.row_span, &bad4, &n4, ctx->stream));
+        ctx->launches += 1;
+        *mismatches = bad4;
+        *tested = n4;
+        return PTB_OK;
+    }
     if (which == 3) {
         unsigned long long bad3 = 0, n3 = 0;
         PTB_CUDA(ctx, ptb::selftest_certain_miss(ctx->k, &bad3, &n3, ctx->stream));

@@ -15,7 +15,9 @@
 // proven (exhaustively, selftest.cu) or provable (Markstein) to round identically on the domain
 // the launch-uniform checks in api.cu guarantee; MODE_GENERIC is the literal intrinsic form and
 // is used whenever those checks fail.  No dense contraction anywhere => no tensor cores.
+#include <algorithm>
 #include <cstdlib>
+#include <numeric>
 #include "ptb_internal.h"
 #include "ptb_math.cuh"
 
@@ -231,18 +233,30 @@ __device__ __forceinline__ F2 screen_uv2(F2 p, float div, float inv_div)
     return ffma2(div_rn_uniform2(p, splat(-div), splat(inv_div)), splat(2.0f), splat(-1.0f));
 }
 
-// ---- 1 spp frame, 4 pixels per thread, one STG.128 of packed RGBA8 per thread -------------
-// Requires width % 4 == 0 (16 B aligned rows).  Block (32,8): a warp covers 128 consecutive
-// pixels of one row = 512 contiguous bytes of RGBA8.
-template <int MODE>
-__global__ void __launch_bounds__(256) csmain_frame_vec4(const FrameK k, uint4 *__restrict__ rgba8,
-                                                         float4 *__restrict__ f32, int4 *__restrict__ hit)
+// Conservative classification of the pixel SPAN [x0, x1] x {y} (integer pixel positions, no jitter: what a 1 spp frame
+// evaluates): the same bound as certain_miss() with the span's centre and half extent.
+__device__ __forceinline__ bool certain_miss_span(const FrameK &k, float fx0, float fx1, float fy)
 {
-    const uint32_t xq = blockIdx.x * blockDim.x + threadIdx.x;   // quad index along x
-    const uint32_t y = shard_row(k.row_offset, k.row_stride, k.row_block, blockIdx.y * blockDim.y + threadIdx.y);   // row shard (multi-GPU tiles)
-    const uint32_t wq = k.width >> 2;
-    if (xq >= wq || y >= k.height) return;                       // the guard Test.hlsl:39 lacks
+    if (!k.cm_on) return false;
+    const float u = (0.5f * (fx0 + fx1)) * k.cm_sx - 1.0f, v = fy * k.cm_sy - 1.0f;   // span centre in uv
+    const float hx = fabsf(k.cm_sx) * (0.5f * (fx1 - fx0) + 0.0005f), hy = fabsf(k.cm_sy) * 0.0005f;
+    const float s = k.oc[0] * u + k.oc[1] * v - k.oc[2];
+    const float G = k.c * (u * u + v * v + 1.0f) - s * s;
+    const float gu = fabsf(2.0f * (k.c * u - s * k.oc[0])), gv = fabsf(2.0f * (k.c * v - s * k.oc[1]));
+    const float au = fabsf(u) + hx, av = fabsf(v) + hy;
+    const float r2max = au * au + av * av + 1.0f;
+    const float lower = G - gu * hx - gv * hy - k.cm_K * (hx * hx + hy * hy);
+    return lower >= 1e-4f * k.cm_K * r2max;
+}
 
+// Four consecutive pixels of one row -> one STG.128 of packed RGBA8 (plus the optional float4 / hit-id planes).
+// row_span[y] = [first, end) quad columns of row y that need the full path; every quad outside is a certain miss
+// (row_span_kernel below evaluates certain_miss_span once per context).  nullptr: no classification.
+template <int MODE>
+__device__ __forceinline__ void frame_quad(const FrameK &k, uint32_t xq, uint32_t y, uint4 *__restrict__ rgba8,
+                                           float4 *__restrict__ f32, int4 *__restrict__ hit, const uint2 *__restrict__ row_span)
+{
+    const uint32_t wq = k.width >> 2;
     const float fy = __uint2float_rn(y);
     const float uvy = screen_uv<MODE>(fy, k.div_y, k.inv_div_y);
     uint32_t px8[4];
@@ -259,21 +273,30 @@ __global__ void __launch_bounds__(256) csmain_frame_vec4(const FrameK k, uint4 *
             if (f32) f32[q * 4 + i] = make_float4(r, g, b, 1.0f);
         }
     } else {
+        bool lean = false;                                             // Test.hlsl:36 for all four pixels
+        if (row_span) {
+            const uint2 sp = __ldg(row_span + y);
+            lean = xq < sp.x || xq >= sp.y;
+        }
+        // a miss stores (uv.x, uv.y, 0, 1): G and alpha bytes are the same for the whole quad
+        const uint32_t ga_miss = (unorm8(uvy) << 8) | 0xFF000000u;
 #pragma unroll
         for (int i = 0; i < 4; i += 2) {   // two pixels per FP32x2 instruction
             const F2 px = make_float2(__uint2float_rn(xq * 4u + i), __uint2float_rn(xq * 4u + i + 1));
             F2 r, g, b;
             bool h0 = false, h1 = false;
             const F2 uvx2 = screen_uv2(px, k.div_x, k.inv_div_x);
-            if (certain_miss(k, px.x, fy) && certain_miss(k, px.y, fy)) {   // Test.hlsl:36 for both pixels
+            if (lean) {
                 r = uvx2;
                 g = splat(uvy);
                 b = splat(0.0f);
+                px8[i] = unorm8(r.x) | ga_miss;
+                px8[i + 1] = unorm8(r.y) | ga_miss;
             } else {
                 csmain_shade2<MODE>(k, uvx2, splat(uvy), r, g, b, h0, h1);
+                px8[i] = pack_rgba8(r.x, g.x, b.x, 1.0f);
+                px8[i + 1] = pack_rgba8(r.y, g.y, b.y, 1.0f);
             }
-            px8[i] = pack_rgba8(r.x, g.x, b.x, 1.0f);
-            px8[i + 1] = pack_rgba8(r.y, g.y, b.y, 1.0f);
             hid[i] = h0 ? 0 : -1;
             hid[i + 1] = h1 ? 0 : -1;
             if (f32) {
@@ -284,6 +307,77 @@ __global__ void __launch_bounds__(256) csmain_frame_vec4(const FrameK k, uint4 *
     }
     rgba8[q] = make_uint4(px8[0], px8[1], px8[2], px8[3]);
     if (hit) hit[q] = make_int4(hid[0], hid[1], hid[2], hid[3]);
+}
+
+// ---- 1 spp frame, 4 pixels per thread, one STG.128 of packed RGBA8 per thread -------------
+// Requires width % 4 == 0 (16 B aligned rows).  Block (32,8): a warp covers 128 consecutive
+// pixels of one row = 512 contiguous bytes of RGBA8.
+template <int MODE>
+__global__ void __launch_bounds__(256) csmain_frame_vec4(const FrameK k, uint4 *__restrict__ rgba8,
+                                                         float4 *__restrict__ f32, int4 *__restrict__ hit,
+                                                         const uint2 *__restrict__ row_span)
+{
+    const uint32_t xq = blockIdx.x * blockDim.x + threadIdx.x;   // quad index along x
+    const uint32_t y = shard_row(k.row_offset, k.row_stride, k.row_block, blockIdx.y * blockDim.y + threadIdx.y);   // row shard (multi-GPU tiles)
+    if (xq >= (k.width >> 2) || y >= k.height) return;           // the guard Test.hlsl:39 lacks
+    frame_quad<MODE>(k, xq, y, rgba8, f32, hit, row_span);
+}
+
+// One block per image row: the span of quad columns that are NOT certain misses (empty span = (wq, 0) -> all lean).
+__global__ void __launch_bounds__(256) row_span_kernel(const FrameK k, uint2 *__restrict__ row_span)
+{
+    __shared__ uint32_t lo, hi;
+    const uint32_t y = blockIdx.x, wq = k.width >> 2;
+    if (threadIdx.x == 0) {
+        lo = wq;
+        hi = 0;
+    }
+    __syncthreads();
+    const float fy = __uint2float_rn(y);
+    for (uint32_t xq = threadIdx.x; xq < wq; xq += blockDim.x) {
+        const float fx0 = __uint2float_rn(xq * 4u);
+        if (!certain_miss_span(k, fx0, fx0 + 3.0f, fy)) {
+            atomicMin(&lo, xq);
+            atomicMax(&hi, xq + 1u);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) row_span[y] = make_uint2(lo, hi);
+}
+
+cudaError_t launch_row_span(const FrameK &k, uint2 *row_span, cudaStream_t s)
+{
+    row_span_kernel<<<k.height, 256, 0, s>>>(k, row_span);
+    return cudaGetLastError();
+}
+
+// ---- n_frames literal frames in ONE persistent launch ---------------------------------------------------------
+// Renderer.ComputeFrame is one ~2 us kernel per frame (Renderer.cs:1006-1040), so per-frame launches are bound by launch
+// latency, not by the machine.  Here one resident wave of blocks loops over 1024-pixel row chunks (256 threads x one quad)
+// of every frame: frame f+1 starts on an SM the moment that SM runs out of chunks of frame f, and the ramp-up / drain of
+// a launch is paid once per call instead of once per frame.  Every frame is computed and stored in full; all frames write
+// the same image (as the reference's frames do), so the final contents are those of a single frame.
+template <int MODE>
+__global__ void __launch_bounds__(256) csmain_frames_persistent(const FrameK k, uint4 *__restrict__ rgba8, uint32_t chunks_per_row,
+                                                                uint32_t total_chunks, uint32_t step_rows, uint32_t step_cols,
+                                                                const uint2 *__restrict__ row_span)
+{
+    // chunk c = blockIdx.x + i * gridDim.x of the (frame, row, chunk-of-row) sequence; (y, cx) advance by the grid size
+    // decomposed on the host into whole rows + columns, so the loop carries no division (all block-uniform)
+    const uint32_t wq = k.width >> 2;
+    uint32_t y = blockIdx.x / chunks_per_row, cx = blockIdx.x - y * chunks_per_row;
+    y %= k.height;
+    for (uint32_t c = blockIdx.x; c < total_chunks; c += gridDim.x) {
+        const uint32_t xq = cx * 256u + threadIdx.x;
+        if (xq < wq) frame_quad<MODE>(k, xq, y, rgba8, nullptr, nullptr, row_span);
+        y += step_rows;
+        cx += step_cols;
+        if (cx >= chunks_per_row) {
+            cx -= chunks_per_row;
+            ++y;
+        }
+        if (y >= k.height) y -= k.height;      // the next frame: same image
+    }
 }
 
 // ---- 1 spp frame, 1 pixel per thread (any width) ------------------------------------------
@@ -323,12 +417,51 @@ static cudaError_t launch_frame_t(const FrameK &k, const Buffers &b, cudaStream_
     if ((k.width & 3u) == 0) {
         const dim3 grid(((k.width >> 2) + 31) / 32, (shard_rows(k) + 7) / 8);
         csmain_frame_vec4<MODE><<<grid, block, 0, s>>>(k, reinterpret_cast<uint4 *>(b.rgba8), b.f32,
-                                                       reinterpret_cast<int4 *>(b.hit));
+                                                       reinterpret_cast<int4 *>(b.hit), ModeTraits<MODE>::fast ? b.row_span : nullptr);
     } else {
         const dim3 grid((k.width + 31) / 32, (shard_rows(k) + 7) / 8);
         csmain_frame_scalar<MODE><<<grid, block, 0, s>>>(k, b.rgba8, b.f32, b.hit);
     }
     return cudaGetLastError();
+}
+
+template <int MODE>
+static cudaError_t launch_frames_t(const FrameK &k, const Buffers &b, uint32_t n_frames, cudaStream_t s)
+{
+    static int grid_cap = 0;     // one resident wave: SMs x resident blocks of this kernel
+    if (grid_cap == 0) {
+        int per_sm = 0, dev = 0, sms = 148;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, csmain_frames_persistent<MODE>, 256, 0) != cudaSuccess || per_sm < 1)
+            per_sm = 1;
+        grid_cap = per_sm * sms;
+    }
+    const uint32_t chunks_per_row = ((k.width >> 2) + 255u) / 256u;
+    const uint64_t per_frame = (uint64_t)chunks_per_row * k.height, total = per_frame * n_frames;
+    if (total > 0xFFFFFFFFull) return cudaErrorNotSupported;
+    // one resident wave; the grid size is made coprime with the chunks of a frame so that, frame after frame, every block
+    // walks through ALL chunk positions (a common factor pins a block to a residue class — e.g. only the left, sphere-
+    // covered halves of the rows — and leaves half of the SMs idle: measured 27 % idle cycles with 888 blocks on 2160 chunks)
+    uint64_t grid = std::min<uint64_t>(total, (uint64_t)grid_cap);
+    if (total > grid)
+        while (grid > 1 && std::gcd(grid, per_frame) != 1) --grid;
+    const uint32_t step_rows = (uint32_t)((grid / chunks_per_row) % k.height), step_cols = (uint32_t)(grid % chunks_per_row);
+    csmain_frames_persistent<MODE><<<(unsigned)grid, 256, 0, s>>>(k, reinterpret_cast<uint4 *>(b.rgba8), chunks_per_row, (uint32_t)total,
+                                                                 step_rows, step_cols, ModeTraits<MODE>::fast ? b.row_span : nullptr);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_csmain_frames(const FrameK &k, const Buffers &b, uint32_t n_frames, cudaStream_t s)
+{
+    if (n_frames == 0) return cudaSuccess;
+    if ((k.width & 3u) != 0 || k.row_stride != 1 || k.row_offset != 0 || b.f32 || b.hit) return cudaErrorNotSupported;
+    switch (pick_mode(k)) {
+    case MODE_FAST_ON_AXIS: return launch_frames_t<MODE_FAST_ON_AXIS>(k, b, n_frames, s);
+    case MODE_FAST: return launch_frames_t<MODE_FAST>(k, b, n_frames, s);
+    case MODE_SPIRV: return launch_frames_t<MODE_SPIRV>(k, b, n_frames, s);
+    default: return launch_frames_t<MODE_GENERIC>(k, b, n_frames, s);
+    }
 }
 
 cudaError_t launch_csmain_frame(const FrameK &k, const Buffers &b, cudaStream_t s)
@@ -505,6 +638,57 @@ __global__ void __launch_bounds__(256) certain_miss_check_kernel(const FrameK k,
         atomicAdd(&out[0], bad);
         atomicAdd(&out[1], n);
     }
+}
+
+// ptb_selftest_exact_math which = 4: every pixel of every quad the row-span table marks "certain miss" really misses
+// in the exactly rounded evaluation (the frame kernels evaluate integer pixel positions only).
+template <int MODE>
+__global__ void __launch_bounds__(256) row_span_check_kernel(const FrameK k, const uint2 *__restrict__ row_span, unsigned long long *out)
+{
+    unsigned long long bad = 0, n = 0;
+    const uint32_t wq = k.width >> 2;
+    const uint64_t total = (uint64_t)wq * k.height;
+    for (uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t xq = (uint32_t)(p % wq), y = (uint32_t)(p / wq);
+        const uint2 sp = row_span[y];
+        if (!(xq < sp.x || xq >= sp.y)) continue;
+        for (uint32_t i = 0; i < 4; ++i) {
+            float r, g, b;
+            bad += csmain_shade<MODE>(k, screen_uv<MODE>(__uint2float_rn(xq * 4u + i), k.div_x, k.inv_div_x),
+                                      screen_uv<MODE>(__uint2float_rn(y), k.div_y, k.inv_div_y), r, g, b) ? 1u : 0u;
+            ++n;
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        bad += __shfl_down_sync(0xFFFFFFFFu, bad, o);
+        n += __shfl_down_sync(0xFFFFFFFFu, n, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&out[0], bad);
+        atomicAdd(&out[1], n);
+    }
+}
+
+cudaError_t selftest_row_span(const FrameK &k, const uint2 *row_span, unsigned long long *mismatches, unsigned long long *tested,
+                              cudaStream_t s)
+{
+    unsigned long long *d = nullptr, h[2] = {0, 0};
+    *mismatches = *tested = 0;
+    if (!row_span) return cudaSuccess;             // nothing classified
+    cudaError_t e = cudaMalloc(&d, sizeof h);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(d, 0, sizeof h, s);
+    if (e == cudaSuccess) {
+        if (pick_mode(k) == MODE_FAST_ON_AXIS) row_span_check_kernel<MODE_FAST_ON_AXIS><<<148 * 8, 256, 0, s>>>(k, row_span, d);
+        else row_span_check_kernel<MODE_FAST><<<148 * 8, 256, 0, s>>>(k, row_span, d);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h, d, sizeof h, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    cudaFree(d);
+    *mismatches = h[0];
+    *tested = h[1];
+    return e;
 }
 
 cudaError_t selftest_certain_miss(const FrameK &k, unsigned long long *mismatches, unsigned long long *tested, cudaStream_t s)

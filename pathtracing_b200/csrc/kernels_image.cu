@@ -7,6 +7,7 @@
 //   present : the arithmetic of the full-screen quad + PSMain
 //             (Assets/Shaders/Source/Basic/PixelShader.hlsl:8-19; sampler nearest/repeat,
 //             Renderer.cs:181-191; quad uv without flip, Renderer.cs:45-56) as a headless copy.
+#include <algorithm>
 #include <cmath>
 #include <cstdlib>
 #include <mutex>
@@ -127,8 +128,11 @@ struct PeerFlagPtrs {
 template <int NP, int UNROLL>
 __global__ void __launch_bounds__(256) peer_merge_kernel(const PeerPtrs peers, uint32_t n_peers, float4 *__restrict__ total,
                                                          uint32_t *__restrict__ dst_img, uint32_t first, uint32_t count, float spp,
-                                                         uint32_t flags)
+                                                         uint32_t flags, const uint32_t *__restrict__ error)
 {
+    // a rendezvous that timed out (peer_barrier_kernel) means some peer's partials may be incomplete: merge nothing, the
+    // error surfaces at the next ptb_wait and the partials stay where they are
+    if (error && *reinterpret_cast<const volatile uint32_t *>(error)) return;
     __shared__ float th[256];
     const bool srgb = flags & PTB_RESOLVE_SRGB, bgra = flags & PTB_RESOLVE_BGRA;     // launch-uniform
     if (srgb) {
@@ -181,7 +185,7 @@ __global__ void __launch_bounds__(256) peer_merge_kernel(const PeerPtrs peers, u
 }
 
 cudaError_t launch_peer_merge(void *const *peer_accum, uint32_t n_peers, float4 *total, uint32_t *dst_img, uint32_t first,
-                              uint32_t count, uint32_t spp_total, uint32_t flags, cudaStream_t s)
+                              uint32_t count, uint32_t spp_total, uint32_t flags, cudaStream_t s, const uint32_t *error)
 {
     if (count == 0) return cudaSuccess;
     PeerPtrs pp{};
@@ -203,41 +207,69 @@ cudaError_t launch_peer_merge(void *const *peer_accum, uint32_t n_peers, float4 
     int grid = (int)((count + block - 1) / block);
     if (grid > sms * per_sm) grid = sms * per_sm;
     const float spp = (float)spp_total;
-    if (n_peers <= 2) peer_merge_kernel<2, 4><<<grid, block, 0, s>>>(pp, n_peers, total, dst_img, first, count, spp, flags);
-    else if (n_peers <= 4) peer_merge_kernel<4, 2><<<grid, block, 0, s>>>(pp, n_peers, total, dst_img, first, count, spp, flags);
-    else if (n_peers <= 8) peer_merge_kernel<8, 1><<<grid, block, 0, s>>>(pp, n_peers, total, dst_img, first, count, spp, flags);
-    else peer_merge_kernel<16, 1><<<grid, block, 0, s>>>(pp, n_peers, total, dst_img, first, count, spp, flags);
+    if (n_peers <= 2) peer_merge_kernel<2, 4><<<grid, block, 0, s>>>(pp, n_peers, total, dst_img, first, count, spp, flags, error);
+    else if (n_peers <= 4) peer_merge_kernel<4, 2><<<grid, block, 0, s>>>(pp, n_peers, total, dst_img, first, count, spp, flags, error);
+    else if (n_peers <= 8) peer_merge_kernel<8, 1><<<grid, block, 0, s>>>(pp, n_peers, total, dst_img, first, count, spp, flags, error);
+    else peer_merge_kernel<16, 1><<<grid, block, 0, s>>>(pp, n_peers, total, dst_img, first, count, spp, flags, error);
     return cudaGetLastError();
 }
 
-// Cross-GPU rendezvous through peer memory: one warp.  Lane q stores `epoch` into slot [phase][self] of peer q's flag
-// array (system-scope release: everything this GPU's stream did before is visible to a peer that observes the flag),
-// then spins until slot [phase][q] of its OWN array reaches `epoch`.  A 32-thread block fits into any SM slot that
-// frees up, so the rendezvous is not starved by a large render grid running at lower priority — which is what happened
-// to the (640-thread) NCCL kernels of a 1-element all-reduce in the pipelined merge (profiles/r01_notes.md).
-// Bounded spin: after ~10 s the kernel gives up and raises *error instead of hanging the GPU.
+// Cross-GPU rendezvous through peer memory: one warp.  Lane q publishes `epoch` into slot [phase][self] of peer q's flag
+// array with a system-scope RELEASE store (everything this GPU's stream did before — the render kernel's writes to its
+// partial buffer — happens-before any peer's acquire that observes the flag), then spins with system-scope ACQUIRE loads
+// until slot [phase][q] of its OWN array reaches `epoch`.  A 32-thread block fits into any SM slot that frees up, so the
+// rendezvous is not starved by a large render grid running at lower priority — which is what happened to the
+// (640-thread) NCCL kernels of a 1-element all-reduce in the pipelined merge (profiles/r01_notes.md).
+// Bounded spin: after `timeout_ns` (default 10 s) the kernel gives up and raises *error (bit 1); the merge and clear
+// kernels that follow on the stream read the word and do nothing, and ptb_wait reports PTB_ERR_STATE.
+__device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v)
+{
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p)
+{
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
 __global__ void peer_barrier_kernel(const PeerFlagPtrs peers, uint32_t n_peers, uint32_t self, uint32_t phase, uint32_t epoch,
-                                    uint32_t *error)
+                                    uint32_t *error, unsigned long long timeout_ns)
 {
     const uint32_t q = threadIdx.x;
-    if (q >= n_peers) return;
-    __threadfence_system();
-    volatile uint32_t *remote = peers.p[q] + phase * PTB_MAX_PEERS + self;
-    *remote = epoch;
-    __threadfence_system();
-    volatile uint32_t *mine = peers.p[self] + phase * PTB_MAX_PEERS + q;
-    unsigned long long t0 = 0;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-    while ((int32_t)(*mine - epoch) < 0) {
-        unsigned long long t1;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-        if (t1 - t0 > 10000000000ull) {
-            atomicOr(error, 2u);
-            break;
+    if (q < n_peers) {
+        st_release_sys(peers.p[q] + phase * PTB_MAX_PEERS + self, epoch);
+        const uint32_t *mine = peers.p[self] + phase * PTB_MAX_PEERS + q;
+        unsigned long long t0 = 0;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
+            unsigned long long t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > timeout_ns) {
+                atomicOr(error, 2u);
+                break;
+            }
+            __nanosleep(100);
         }
-        __nanosleep(200);
     }
-    __threadfence_system();
+    __syncwarp();
+    __threadfence_system();      // the kernels that follow on this stream read peer memory: order them after every lane's acquire
+}
+
+// zero the partial accumulation buffer unless the rendezvous before it failed (see peer_merge_kernel)
+__global__ void __launch_bounds__(256) accum_clear_kernel(float4 *__restrict__ accum, uint32_t n, const uint32_t *__restrict__ error)
+{
+    if (error && *reinterpret_cast<const volatile uint32_t *>(error)) return;
+    const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) accum[i] = z;
+}
+
+cudaError_t launch_accum_clear(float4 *accum, uint32_t n_pixels, const uint32_t *error, cudaStream_t s)
+{
+    if (n_pixels == 0) return cudaSuccess;
+    const unsigned blocks = (unsigned)std::min<uint64_t>(((uint64_t)n_pixels + 255u) / 256u, 148u * 4u);
+    accum_clear_kernel<<<blocks, 256, 0, s>>>(accum, n_pixels, error);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_peer_barrier(void *const *peer_flags, uint32_t n_peers, uint32_t self, uint32_t phase, uint32_t epoch,
@@ -245,7 +277,12 @@ cudaError_t launch_peer_barrier(void *const *peer_flags, uint32_t n_peers, uint3
 {
     PeerFlagPtrs pf{};
     for (uint32_t q = 0; q < n_peers; ++q) pf.p[q] = static_cast<uint32_t *>(peer_flags[q]);
-    peer_barrier_kernel<<<1, 32, 0, s>>>(pf, n_peers, self, phase, epoch, error);
+    static const unsigned long long timeout_ns = [] {
+        const char *e = std::getenv("PTB200_BARRIER_TIMEOUT_MS");      // tests shorten the 10 s default
+        const long long v = e ? std::atoll(e) : 0;
+        return v > 0 ? (unsigned long long)v * 1000000ull : 10000000000ull;
+    }();
+    peer_barrier_kernel<<<1, 32, 0, s>>>(pf, n_peers, self, phase, epoch, error, timeout_ns);
     return cudaGetLastError();
 }
 

@@ -131,7 +131,7 @@ __device__ __forceinline__ bool hit_triangle(const float4 v0, const float4 e1, c
 // (6 FFMA per box; its cancellation error is at most half an ulp of the ray origin in space, covered
 // by the 2^-18-of-scene-extent padding the boxes get at build time, which includes the camera);
 // otherwise t = (plane - o) * (1/d) for rays whose origin may lie far outside the scene
-// (ptb_trace_rays).  The interval is widened by 2^-19 relative (approximate reciprocal + 3 roundings),
+// (ptb_trace_rays).  The interval is widened by 2^-19 of |t| (approximate reciprocal + 3 roundings),
 // so a box is never rejected when a primitive inside it would be accepted.  fminf/fmaxf drop NaNs.
 template <bool FMA_SLAB>
 __device__ __forceinline__ bool slab(float lox, float hix, float loy, float hiy, float loz, float hiz, const RayT &r,
@@ -149,7 +149,7 @@ __device__ __forceinline__ bool slab(float lox, float hix, float loy, float hiy,
     }
     t_near = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
     const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_far));
-    return t_near <= tf * 1.000002f;
+    return t_near <= fmaf(fabsf(tf), 1.9073486e-6f, tf);     // widened away from zero whatever the sign of tf
 }
 
 template <int CLS, bool ANY>
@@ -178,7 +178,7 @@ __device__ __forceinline__ bool test_leaf(const SceneK &k, int leaf, const RayT 
         }
         if (t < best.t || id < best.id || best.id < 0) {     // equal t: the smaller id wins (order independent)
             best.t = t;
-            best.t_cull = t * 1.000002f;
+            best.t_cull = fmaf(fabsf(t), 1.9073486e-6f, t);
             best.id = id;
             best.pos = (int)i;
             best.cls = CLS;
@@ -721,7 +721,9 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
     const uint32_t n0_pixels = rows * k.width;
     if (n0_pixels == 0) return cudaSuccess;
     const uint32_t tiles_x = (k.width + 7u) / 8u, tiles_y = (rows + 3u) / 4u;
-    const uint32_t n0 = tiles_x * tiles_y * 32u * batch;
+    const uint64_t n0_64 = (uint64_t)tiles_x * tiles_y * 32u * batch;
+    if (n0_64 > 0xFFFFFFFFull) return cudaErrorInvalidValue;      // scene.cu sizes waves so that this cannot happen
+    const uint32_t n0 = (uint32_t)n0_64;
     const uint32_t depths = k.shade_mode == PTB_SHADE_NORMALS ? 1u : k.max_depth + 1u;
     // bounces >= tail_depth run inside ONE launch (0 disables): queues that deep are too small to fill the GPU, unless the
     // wave is a big batched one (>= 8 Mi camera rays), whose queues stay large two bounces longer (c3: tail at 4 costs 6 %

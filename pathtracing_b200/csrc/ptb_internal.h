@@ -47,6 +47,7 @@ struct Buffers {
     uint32_t *rgba8_alt = nullptr; // second image, allocated by the first ptb_render_resolve (which writes it and swaps)
     float4 *f32 = nullptr;       // W*H float4 (Test.hlsl:1), optional
     int32_t *hit = nullptr;      // W*H hit ids, optional
+    uint2 *row_span = nullptr;   // per image row: [first, end) quad columns that are not certain misses (fast modes, width % 4 == 0)
     float4 *accum = nullptr;     // W*H float4 accumulation (n2)
     float4 *accum_owned = nullptr;
     uint32_t *present = nullptr; // dst_w*dst_h packed B8G8R8A8
@@ -57,6 +58,11 @@ struct Buffers {
 // kernels_csmain.cu
 cudaError_t prepare_terms(FrameK *k_host, cudaStream_t s);   // fills the derived fields (device-evaluated)
 cudaError_t launch_csmain_frame(const FrameK &k, const Buffers &b, cudaStream_t s);
+// n_frames literal frames in ONE persistent launch (one resident wave of blocks looping over 1024-pixel row chunks of
+// every frame): RGBA8 only, width % 4 == 0, no row shard.  Returns cudaErrorNotSupported when the configuration needs
+// the per-frame kernels.
+cudaError_t launch_csmain_frames(const FrameK &k, const Buffers &b, uint32_t n_frames, cudaStream_t s);
+cudaError_t launch_row_span(const FrameK &k, uint2 *row_span, cudaStream_t s);   // fills Buffers::row_span (height entries)
 // counts, over every pixel classified "certain miss", the jitter positions (8x8 grid incl. both extremes) whose exact
 // discriminant says HIT — must be 0; tested = positions evaluated (ptb_selftest_exact_math which = 3)
 cudaError_t selftest_certain_miss(const FrameK &k, unsigned long long *mismatches, unsigned long long *tested, cudaStream_t s);
@@ -65,6 +71,9 @@ cudaError_t selftest_certain_miss(const FrameK &k, unsigned long long *mismatche
 cudaError_t launch_csmain_accumulate(const FrameK &k, float4 *accum, uint32_t first_sample,
                                      uint32_t n_samples, uint32_t seed, bool jitter, cudaStream_t s,
                                      uint32_t *out8 = nullptr, float spp_total = 1.0f, bool bgra = false);
+// the same for the row-span table of the 1 spp frame kernels: pixels of quads outside a row's span that HIT (must be 0)
+cudaError_t selftest_row_span(const FrameK &k, const uint2 *row_span, unsigned long long *mismatches, unsigned long long *tested,
+                              cudaStream_t s);
 // selftest.cu — exhaustive proofs of the short exact sequences in ptb_math.cuh
 //   which: 0 = sqrt_rn_fast over [2^-20,2^24), 1 = rcp_rn_fast over [2^-12,2^12),
 //          2 = div_rn_uniform(v, D) for v in {0} U [2^-24, 2^17)
@@ -79,8 +88,10 @@ cudaError_t launch_resolve(const float4 *accum, uint32_t *out8, uint32_t n_pixel
 cudaError_t launch_present(const uint32_t *src, uint32_t sw, uint32_t sh, uint32_t *dst, uint32_t dw,
                            uint32_t dh, uint32_t flags, cudaStream_t s);
 
+// error: device word raised by a rendezvous that timed out (nullptr = none): the merge / clear then do nothing
 cudaError_t launch_peer_merge(void *const *peer_accum, uint32_t n_peers, float4 *total, uint32_t *dst_img, uint32_t first,
-                              uint32_t count, uint32_t spp_total, uint32_t flags, cudaStream_t s);
+                              uint32_t count, uint32_t spp_total, uint32_t flags, cudaStream_t s, const uint32_t *error = nullptr);
+cudaError_t launch_accum_clear(float4 *accum, uint32_t n_pixels, const uint32_t *error, cudaStream_t s);
 
 cudaError_t launch_peer_barrier(void *const *peer_flags, uint32_t n_peers, uint32_t self, uint32_t phase, uint32_t epoch,
                                 uint32_t *error, cudaStream_t s);
@@ -95,6 +106,28 @@ int scene_wait_check(ptb_context *ctx);
 int fail_msg(ptb_context *ctx, int code, const char *msg);
 int fail_cuda(ptb_context *ctx, cudaError_t e, const char *what);
 
+}  // namespace ptb
+
+namespace ptb {
+// Native multi-GPU frame loop (ptb_peer_group_* / ptb_peer_frame): sample-range sharding with the fused, pipelined
+// peer-memory merge, driven entirely from this library (one C-ABI call per frame and rank).
+struct PeerGroup {
+    bool bound = false;
+    cudaStream_t merge_stream = nullptr;          // highest priority: its small kernels must get SM slots under a render grid
+    float4 *partial[2] = {nullptr, nullptr};      // frame k renders into partial[k & 1]; [0] is the context's own accumulation buffer
+    uint32_t *image[2] = {nullptr, nullptr};      // frame k's merged image lands in image[k & 1] of the destination rank
+    cudaEvent_t ev_rendered = nullptr;
+    cudaEvent_t ev_released[2] = {nullptr, nullptr};   // partial[b] merged by every peer and cleared: free for frame k + 2
+    cudaEvent_t ev_merged[2] = {nullptr, nullptr};     // image[b] complete (after the second rendezvous)
+    bool released_pending[2] = {false, false};
+    bool merged_valid[2] = {false, false};
+    uint32_t n_peers = 0, self = 0, dst = 0;
+    void *peer_partial[2][PTB_MAX_PEERS] = {};
+    void *peer_flags[PTB_MAX_PEERS] = {};
+    void *dst_image[2] = {nullptr, nullptr};
+    uint32_t epoch[2] = {0, 0};
+    uint64_t frame = 0;
+};
 }  // namespace ptb
 
 struct ptb_context {
@@ -122,4 +155,5 @@ struct ptb_context {
     uint32_t slab_first = 0, slab_count = 0;
     std::vector<void *> ipc_opened;
     uint32_t *peer_flags = nullptr;   // 2 x PTB_MAX_PEERS epochs (arrive / done) + 1 error word, written by the peers
+    ptb::PeerGroup *peer = nullptr;   // ptb_peer_group_create
 };

@@ -99,6 +99,16 @@ uint32_t wave_paths(const ptb_context *ctx)
     return ptb::shard_row_count(ctx->cfg.height, ctx->k.row_offset, ctx->k.row_stride, ctx->k.row_block) * ctx->cfg.width;
 }
 
+// camera rays are indexed in 32 bits: 32 lanes per 8x4 pixel tile covering the row shard (times the samples of a wave)
+int camera_ray_slots(ptb_context *ctx, uint64_t *slots)
+{
+    const uint64_t rows = ptb::shard_row_count(ctx->cfg.height, ctx->k.row_offset, ctx->k.row_stride, ctx->k.row_block);
+    *slots = std::max<uint64_t>(1u, (((uint64_t)ctx->cfg.width + 7u) / 8u) * ((rows + 3u) / 4u) * 32u);
+    if (*slots > 0xFFFFFFFFull)
+        return ptb::fail_msg(ctx, PTB_ERR_UNSUPPORTED, "scene path: the image's 8x4 tile grid exceeds 2^32 camera-ray slots");
+    return PTB_OK;
+}
+
 int check_error_flag(ptb_context *ctx, SceneState *st)
 {
     uint32_t flag = 0;
@@ -125,6 +135,8 @@ int scene_compute_frame(ptb_context *ctx)
 {
     SceneState *st = state(ctx);
     const size_t n = (size_t)ctx->cfg.width * ctx->cfg.height;
+    uint64_t slots = 0;
+    if (int rc = camera_ray_slots(ctx, &slots)) return rc;
     if (!st->frame_accum) SC_CUDA(ctx, cudaMalloc(&st->frame_accum, n * sizeof(float4)));
     SC_CUDA(ctx, cudaMemsetAsync(st->frame_accum, 0, n * sizeof(float4), ctx->stream));
     if (ctx->buf.hit) SC_CUDA(ctx, cudaMemsetAsync(ctx->buf.hit, 0xFF, n * sizeof(int32_t), ctx->stream));
@@ -145,10 +157,13 @@ int scene_render_samples(ptb_context *ctx, uint32_t first_sample, uint32_t n_sam
     // for bit: the samples land in per-sample slices that are added to the accumulator in sample order.
     const uint32_t shard = wave_paths(ctx);
     if (shard == 0 || n_samples == 0) return PTB_OK;
+    uint64_t slots = 0;
+    if (int rc = camera_ray_slots(ctx, &slots)) return rc;
     uint32_t per_wave = std::min<uint32_t>(MAX_WAVE_SAMPLES, std::max<uint32_t>(1u, st->q_cap / shard));
     if (st->wave_samples) per_wave = std::min(per_wave, st->wave_samples);
     if (shard > (1u << 26)) per_wave = 1u;              // a batched wave keeps 26 bits of the path id word for the pixel
     per_wave = std::min(per_wave, n_samples);
+    per_wave = (uint32_t)std::max<uint64_t>(1u, std::min<uint64_t>(per_wave, 0xFFFFFFFFull / slots));   // 32-bit camera-ray index
     if (per_wave > 1u && !st->slices)                   // one radiance slot per path of a full wave
         SC_CUDA(ctx, cudaMalloc(&st->slices, (size_t)st->q_cap * sizeof(float4)));
     for (uint32_t s = 0; s < n_samples; s += per_wave) {
@@ -197,15 +212,25 @@ int ptb_upload_scene(ptb_context *ctx, const ptb_scene_desc *d)
 
     // largest coordinate magnitude (host pass): the boxes are padded by 2^-18 of it so that
     // culling stays conservative against the rounding of the primitive tests
+    // (std::fmax drops NaN operands, so finiteness is tested on every value, not on the running maximum)
     float ext = 0.0f;
-    for (int i = 0; i < 3; ++i) ext = std::fmax(ext, std::fabs(d->cam_origin[i]));
+    bool finite = std::isfinite(d->t_min);
+    for (int i = 0; i < 3; ++i) {
+        finite = finite && std::isfinite(d->cam_origin[i]) && std::isfinite(d->cam_u[i]) && std::isfinite(d->cam_v[i]) &&
+                 std::isfinite(d->cam_w[i]);
+        ext = std::fmax(ext, std::fabs(d->cam_origin[i]));
+    }
     for (uint32_t i = 0; i < d->n_spheres; ++i) {
         const float *c = d->spheres + 4 * (size_t)i;
         const float r = std::fabs(c[3]);
+        finite = finite && std::isfinite(c[0]) && std::isfinite(c[1]) && std::isfinite(c[2]) && std::isfinite(c[3]);
         for (int kx = 0; kx < 3; ++kx) ext = std::fmax(ext, std::fabs(c[kx]) + r);
     }
-    for (size_t i = 0; i < (size_t)d->n_triangles * 9; ++i) ext = std::fmax(ext, std::fabs(d->tri_vertices[i]));
-    if (!std::isfinite(ext)) return ptb::fail_msg(ctx, PTB_ERR_INVALID, "ptb_upload_scene: non-finite coordinate");
+    for (size_t i = 0; i < (size_t)d->n_triangles * 9; ++i) {
+        finite = finite && std::isfinite(d->tri_vertices[i]);
+        ext = std::fmax(ext, std::fabs(d->tri_vertices[i]));
+    }
+    if (!finite || !std::isfinite(ext)) return ptb::fail_msg(ctx, PTB_ERR_INVALID, "ptb_upload_scene: non-finite coordinate");
     const float pad = ext * 3.814697265625e-6f;
 
     SceneState *st = new (std::nothrow) SceneState();
@@ -411,6 +436,9 @@ int ptb_trace_rays(ptb_context *ctx, uint64_t n, const float *origins, const flo
     if (n == 0) return PTB_OK;
     if (!origins || !dirs || !out_prim) return ptb::fail_msg(ctx, PTB_ERR_INVALID, "ptb_trace_rays: NULL array");
     if (n > (1ull << 31)) return ptb::fail_msg(ctx, PTB_ERR_UNSUPPORTED, "ptb_trace_rays: more than 2^31 rays");
+    if (!(t_min >= 0.0f) || !(t_max >= t_min))
+        return ptb::fail_msg(ctx, PTB_ERR_INVALID, "ptb_trace_rays: need 0 <= t_min <= t_max (the conservative culling interval is "
+                             "widened relative to non-negative distances)");
     SC_CUDA(ctx, cudaSetDevice(ctx->cfg.device));
     SceneState *st = state(ctx);
     float *d_o = nullptr, *d_d = nullptr, *d_t = nullptr;

@@ -16,9 +16,11 @@ rendering; the only collective is the merge of the per-rank results:
   p2p      samples sharding whose merge is ONE fused kernel per GPU over NVLink peer memory instead of an
            NCCL reduce: every rank owns a contiguous slab of pixels, loads the partials of that slab from
            all peers (CUDA IPC mappings of their accumulation buffers), adds them in rank order, resolves
-           and stores the pixels into rank `dst`'s image (`ptb_peer_merge`).  Cross-rank ordering is a
-           one-warp rendezvous kernel over peer-memory flags (`ptb_peer_barrier`) before and after.  Deterministic sum order;
-           8x less data over NVLink than reduce-to-one at 8 GPUs.
+           and stores the pixels into rank `dst`'s image.  The whole frame loop lives in the library
+           (`ptb_peer_group_*`, `ptb_peer_frame`: render into partial buffer k & 1, rendezvous kernel over
+           peer-memory flags, fused merge into image k & 1 of `dst`, rendezvous, clear — the merge of frame k on a
+           high-priority stream overlaps the rendering of frame k+1); this module only exchanges the IPC
+           handles.  Deterministic sum order; 8x less data over NVLink than reduce-to-one at 8 GPUs.
 
 The engine behind a rank is anything with the `LocalEngine` methods: `GpuEngine` (NativeTracer with
 a torch-owned accumulation tensor) on the box, an oracle-backed engine in the gloo tests.  This
@@ -107,73 +109,35 @@ class GpuEngine:
 
     def accum_reset(self):
         if self.peer_memory:
-            self.tracer.accum_reset()
-            if getattr(self, "merger", None) is not None:
-                self.merger.accum_reset()      # second partial buffer + this rank's slab of the running total
+            self.tracer.accum_reset()          # both partial buffers, this rank's slab of the running total, the error word
             return
         with torch.cuda.stream(self.stream):
             self.accum.zero_()
         self.tracer.set_accum_spp(0)
 
-    # -- fused peer merge -------------------------------------------------------------------------
+    # -- fused peer merge: the native frame loop ----------------------------------------------------
     def peer_setup(self, rank: int, world: int, dst: int, group=None) -> None:
-        """Exchange CUDA IPC handles; map every peer's two partial accumulation buffers and rank `dst`'s image.
-        Two buffers per rank (double buffering): frame k+1 renders into one while the merge kernels still read the
-        other.  The second buffer and the merge launches belong to a second context on its own stream."""
+        """Create this rank's peer group, exchange the CUDA IPC handles of its five buffers (two partial accumulation
+        buffers, two images, the rendezvous flag block) and bind the rank-ordered pointer tables."""
         assert self.peer_memory, "GpuEngine(peer_memory=True) required"
-        from .tracer import NativeTracer
-        # high priority: the merge kernel's blocks must get SM slots while the next frame's (much larger) render grid
-        # is in flight, otherwise the merge only starts when that grid drains and nothing overlaps
-        self.merge_stream = torch.cuda.Stream(device=self.device, priority=-1)
-        self.merger = NativeTracer(self.width, self.height, device=self.device.index, stream=self.merge_stream.cuda_stream)
-        self.merger.accum_reset()
-        self._bufs = [self.tracer.device_accum(), self.merger.device_accum()]
-        mine = (self.tracer.ipc_export(0), self.merger.ipc_export(0), self.tracer.ipc_export(1), self.merger.ipc_export(2))
+        t = self.tracer
+        t.peer_group_create()
+        local = t.peer_group_local()               # (partial0, image0, flags, partial1, image1)
         handles = [None] * world
         if world > 1:
-            dist.all_gather_object(handles, mine, group=group)
-        else:
-            handles[0] = mine
-        accum_ptrs = [[self._bufs[b] if r == rank else self.merger.ipc_open(handles[r][b]) for r in range(world)]
-                      for b in range(2)]
-        image_ptr = self.tracer.device_rgba8() if dst == rank else self.merger.ipc_open(handles[dst][2])
-        self._peers = (accum_ptrs, image_ptr, slab_range(rank, world, self.width * self.height))
-        # rendezvous flag blocks (ptb_peer_barrier): one-warp kernels over peer memory instead of NCCL all-reduces
-        self._flag_ptrs = [self.merger.device_peer_flags() if r == rank else self.merger.ipc_open(handles[r][3])
-                           for r in range(world)]
-        self._rank = rank
-        self._epoch = [0, 0]
+            dist.all_gather_object(handles, t.peer_group_export(), group=group)
+        ptrs = [local if r == rank else tuple(t.ipc_open(h) for h in handles[r]) for r in range(world)]
+        t.peer_group_bind(rank, dst, [p[0] for p in ptrs], [p[3] for p in ptrs], [p[2] for p in ptrs],
+                          ptrs[dst][1], ptrs[dst][4])
+        self._rank, self._world, self._dst = rank, world, dst
         if world > 1:
             dist.barrier(group=group)          # every flag block exists and is mapped before the first signal
-        self._cur = 0
-        self.torch_streams_synced = True
 
-    def peer_use_buffer(self, b: int) -> None:
-        """Render into partial buffer b from now on."""
-        if b != self._cur:
-            self.tracer.set_accum_buffer(None if b == 0 else self._bufs[1])
-            if b == 0:
-                self.tracer.device_accum()     # re-binds the context's own buffer
-            self._cur = b
+    def peer_frame(self, first_sample: int, n_samples: int, spp_total: int, render_only: bool = False) -> None:
+        self.tracer.peer_frame(first_sample, n_samples, spp_total, render_only=render_only)
 
-    def peer_barrier(self, phase: int) -> None:
-        """On the merge stream: wait until every GPU has reached this point of the same frame."""
-        if len(self._flag_ptrs) > 1:
-            self._epoch[phase] += 1
-            self.merger.peer_barrier(self._flag_ptrs, self._rank, phase, self._epoch[phase])
-
-    def peer_merge(self, b: int, spp_total: int, background: bool = False) -> None:
-        """On the merge stream: this rank's slab of frame buffer b, summed over all peers, into dst's image.
-        background: small grid, for a merge that overlaps the next frame's render kernel."""
-        accum_ptrs, image_ptr, (first, count) = self._peers
-        self.merger.peer_merge(accum_ptrs[b], image_ptr, first, count, spp_total, background=background)
-
-    def peer_clear(self, b: int) -> None:
-        """On the merge stream: local memset of this rank's partial buffer b."""
-        self.merger.set_accum_buffer(None if b == 1 else self._bufs[0])
-        if b == 1:
-            self.merger.device_accum()
-        self.merger.accum_clear()
+    def peer_finish(self) -> None:
+        self.tracer.peer_finish()
 
     def render_samples(self, first_sample, n_samples):
         self.tracer.render_samples(first_sample, n_samples, jitter=True)
@@ -186,17 +150,17 @@ class GpuEngine:
         self.tracer.resolve()
 
     def image_tensor(self):
-        if self._image is None:
-            # zero-copy int32 view of the library's RGBA8 image through the CUDA array interface
-            self._image = self._wrap(self.tracer.device_rgba8(), (self.height, self.width), "<i4")
-        return self._image
+        # zero-copy int32 view of the library's CURRENT RGBA8 image through the CUDA array interface (the fused paths
+        # alternate between two image buffers)
+        ptr = self.tracer.device_rgba8()
+        if self._image is None or self._image[0] != ptr:
+            self._image = (ptr, self._wrap(ptr, (self.height, self.width), "<i4"))
+        return self._image[1]
 
     def read_image(self):
         return self.tracer.read_rgba8()
 
     def close(self):
-        if getattr(self, "merger", None) is not None:
-            self.merger.destroy()
         self.tracer.destroy()
 
 
@@ -220,36 +184,41 @@ class ShardedRenderer:
         self.dst = dst
         if mode == "p2p":
             engine.peer_setup(self.rank, self.world, dst, group)
-            self._flag = torch.zeros(1, dtype=torch.int32, device=engine.accum_tensor().device)
-            self._frame = 0                    # merges so far: frame k renders into partial buffer k & 1
-            self._cleared = [None, None]       # event: the merge that last used buffer b has released it
+            self._pending = False              # samples rendered into the current frame's partial buffer, not merged yet
+
+    def frame(self, first_sample: int, n_samples: int, dst: int = 0, pipelined: bool = True) -> Optional[torch.Tensor]:
+        """One frame = render this rank's share of samples [first, first+n) + merge.  p2p: ONE library call
+        (ptb_peer_frame); with pipelined=True the merge overlaps the next frame and the image is complete after finish()."""
+        if self.mode != "p2p":
+            self.render(first_sample, n_samples)
+            return self.merge(dst)
+        if dst != self.dst:
+            raise ValueError("p2p merge: the destination rank is fixed when the renderer is created")
+        start, n = sample_range(first_sample, n_samples, self.rank, self.world)
+        self.spp_total += n_samples
+        self.engine.peer_frame(start, n, self.spp_total)
+        self._pending = False
+        if not pipelined:
+            self.finish()
+        return self.engine.image_tensor() if self.rank == dst else None
 
     def render(self, first_sample: int, n_samples: int) -> None:
         """Render samples [first, first+n) of the frame, this rank's share only.  No communication."""
-        if self.mode == "p2p":
-            b = self._frame & 1
-            if self._cleared[b] is not None:   # the merge of frame k-2 must be done with this buffer
-                self.engine.stream.wait_event(self._cleared[b])
-                self._cleared[b] = None
-            self.engine.peer_use_buffer(b)
         if self.mode in ("samples", "p2p"):
             start, n = sample_range(first_sample, n_samples, self.rank, self.world)
-            if n:
+            if self.mode == "p2p":
+                self.engine.peer_frame(start, n, 0, render_only=True)
+                self._pending = True
+            elif n:
                 self.engine.render_samples(start, n)
         else:
             self.engine.render_samples(first_sample, n_samples)
         self.spp_total += n_samples
 
-    def _rendezvous(self) -> None:
-        if self.world > 1:
-            dist.all_reduce(self._flag, group=self.group)
-
     def finish(self) -> None:
         """p2p, pipelined merges: make the render stream wait for every merge issued so far (image complete on dst)."""
         if self.mode == "p2p":
-            for b in range(2):
-                if self._cleared[b] is not None:
-                    self.engine.stream.wait_event(self._cleared[b])
+            self.engine.peer_finish()
 
     def merge(self, dst: int = 0, pipelined: bool = False) -> Optional[torch.Tensor]:
         """The path's one exchange step.  Returns the (H, W) packed RGBA8 image (int32) on `dst`, else None.
@@ -259,19 +228,8 @@ class ShardedRenderer:
         if self.mode == "p2p":
             if dst != self.dst:
                 raise ValueError("p2p merge: the destination rank is fixed when the renderer is created")
-            b = self._frame & 1
-            rendered = torch.cuda.Event()
-            rendered.record(e.stream)
-            with torch.cuda.stream(e.merge_stream):
-                e.merge_stream.wait_event(rendered)
-                e.peer_barrier(0)          # every rank has rendered this frame's samples (stream-ordered, no host sync)
-                e.peer_merge(b, self.spp_total, background=pipelined)
-                e.peer_barrier(1)          # every slab has landed in dst's image; nobody reads these partials any more
-                e.peer_clear(b)            # local memset of this rank's partial buffer
-                done = torch.cuda.Event()
-                done.record(e.merge_stream)
-            self._cleared[b] = done
-            self._frame += 1
+            e.peer_frame(0, 0, self.spp_total)       # n_samples = 0: merge what render() put into the partial buffer
+            self._pending = False
             if not pipelined:
                 self.finish()
             return e.image_tensor() if self.rank == dst else None

@@ -87,6 +87,10 @@ class NativeTracer:
     def compute_frame(self) -> None:
         self._ck(self._lib.ptb_compute_frame(self._ctx))
 
+    def compute_frames(self, n_frames: int) -> None:
+        """n_frames literal frames in one persistent launch (falls back to n launches where that is not possible)."""
+        self._ck(self._lib.ptb_compute_frames(self._ctx, n_frames))
+
     def wait(self) -> None:
         self._ck(self._lib.ptb_wait(self._ctx))
 
@@ -235,7 +239,7 @@ class NativeTracer:
         self._ck(self._lib.ptb_accum_clear(self._ctx))
 
     def ipc_export(self, which: int) -> bytes:
-        """cudaIpcMemHandle_t (64 bytes) of this context's accumulation buffer (0) or RGBA8 image (1)."""
+        """cudaIpcMemHandle_t (64 bytes): 0 accumulation buffer, 1 RGBA8 image, 2 flag block, 3 / 4 second partial / image."""
         buf = C.create_string_buffer(64)
         self._ck(self._lib.ptb_ipc_export(self._ctx, which, buf))
         return buf.raw
@@ -252,6 +256,43 @@ class NativeTracer:
         self._ck(self._lib.ptb_peer_merge(self._ctx, len(peer_accum), arr, dst_image, slab_first, slab_count, spp_total,
                                           (RESOLVE_SRGB if srgb else 0) | (RESOLVE_BGRA if bgra else 0) |
                                           (0x10 if background else 0)))
+
+    # -- native multi-GPU frame loop (ptb_peer_group_* / ptb_peer_frame) ------------------------------
+    def peer_group_create(self) -> None:
+        self._ck(self._lib.ptb_peer_group_create(self._ctx))
+
+    def peer_group_local(self):
+        """Device pointers (partial0, image0, flags, partial1, image1) for peers in the same process."""
+        return tuple(int(self._lib.ptb_peer_group_local(self._ctx, w) or 0) for w in range(5))
+
+    def peer_group_export(self):
+        """CUDA IPC handles of the same five buffers, for peers in other processes."""
+        return tuple(self.ipc_export(w) for w in range(5))
+
+    def peer_group_bind(self, self_rank: int, dst_rank: int, partial0, partial1, flags, dst_image0: int, dst_image1: int) -> None:
+        n = len(partial0)
+        arr = lambda v: (C.c_void_p * n)(*v)
+        self._ck(self._lib.ptb_peer_group_bind(self._ctx, n, self_rank, dst_rank, arr(partial0), arr(partial1), arr(flags),
+                                               dst_image0, dst_image1))
+
+    def peer_frame(self, first_sample: int, n_samples: int, spp_total: int, jitter: bool = True, srgb: bool = False,
+                   bgra: bool = False, render_only: bool = False) -> None:
+        """Render this rank's samples of the frame and queue the pipelined fused merge (one call per frame and rank).
+        render_only: no merge yet (more sample ranges of the same frame follow)."""
+        self._ck(self._lib.ptb_peer_frame(self._ctx, first_sample, n_samples, int(jitter), spp_total,
+                                          (RESOLVE_SRGB if srgb else 0) | (RESOLVE_BGRA if bgra else 0) |
+                                          (0x20 if render_only else 0)))
+
+    def peer_finish(self) -> None:
+        self._ck(self._lib.ptb_peer_finish(self._ctx))
+
+    def peer_read_total(self):
+        """-> (slab_first, float32 (slab_count, 4)): this rank's slab of the merged accumulation."""
+        first, count = C.c_uint32(), C.c_uint32()
+        self._ck(self._lib.ptb_peer_read_total(self._ctx, None, C.byref(first), C.byref(count)))
+        out = np.empty((count.value, 4), np.float32)
+        self._ck(self._lib.ptb_peer_read_total(self._ctx, out.ctypes.data, C.byref(first), C.byref(count)))
+        return int(first.value), out
 
     # -- present-equivalent ----------------------------------------------------------------
     def present(self, dst_w: Optional[int] = None, dst_h: Optional[int] = None, srgb: bool = True) -> None:

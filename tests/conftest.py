@@ -3,6 +3,12 @@ import sys
 
 import pytest
 
+# the cross-GPU rendezvous gives up after 10 s by default; the timeout test wants that quickly (read once, at first launch)
+os.environ.setdefault("PTB200_BARRIER_TIMEOUT_MS", "300")
+# single-device emulation of several ranks = several contexts x (render, merge, copy) streams: give every stream its own
+# hardware queue, so that a rendezvous kernel waiting for a peer never sits in front of that peer's kernels (default: 8)
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)

@@ -349,6 +349,10 @@ def test_certain_miss_classification_is_conservative(oracle, size, kw):
     with NativeTracer(w, h, seed=4, **kw) as t:
         bad, n = t.selftest_exact_math(3)
         assert bad == 0, f"{bad} sample positions of 'certain miss' pixels actually hit"
+        bad4, n4 = t.selftest_exact_math(4)          # the row-span table of the 1 spp frame kernels
+        assert bad4 == 0, f"{bad4} pixels of skipped quads actually hit"
+        if not kw and w * 9 == h * 16:
+            assert n4 > 0.75 * w * h                 # default scene: most quads skip the intersection
         frac = n / 64 / (w * h)
         if not kw and w * 9 == h * 16:
             assert 0.80 < frac < 0.86          # default scene, 16:9: 85.3 % of the pixels miss; the silhouette band stays out
