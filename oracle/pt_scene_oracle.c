@@ -411,8 +411,27 @@ static void prim_normal(const pto_scene *s, int32_t id, const float P[3], float 
     }
 }
 
+static int32_t scene_sample_core(const pto_scene *s, const pto_accel *a, uint32_t px, uint32_t py,
+                                 uint32_t sample, uint32_t seed, int jitter, float rgb[3], float *segs, int cap, int *nseg);
+
 int32_t pto_scene_sample(const pto_scene *s, const pto_accel *a, uint32_t px, uint32_t py,
                          uint32_t sample, uint32_t seed, int jitter, float rgb[3])
+{
+    return scene_sample_core(s, a, px, py, sample, seed, jitter, rgb, NULL, 0, NULL);
+}
+
+/* Debugging aid: the same path, recording every segment as 8 floats (origin, direction, t or +inf on a miss, primitive id
+ * or -1); returns the number of segments written (<= cap). */
+int pto_scene_sample_path(const pto_scene *s, const pto_accel *a, uint32_t px, uint32_t py, uint32_t sample, uint32_t seed,
+                          int jitter, float rgb[3], float *segs, int cap)
+{
+    int n = 0;
+    scene_sample_core(s, a, px, py, sample, seed, jitter, rgb, segs, cap, &n);
+    return n;
+}
+
+static int32_t scene_sample_core(const pto_scene *s, const pto_accel *a, uint32_t px, uint32_t py,
+                                 uint32_t sample, uint32_t seed, int jitter, float rgb[3], float *segs, int cap, int *nseg)
 {
     const uint32_t pix = py * s->width + px;
     float jx = 0.0f, jy = 0.0f;
@@ -437,6 +456,11 @@ int32_t pto_scene_sample(const pto_scene *s, const pto_accel *a, uint32_t px, ui
     for (uint32_t depth = 0;; ++depth) {
         int32_t prim; float t;
         int hit = pto_closest_hit(s, a, o, d, s->t_min, INFINITY, &prim, &t);
+        if (segs && *nseg < cap) {
+            float *g = segs + 8 * (*nseg)++;
+            g[0] = o[0]; g[1] = o[1]; g[2] = o[2]; g[3] = d[0]; g[4] = d[1]; g[5] = d[2];
+            g[6] = hit ? t : INFINITY; g[7] = hit ? (float)prim : -1.0f;
+        }
         if (depth == 0) primary = hit ? prim : -1;
         float P[3], n_out[3];
         if (hit) {

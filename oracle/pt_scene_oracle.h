@@ -104,6 +104,9 @@ int64_t pto_scene_frame(const pto_scene *s, const pto_accel *a, uint32_t seed, f
                         uint8_t *out_rgba8, int32_t *out_hit, int nthreads);
 
 /* accum[pixel] += (rgb,1) for samples first..first+n-1, in sample order. */
+/* Debugging aid: one path with every segment recorded as 8 floats (origin, direction, t or +inf, primitive id or -1). */
+int pto_scene_sample_path(const pto_scene *s, const pto_accel *a, uint32_t px, uint32_t py, uint32_t sample, uint32_t seed,
+                          int jitter, float rgb[3], float *segs, int cap);
 void pto_scene_accumulate(const pto_scene *s, const pto_accel *a, uint32_t first_sample,
                           uint32_t n_samples, uint32_t seed, int jitter, float *accum, int nthreads);
 /* One interleaved row shard only (ptb_set_row_shard_bands semantics); other rows of accum are untouched. */

@@ -53,6 +53,9 @@ def lib() -> C.CDLL:
         L.pto_scene_accumulate_rows.argtypes = [P(SceneC), C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int,
                                                 C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int]
         L.pto_scene_accumulate_rows.restype = None
+        L.pto_scene_sample_path.argtypes = [P(SceneC), C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int,
+                                            P(C.c_float), C.c_void_p, C.c_int]
+        L.pto_scene_sample_path.restype = C.c_int
         L.pto_sincos2pi.argtypes = [C.c_float, P(C.c_float), P(C.c_float)]
         L.pto_sincos2pi.restype = None
         L.pto_unit_vector.argtypes = [C.c_float, C.c_float, P(C.c_float)]
@@ -119,6 +122,14 @@ class SceneOracle:
         n = lib().pto_scene_frame(C.byref(self.c), None if brute else self._accel, seed, f32.ctypes.data,
                                   rgba8.ctypes.data, hit.ctypes.data, 0)
         return {"f32": f32, "rgba8": rgba8, "hit": hit, "hits": int(n)}
+
+    def sample_path(self, px: int, py: int, sample: int, seed: int = 0, jitter: bool = True, brute: bool = False):
+        """-> (rgb, segments (n, 8): origin, direction, t (inf = miss), primitive id) of one path (debugging aid)."""
+        rgb = (C.c_float * 3)()
+        segs = np.zeros((256, 8), np.float32)
+        n = lib().pto_scene_sample_path(C.byref(self.c), None if brute else self._accel, px, py, sample, seed, int(jitter), rgb,
+                                        segs.ctypes.data, 256)
+        return np.array(rgb[:], np.float32), segs[:n]
 
     def accumulate(self, first_sample: int, n_samples: int, seed: int = 0, jitter: bool = True, accum=None,
                    brute: bool = False, nthreads: int = 0, rows=None):

@@ -1,6 +1,7 @@
 // api.cu — the extern "C" boundary of libptb200.so (include/ptb200.h).
 // Each entry point names the reference member it replaces in the header; this file only does
 // argument checking, resource ownership and stream/event plumbing around the kernel launchers.
+#include <algorithm>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -258,6 +259,13 @@ int ptb_destroy(ptb_context *ctx)
         cudaStreamSynchronize(ctx->copy_stream);
         cudaStreamDestroy(ctx->copy_stream);
     }
+    for (int i = 0; i < 3; ++i) {
+        if (ctx->copy_extra[i]) {
+            cudaStreamSynchronize(ctx->copy_extra[i]);
+            cudaStreamDestroy(ctx->copy_extra[i]);
+        }
+        if (ctx->ev_copy_part[i]) cudaEventDestroy(ctx->ev_copy_part[i]);
+    }
     if (ctx->ev_img_ready) cudaEventDestroy(ctx->ev_img_ready);
     if (ctx->ev_copy_done) cudaEventDestroy(ctx->ev_copy_done);
     if (ctx->ev_copy_done_alt) cudaEventDestroy(ctx->ev_copy_done_alt);
@@ -338,8 +346,35 @@ int ptb_read_rgba8_async(ptb_context *ctx, void *host_dst, size_t pitch_bytes)
         PTB_CUDA(ctx, cudaEventRecord(ctx->ev_img_ready, ctx->stream));
         PTB_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_img_ready, 0));
     }
-    PTB_CUDA(ctx, cudaMemcpy2DAsync(host_dst, pitch_bytes, ctx->buf.rgba8, row, row, ctx->cfg.height,
+    // The frame goes down in up to 4 row bands on 4 copy streams, so that several copy engines work on one read-back: one
+    // engine sustains ~40 GB/s device-to-host on these hosts, which made the 8.3 MB frame of a 1080p step (205 us) the
+    // bottleneck of the multi-GPU end-to-end loop; 2 / 4 bands: 179 / 175 us per step next to a 172 us render
+    // (experiments/peer_timing.py; PTB200_COPY_SPLIT = 1..4 for A/B runs).  Small images stay on one stream.
+    static const int split = [] {
+        const char *e = std::getenv("PTB200_COPY_SPLIT");
+        const int v = e ? std::atoi(e) : 4;
+        return v >= 1 && v <= 4 ? v : 4;
+    }();
+    const uint32_t H = ctx->cfg.height;
+    const int parts = (row * H >= (1u << 20)) ? (int)std::min<uint32_t>((uint32_t)split, H) : 1;
+    if (parts > 1) {
+        PTB_CUDA(ctx, cudaEventRecord(ctx->ev_img_ready, ctx->copy_stream));       // "the image may be read" as seen by the copy stream
+        for (int i = 1; i < parts; ++i) {
+            if (!ctx->copy_extra[i - 1]) {
+                PTB_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_extra[i - 1], cudaStreamNonBlocking));
+                PTB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_copy_part[i - 1], cudaEventDisableTiming));
+            }
+            const uint32_t r0 = (uint32_t)((uint64_t)H * i / parts), r1 = (uint32_t)((uint64_t)H * (i + 1) / parts);
+            PTB_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_extra[i - 1], ctx->ev_img_ready, 0));
+            PTB_CUDA(ctx, cudaMemcpy2DAsync(static_cast<char *>(host_dst) + (size_t)r0 * pitch_bytes, pitch_bytes,
+                                            reinterpret_cast<const char *>(ctx->buf.rgba8) + (size_t)r0 * row, row, row, r1 - r0,
+                                            cudaMemcpyDeviceToHost, ctx->copy_extra[i - 1]));
+            PTB_CUDA(ctx, cudaEventRecord(ctx->ev_copy_part[i - 1], ctx->copy_extra[i - 1]));
+        }
+    }
+    PTB_CUDA(ctx, cudaMemcpy2DAsync(host_dst, pitch_bytes, ctx->buf.rgba8, row, row, parts > 1 ? (uint32_t)((uint64_t)H / parts) : H,
                                     cudaMemcpyDeviceToHost, ctx->copy_stream));
+    for (int i = 1; i < parts; ++i) PTB_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_copy_part[i - 1], 0));
     PTB_CUDA(ctx, cudaEventRecord(ctx->ev_copy_done, ctx->copy_stream));
     ctx->copy_pending = true;
     return PTB_OK;

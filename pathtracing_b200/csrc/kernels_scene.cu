@@ -77,7 +77,15 @@ __device__ __forceinline__ void make_ray(RayT &r, float ox, float oy, float oz, 
 {
     r.ox = ox; r.oy = oy; r.oz = oz;
     r.dx = dx; r.dy = dy; r.dz = dz;
-    r.ix = rcp_approx(dx); r.iy = rcp_approx(dy); r.iz = rcp_approx(dz);   // 1 ulp; absorbed by the culling slack
+    // 1 ulp; absorbed by the culling slack.  A direction component of exactly 0 (or a denormal, flushed) gives +-inf, and an
+    // infinite reciprocal poisons the FMA slab form: plane * inf + (-o * inf) is inf - inf = NaN on one side of the origin
+    // and -inf on the other, so a box the ray lies INSIDE came out as the empty interval and whole subtrees were culled
+    // (found by the 2-GPU scene test: 1 path in 3*10^5 takes a scattered direction with d.x == 0).  Clamped to +-2^96 the
+    // products stay finite and the slab of a parallel ray is [-huge, +huge] inside the box, same-signed outside.
+    constexpr float RCP_MAX = 7.9228163e28f;
+    r.ix = fminf(fmaxf(rcp_approx(dx), -RCP_MAX), RCP_MAX);
+    r.iy = fminf(fmaxf(rcp_approx(dy), -RCP_MAX), RCP_MAX);
+    r.iz = fminf(fmaxf(rcp_approx(dz), -RCP_MAX), RCP_MAX);
     r.px = -(ox * r.ix); r.py = -(oy * r.iy); r.pz = -(oz * r.iz);
     r.a = dot3f(dx, dy, dz, dx, dy, dz);
     r.a2 = 2.0f * r.a;
@@ -149,7 +157,11 @@ __device__ __forceinline__ bool slab(float lox, float hix, float loy, float hiy,
     }
     t_near = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
     const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_far));
+#ifdef PTB_SLAB_WIDEN_OLD
+    return t_near <= tf * 1.000002f;
+#else
     return t_near <= fmaf(fabsf(tf), 1.9073486e-6f, tf);     // widened away from zero whatever the sign of tf
+#endif
 }
 
 template <int CLS, bool ANY>
@@ -178,7 +190,11 @@ __device__ __forceinline__ bool test_leaf(const SceneK &k, int leaf, const RayT 
         }
         if (t < best.t || id < best.id || best.id < 0) {     // equal t: the smaller id wins (order independent)
             best.t = t;
+#ifdef PTB_SLAB_WIDEN_OLD
+            best.t_cull = t * 1.000002f;
+#else
             best.t_cull = fmaf(fabsf(t), 1.9073486e-6f, t);
+#endif
             best.id = id;
             best.pos = (int)i;
             best.cls = CLS;

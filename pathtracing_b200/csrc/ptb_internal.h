@@ -142,6 +142,8 @@ struct ptb_context {
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev_img_ready = nullptr, ev_copy_done = nullptr;
     bool copy_pending = false;
+    cudaStream_t copy_extra[3] = {nullptr, nullptr, nullptr};     // PTB200_COPY_SPLIT: further row bands of one read-back
+    cudaEvent_t ev_copy_part[3] = {nullptr, nullptr, nullptr};
     // the same pair for buf.rgba8_alt (ptb_render_resolve swaps image, event and flag together)
     cudaEvent_t ev_copy_done_alt = nullptr;
     bool copy_pending_alt = false;

@@ -321,6 +321,9 @@ int ptb_upload_scene(ptb_context *ctx, const ptb_scene_desc *d)
         UP(cudaMalloc(&st->q[i].s1, sizeof(float4) * st->q_cap));
         UP(cudaMalloc(&st->q[i].s2, sizeof(float2) * st->q_cap));
     }
+    // one radiance slot per path of a full wave (batched waves).  Allocated here rather than at the first render: cudaMalloc
+    // synchronises the device, which inside a pipelined multi-GPU frame loop would stall behind a rendezvous kernel
+    UP(cudaMalloc(&st->slices, (size_t)st->q_cap * sizeof(float4)));
     st->counts_len = 2u * (ctx->cfg.max_depth + 2u);
     UP(cudaMalloc(&st->counts, sizeof(uint32_t) * st->counts_len));
     UP(cudaMalloc(&st->stats, sizeof(ptb::SceneStatsDev)));

@@ -8,6 +8,9 @@ os.environ.setdefault("PTB200_BARRIER_TIMEOUT_MS", "300")
 # single-device emulation of several ranks = several contexts x (render, merge, copy) streams: give every stream its own
 # hardware queue, so that a rendezvous kernel waiting for a peer never sits in front of that peer's kernels (default: 8)
 os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+# ... and load every kernel when the library is loaded: a lazily loaded kernel synchronises the context on its first
+# launch, which deadlocks (until the rendezvous times out) when another "rank" of the same process is spinning meanwhile
+os.environ.setdefault("CUDA_MODULE_LOADING", "EAGER")
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:

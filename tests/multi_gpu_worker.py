@@ -107,12 +107,25 @@ def main():
         sr.frame(9, 6, pipelined=True)
         sr.finish()
         eng.tracer.wait()
+        first_px, slab = eng.tracer.peer_read_total()
+        slabs = [None] * world
+        dist.all_gather_object(slabs, (first_px, slab))
         if rank == 0:
             so = S.SceneOracle(sc, sw, sh, max_depth=depth)
             total = np.zeros((sh, sw, 4), np.float32)
             for first, count in ((0, 9), (9, 6)):
                 total = total + rank_sum([so.accumulate(*sample_range(first, count, r, world), seed=2) for r in range(world)])
-            checks.append(("scene p2p", np.array_equal(eng.tracer.read_rgba8(), O.resolve(total, 15))))
+            got = np.zeros((sh * sw, 4), np.float32)
+            for f, s_ in slabs:
+                got[f:f + len(s_)] = s_
+            got = got.reshape(sh, sw, 4)
+            bad = np.argwhere((bits(got) != bits(total)).any(axis=-1))
+            if len(bad):
+                y, x = bad[0]
+                print(f"scene p2p: {len(bad)} pixels of the merged accumulation differ, first ({x},{y}): got {got[y, x]} want {total[y, x]}",
+                      flush=True)
+            checks.append(("scene p2p merged accumulation", len(bad) == 0))
+            checks.append(("scene p2p image", np.array_equal(eng.tracer.read_rgba8(), O.resolve(total, 15))))
         eng.close()
         dist.barrier()
 

@@ -271,6 +271,34 @@ def test_config4_full_size_million_triangles_4k(S):
         assert_images_equal(total, full, "c4 8-way row-sharded merge")
 
 
+def test_zero_direction_components_do_not_break_the_slab_test(S):
+    """Rays with a direction component of exactly 0 inside the path tracer (FMA slab form): with the reference's camera
+    basis the centre column / row of the image has d.x == 0 / d.y == 0 exactly; and the scattered direction with d.x == 0
+    that the 2-GPU test found (mixed scene 192x108, seed 2, pixel (113, 54), sample 7: the path was lost to the sky)."""
+    w = h = 64
+    sc = scenes.mixed_small(n_spheres=300, n_tris=2000)
+    sc.cam_origin = np.array([0.3, 1.2, 9.0], np.float32)          # reference basis (Test.hlsl:10), origin off the box planes
+    sc.cam_u, sc.cam_v, sc.cam_w = (np.array(v, np.float32) for v in ((1, 0, 0), (0, -1, 0), (0, 0, -1)))
+    so = S.SceneOracle(sc, w, h, max_depth=4)
+    ref = so.frame(seed=1)
+    assert (ref["hit"][:, 32] >= 0).sum() > 5 and (ref["hit"][32, :] >= 0).sum() > 5     # the zero-component rays do hit things
+    with NativeTracer(w, h, seed=1, max_depth=4, keep_f32=True, keep_hit_ids=True) as t:
+        t.upload_scene(sc)
+        t.compute_frame()
+        t.wait()
+        assert np.array_equal(t.read_hit_ids(), ref["hit"])
+        assert_images_equal(t.read_f32(), ref["f32"], "frame with axis-parallel direction components")
+    sw, sh = 192, 108
+    sc = scenes.mixed_small(width=sw, height=sh)
+    so = S.SceneOracle(sc, sw, sh, max_depth=6)
+    rgb, segs = so.sample_path(113, 54, 7, seed=2)
+    assert len(segs) == 7 and segs[6, 3] == 0.0 and np.isfinite(segs[6, 6])       # the last segment has d.x == 0 and hits
+    with NativeTracer(sw, sh, seed=2, max_depth=6) as t:
+        t.upload_scene(sc)
+        t.render_samples(7, 1)
+        assert_images_equal(t.read_accum(), so.accumulate(7, 1, seed=2), "sample 7 of the mixed scene")
+
+
 def test_results_do_not_depend_on_the_hierarchy(S):
     """max_leaf changes the tree (and with it traversal order and compaction order); results may not change."""
     w, h = 160, 90
