@@ -2,7 +2,8 @@
 // RayTracing/Graphics/Renderer.cs to run the tracing path on libptb200.so instead of the Vulkan
 // compute pipeline.  SOURCE ONLY: there is no .NET SDK on the build or GPU box, so this file is
 // not compiled or exercised here (the executable stand-in is pathtracing_b200/tracer.py, which
-// makes the same calls in the same order).  Signatures mirror include/ptb200.h one to one.
+// makes the same calls in the same order).  EVERY entry point of include/ptb200.h has a [DllImport] here
+// (tests/test_abi.py diffs the two name lists); the public members wrap the ones a renderer needs.
 //
 // Replaces, in Renderer.cs: CreateResources (105-196) + CreateComputePipeline (293-403) ->
 // NativeTracer ctor; ComputeFrame (1006-1040) -> ComputeFrame(); ResetFences/WaitForFences
@@ -94,19 +95,67 @@ public sealed unsafe class NativeTracer : IDisposable
     [DllImport(Lib)] private static extern int ptb_peer_merge(IntPtr ctx, uint nPeers, IntPtr* peerAccum, IntPtr dstImage,
                                                               uint slabFirst, uint slabCount, uint sppTotal, uint flags);
 
-    public const uint ResolveSrgb = 1, ResolveBgra = 2;
+    // ---- the rest of include/ptb200.h: versions, planes, checkpoint, multi-frame launch, peer group, inspection, timing
+    [StructLayout(LayoutKind.Sequential)]
+    public struct SceneInfo                     // == ptb_scene_info
+    {
+        public uint NSpheres, NTriangles, SphereNodes, TriangleNodes, SphereLeaves, TriangleLeaves, MaxLeaf;
+        public float BuildMs;
+        public ulong DeviceBytes;
+    }
+
+    [StructLayout(LayoutKind.Sequential)]
+    public struct SceneStats                    // == ptb_scene_stats
+    {
+        public ulong Rays, NodesVisited, PrimsTested, Scatters, Paths, MaxStack;
+    }
+
+    [DllImport(Lib)] private static extern int ptb_abi_version();
+    [DllImport(Lib)] private static extern int ptb_device_count();
+    [DllImport(Lib)] private static extern int ptb_kernel_mode(IntPtr ctx);
+    [DllImport(Lib)] private static extern ulong ptb_launch_count(IntPtr ctx);
+    [DllImport(Lib)] private static extern int ptb_compute_frames(IntPtr ctx, uint nFrames);
+    [DllImport(Lib)] private static extern int ptb_read_f32(IntPtr ctx, float* hostDst, nuint pitchBytes);
+    [DllImport(Lib)] private static extern int ptb_read_hit_ids(IntPtr ctx, int* hostDst, nuint pitchBytes);
+    [DllImport(Lib)] private static extern void* ptb_device_f32(IntPtr ctx);
+    [DllImport(Lib)] private static extern int ptb_read_accum(IntPtr ctx, float* hostDst, nuint pitchBytes);
+    [DllImport(Lib)] private static extern int ptb_write_accum(IntPtr ctx, float* hostSrc, nuint pitchBytes, uint sppTotal);
+    [DllImport(Lib)] private static extern int ptb_set_row_shard(IntPtr ctx, uint rowOffset, uint rowStride);
+    [DllImport(Lib)] private static extern int ptb_scene_info_get(IntPtr ctx, SceneInfo* info);
+    [DllImport(Lib)] private static extern int ptb_scene_stats_get(IntPtr ctx, SceneStats* stats);
+    [DllImport(Lib)] private static extern int ptb_scene_stats_reset(IntPtr ctx);
+    [DllImport(Lib)] private static extern int ptb_scene_queue_sizes(IntPtr ctx, uint* sizes, uint cap, out uint n);
+    [DllImport(Lib)] private static extern int ptb_scene_read_bvh(IntPtr ctx, int which, void* nodes, uint capNodes, out uint nNodes,
+                                                                  uint* order, uint capPrims, out uint nPrims);
+    [DllImport(Lib)] private static extern void* ptb_device_peer_flags(IntPtr ctx);
+    [DllImport(Lib)] private static extern int ptb_peer_barrier(IntPtr ctx, uint nPeers, IntPtr* peerFlags, uint selfRank, uint phase, uint epoch);
+    [DllImport(Lib)] private static extern int ptb_peer_group_create(IntPtr ctx);
+    [DllImport(Lib)] private static extern void* ptb_peer_group_local(IntPtr ctx, int which);
+    [DllImport(Lib)] private static extern int ptb_peer_group_bind(IntPtr ctx, uint nPeers, uint selfRank, uint dstRank, IntPtr* partial0,
+                                                                   IntPtr* partial1, IntPtr* flags, IntPtr dstImage0, IntPtr dstImage1);
+    [DllImport(Lib)] private static extern int ptb_peer_frame(IntPtr ctx, uint firstSample, uint nSamples, int jitter, uint sppTotal, uint flags);
+    [DllImport(Lib)] private static extern int ptb_peer_finish(IntPtr ctx);
+    [DllImport(Lib)] private static extern int ptb_peer_read_total(IntPtr ctx, float* hostDst, out uint slabFirst, out uint slabCount);
+    [DllImport(Lib)] private static extern int ptb_timer_begin(IntPtr ctx);
+    [DllImport(Lib)] private static extern int ptb_timer_end(IntPtr ctx, out float elapsedMs);
+    [DllImport(Lib)] private static extern int ptb_selftest_exact_math(IntPtr ctx, int which, float divisor, out ulong mismatches, out ulong tested);
+
+    public const uint ResolveSrgb = 1, ResolveBgra = 2, PeerRenderOnly = 0x20;
+    public const uint CfgKeepF32 = 1, CfgKeepHitIds = 2, CfgForceIeee = 8, CfgSpirvArith = 0x10;
 
     private IntPtr _ctx;
     public uint Width { get; }
     public uint Height { get; }
 
     // ≙ CreateResources + CreateComputePipeline: size from Window.FramebufferSize (Renderer.cs:128-129).
-    public NativeTracer(uint width, uint height, int device = 0, uint seed = 0)
+    public NativeTracer(uint width, uint height, int device = 0, uint seed = 0, uint maxDepth = 0, uint flags = 0)
     {
         Config cfg;
         Check(IntPtr.Zero, ptb_default_config(&cfg, width, height));
         cfg.Device = device;
         cfg.Seed = seed;
+        cfg.MaxDepth = maxDepth;
+        cfg.Flags = flags;                      // CfgKeepF32 | CfgKeepHitIds | CfgForceIeee | CfgSpirvArith
         Check(IntPtr.Zero, ptb_create(&cfg, out _ctx));
         Width = width;
         Height = height;
@@ -186,6 +235,75 @@ public sealed unsafe class NativeTracer : IDisposable
     {
         fixed (IntPtr* p = peerAccum)
             Check(_ctx, ptb_peer_merge(_ctx, (uint)peerAccum.Length, p, dstImage, slabFirst, slabCount, sppTotal, flags));
+    }
+
+    // ---- members over the remaining entry points
+    public static int AbiVersion => ptb_abi_version();
+    public static int DeviceCount => ptb_device_count();
+    public int KernelMode => ptb_kernel_mode(_ctx);
+    public ulong LaunchCount => ptb_launch_count(_ctx);
+    /// n reference frames in ONE persistent launch (Renderer.ComputeFrame x n without n launch latencies).
+    public void ComputeFrames(uint n) => Check(_ctx, ptb_compute_frames(_ctx, n));
+    public void ReadFloatImage(Span<float> f32) { fixed (float* p = f32) Check(_ctx, ptb_read_f32(_ctx, p, 0)); }      // needs CfgKeepF32
+    public void ReadHitIds(Span<int> ids) { fixed (int* p = ids) Check(_ctx, ptb_read_hit_ids(_ctx, p, 0)); }          // needs CfgKeepHitIds
+    public IntPtr DeviceFloatImage => (IntPtr)ptb_device_f32(_ctx);
+    // checkpoint / restore of the progressive state (SURVEY.md 8f-4)
+    public void ReadAccumulation(Span<float> acc) { fixed (float* p = acc) Check(_ctx, ptb_read_accum(_ctx, p, 0)); }
+    public void WriteAccumulation(ReadOnlySpan<float> acc, uint sppTotal) { fixed (float* p = acc) Check(_ctx, ptb_write_accum(_ctx, p, 0, sppTotal)); }
+    public void SetAccumBuffer(IntPtr devicePtr) => Check(_ctx, ptb_set_accum_buffer(_ctx, (void*)devicePtr));
+    public void SetAccumulatedSamples(uint spp) => Check(_ctx, ptb_set_accum_spp(_ctx, spp));
+    public void SetRowShardRows(uint rowOffset, uint rowStride) => Check(_ctx, ptb_set_row_shard(_ctx, rowOffset, rowStride));
+    public SceneInfo GetSceneInfo() { SceneInfo i; Check(_ctx, ptb_scene_info_get(_ctx, &i)); return i; }
+    public SceneStats GetSceneStats() { SceneStats s; Check(_ctx, ptb_scene_stats_get(_ctx, &s)); return s; }
+    public void ResetSceneStats() => Check(_ctx, ptb_scene_stats_reset(_ctx));
+    public uint[] SceneQueueSizes()
+    {
+        var q = new uint[256];
+        uint n;
+        fixed (uint* p = q) Check(_ctx, ptb_scene_queue_sizes(_ctx, p, (uint)q.Length, out n));
+        Array.Resize(ref q, (int)n);
+        return q;
+    }
+    public (float[] nodes, uint[] order) ReadBvh(int which)                // 64 B nodes as 16 floats each, leaf-order primitive ids
+    {
+        Check(_ctx, ptb_scene_read_bvh(_ctx, which, null, 0, out uint nn, null, 0, out uint np));
+        var nodes = new float[nn * 16];
+        var order = new uint[np];
+        fixed (float* pn = nodes) fixed (uint* po = order)
+            Check(_ctx, ptb_scene_read_bvh(_ctx, which, pn, nn, out nn, po, np, out np));
+        return (nodes, order);
+    }
+    // cross-GPU rendezvous + the native multi-GPU frame loop
+    public IntPtr DevicePeerFlags => (IntPtr)ptb_device_peer_flags(_ctx);
+    public void PeerBarrier(ReadOnlySpan<IntPtr> peerFlags, uint selfRank, uint phase, uint epoch)
+    {
+        fixed (IntPtr* p = peerFlags) Check(_ctx, ptb_peer_barrier(_ctx, (uint)peerFlags.Length, p, selfRank, phase, epoch));
+    }
+    public void PeerGroupCreate() => Check(_ctx, ptb_peer_group_create(_ctx));
+    public IntPtr PeerGroupLocal(int which) => (IntPtr)ptb_peer_group_local(_ctx, which);
+    public void PeerGroupBind(uint selfRank, uint dstRank, ReadOnlySpan<IntPtr> partial0, ReadOnlySpan<IntPtr> partial1,
+                              ReadOnlySpan<IntPtr> flags, IntPtr dstImage0, IntPtr dstImage1)
+    {
+        fixed (IntPtr* a = partial0, b = partial1, f = flags)
+            Check(_ctx, ptb_peer_group_bind(_ctx, (uint)partial0.Length, selfRank, dstRank, a, b, f, dstImage0, dstImage1));
+    }
+    /// This rank's samples of one frame + the pipelined fused peer merge: ONE call per frame and rank.
+    public void PeerFrame(uint firstSample, uint nSamples, uint sppTotal, bool jitter = true, uint flags = 0) =>
+        Check(_ctx, ptb_peer_frame(_ctx, firstSample, nSamples, jitter ? 1 : 0, sppTotal, flags));
+    public void PeerFinish() => Check(_ctx, ptb_peer_finish(_ctx));
+    public float[] PeerReadTotal(out uint slabFirst)
+    {
+        Check(_ctx, ptb_peer_read_total(_ctx, null, out slabFirst, out uint count));
+        var t = new float[count * 4];
+        fixed (float* p = t) Check(_ctx, ptb_peer_read_total(_ctx, p, out slabFirst, out count));
+        return t;
+    }
+    public void TimerBegin() => Check(_ctx, ptb_timer_begin(_ctx));
+    public float TimerEnd() { Check(_ctx, ptb_timer_end(_ctx, out float ms)); return ms; }
+    public (ulong mismatches, ulong tested) SelfTestExactMath(int which, float divisor = 1f)
+    {
+        Check(_ctx, ptb_selftest_exact_math(_ctx, which, divisor, out ulong bad, out ulong n));
+        return (bad, n);
     }
 
     public void Dispose()

@@ -26,9 +26,8 @@ int main(int argc, char **argv)
         else if (a == "--out" && i + 1 < argc) out = argv[++i];
         else return fprintf(stderr, "usage: pt_render [--size WxH] [--spp N] [--seed S] [--frames K] [--out file.ppm]\n"), 2;
     }
-    (void)seed;
     try {
-        ptb_host::Renderer r(win);
+        ptb_host::Renderer r(win, 0, seed);
         r.Init();
         const auto t0 = std::chrono::steady_clock::now();
         for (unsigned f = 0; f < frames; ++f) {

@@ -28,7 +28,8 @@ struct Window {                       // stand-in for Silk.NET IWindow: only Fra
 
 class Renderer {
 public:
-    explicit Renderer(Window w = Window(), int device = 0) : window_(w), device_(device) {}
+    // seed: RNG seed of jittered samples (no reference counterpart: Test.hlsl is deterministic)
+    explicit Renderer(Window w = Window(), int device = 0, uint32_t seed = 0) : window_(w), seed_(seed), device_(device) {}
     ~Renderer() { Dispose(); }
     Renderer(const Renderer &) = delete;
     Renderer &operator=(const Renderer &) = delete;
@@ -44,6 +45,7 @@ public:
         ptb_config cfg;
         check(nullptr, ptb_default_config(&cfg, window_.width, window_.height));
         cfg.device = device_;
+        cfg.seed = seed_;
         check(nullptr, ptb_create(&cfg, &ctx_));
     }
 
@@ -103,6 +105,7 @@ private:
     }
 
     Window window_;
+    uint32_t seed_ = 0;
     int device_;
     ptb_context *ctx_ = nullptr;
     bool pipeline_ready_ = false;

@@ -33,6 +33,20 @@ def test_every_declared_symbol_is_exported_and_bound():
     assert sorted(_lib.SIGNATURES) == syms
 
 
+def test_csharp_binding_declares_every_entry_point():
+    """pathtracing_b200/cs/NativeTracer.cs cannot be compiled here (no dotnet): at least its [DllImport] list must be
+    the header's list, name for name, and every import must be used by a member."""
+    cs = open(os.path.join(ROOT, "pathtracing_b200", "cs", "NativeTracer.cs")).read()
+    imports = re.findall(r"\[DllImport\(Lib\)\]\s*private static extern\s+[\w\*]+\s+(ptb_[a-z0-9_]+)\s*\(", cs)
+    assert sorted(imports) == header_symbols(), sorted(set(header_symbols()) ^ set(imports))
+    assert len(imports) == len(set(imports))
+    body = re.sub(r"\[DllImport\(Lib\)\][^;]*;", "", cs, flags=re.S)
+    unused = [n for n in imports if not re.search(r"\b" + n + r"\s*\(", body)]
+    assert not unused, f"imported but never called: {unused}"
+    for struct, size in (("Config", None), ("Material", 32)):
+        assert f"public struct {struct}" in cs
+
+
 def test_only_c_abi_types_in_header():
     src = open(os.path.join(ROOT, "include", "ptb200.h")).read()
     assert 'extern "C"' in src

@@ -51,3 +51,14 @@ def test_cli_progressive_mode(tmp_path, oracle):
     acc = oracle.accumulate(p, 0, 4, 0, True)
     acc = oracle.accumulate(p, 4, 4, 0, True, accum=acc)
     assert np.array_equal(read_ppm(str(out)), oracle.resolve(acc, 8)[..., :3])
+
+
+@pytest.mark.gpu
+def test_cli_seed_is_honoured(tmp_path, oracle):
+    from pathtracing_b200.image_io import read_ppm
+    out = tmp_path / "seed.ppm"
+    r = subprocess.run([CLI, "--size", "320x180", "--spp", "3", "--seed", "77", "--out", str(out)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    acc = oracle.accumulate(oracle.frame_params(320, 180), 0, 3, 77, True)
+    assert np.array_equal(read_ppm(str(out)), oracle.resolve(acc, 3)[..., :3])
+    assert not np.array_equal(read_ppm(str(out)), oracle.resolve(oracle.accumulate(oracle.frame_params(320, 180), 0, 3, 0, True), 3)[..., :3])
