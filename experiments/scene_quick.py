@@ -46,3 +46,18 @@ if which in ("c4", "all"):
 if which == "leaf8":
     run("c3", scenes.random_spheres(500, width=1920, height=1080), 1920, 1080, 8, 8, 8)
     run("c4", scenes.triangle_terrain(512, 2, width=3840, height=2160), 3840, 2160, 4, 8, 8)
+if which == "ab":
+    # one timing per workload under the current PTB200_* switches, plus a digest of the accumulation buffer so that two
+    # runs under different switches can be compared bit for bit
+    import hashlib
+    for nm, sc, w, h, spp in (("c3", scenes.random_spheres(500, seed=1, width=1920, height=1080), 1920, 1080, 64),
+                              ("c4", scenes.triangle_terrain(512, 2, seed=2, width=3840, height=2160), 3840, 2160, 16)):
+        with NativeTracer(w, h, max_depth=8) as t:
+            t.upload_scene(sc)
+            t.render_samples(0, spp); t.wait()
+            dig = hashlib.sha256(t.read_accum().tobytes()).hexdigest()[:16]
+            best = 1e9
+            for rep in range(3):
+                t.timer_begin(); t.render_samples(spp * (rep + 1), spp); best = min(best, t.timer_end())
+            tag = " ".join(f"{k}={v}" for k, v in sorted(os.environ.items()) if k.startswith("PTB200_"))
+            print(f"AB {nm} [{tag}] {best:.2f} ms  {w*h*spp/best/1e3:.0f} Msamples/s  accum {dig}", flush=True)

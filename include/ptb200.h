@@ -344,7 +344,7 @@ uint64_t ptb_launch_count(const ptb_context *ctx);
 int ptb_kernel_mode(const ptb_context *ctx);
 /* Proof by exhaustion, on the device, that a shortened sequence equals the IEEE intrinsic on its
  * whole domain: which = 0 sqrt over [2^-20,2^24), 1 reciprocal over [2^-12,2^12), 2 division of
- * every float in [2^-24,2^17) by `divisor`, 3 = the per-pixel "every sample of this pixel misses" classification of THIS
+ * every float in [2^-24,2^17) by `divisor` (5 = the same for the 2-instruction split-reciprocal division), 3 = the per-pixel "every sample of this pixel misses" classification of THIS
  * context's parameters against the exact discriminant at an 8x8 grid of jitter positions (both extremes included) of
  * every pixel so classified; 4 = the per-row span table of the 1 spp frame kernels (quads of four pixels that skip the
  * intersection): every pixel of every skipped quad against the exact discriminant.  Writes the number of disagreeing inputs (must be 0

@@ -85,6 +85,9 @@ void derive_fast_flags(ptb_context *c)
     k.on_axis = 0;
     k.cm_on = 0;
     k.cm_sx = k.cm_sy = k.cm_K = 0.0f;
+    k.div2 = 0;
+    k.one = 1u;
+    k.dl_x = k.dl_y = 0.0f;
     k.spirv = (c->cfg.flags & PTB_CFG_SPIRV_ARITH) ? 1u : 0u;
     if (c->cfg.flags & (PTB_CFG_FORCE_IEEE | PTB_CFG_SPIRV_ARITH)) return;
     const float vals[] = {k.cam[0], k.cam[1], k.cam[2], k.centre[0], k.centre[1], k.centre[2], k.radius,
@@ -95,9 +98,12 @@ void derive_fast_flags(ptb_context *c)
     const double ux = 2.0 * (k.width + 1.0) / std::fabs((double)k.div_x) + 1.0;
     const double uy = 2.0 * (k.height + 1.0) / std::fabs((double)k.div_y) + 1.0;
     if (!(ux * ux + uy * uy + 1.0 < 8388608.0)) return;
-    if (!ptb::uniform_divisor_verified(k.div_x, c->stream)) return;
-    if (!ptb::uniform_divisor_verified(k.div_y, c->stream)) return;
+    const int vx = ptb::uniform_divisor_verified(k.div_x, c->stream), vy = ptb::uniform_divisor_verified(k.div_y, c->stream);
+    if (!(vx & 1) || !(vy & 1)) return;
     k.fast = 1;
+    k.div2 = ((vx & 2) && (vy & 2) && !std::getenv("PTB200_NO_DIV2")) ? 1u : 0u;
+    k.dl_x = ptb::reciprocal_low(k.div_x);
+    k.dl_y = ptb::reciprocal_low(k.div_y);
     // per-pixel certain-miss classification: only bounds are needed, so plain host arithmetic is fine
     k.cm_sx = 2.0f / k.div_x;
     k.cm_sy = 2.0f / k.div_y;
@@ -947,7 +953,7 @@ int ptb_kernel_mode(const ptb_context *ctx)
 int ptb_selftest_exact_math(ptb_context *ctx, int which, float divisor, uint64_t *mismatches, uint64_t *tested)
 {
     PTB_ENTER(ctx);
-    if (which < 0 || which > 4 || !mismatches || !tested)
+    if (which < 0 || which > 5 || !mismatches || !tested)
         return fail(ctx, PTB_ERR_INVALID, "ptb_selftest_exact_math: bad argument");
     if (which == 4) {
         unsigned long long bad4 = 0, n4 = 0;
@@ -965,7 +971,7 @@ int ptb_selftest_exact_math(ptb_context *ctx, int which, float divisor, uint64_t
         *tested = n3;
         return PTB_OK;
     }
-    if (which == 2 && !(std::fabs(divisor) > 0.0f && std::isfinite(divisor)))
+    if ((which == 2 || which == 5) && !(std::fabs(divisor) > 0.0f && std::isfinite(divisor)))
         return fail(ctx, PTB_ERR_INVALID, "ptb_selftest_exact_math: divisor must be finite and non-zero");
     unsigned long long bad = 0, n = 0;
     PTB_CUDA(ctx, ptb::selftest_exact(which, divisor, &bad, &n, ctx->stream));

@@ -309,6 +309,32 @@ __device__ __forceinline__ void frame_quad(const FrameK &k, uint32_t xq, uint32_
     if (hit) hit[q] = make_int4(hid[0], hid[1], hid[2], hid[3]);
 }
 
+// Test.hlsl:7 for two lanes with per-lane divisor constants dn = -D, dh = RN(1/D), dl = RN(1/D - dh).
+// DIV2: RN(p/D) = fma(p, dh, RN(p*dl)) — division by a constant through its reciprocal split in two floats (Brisebarre,
+// Muller & Raina 2004), one instruction less than the Markstein form; correct for every binary32 p only for divisors that
+// pass the exhaustive check made when the context is created (selftest.cu which = 5: every float in [2^-24, 2^17)
+// against __fdiv_rn; 1080, 2160 and every divisor tried pass), otherwise FrameK::div2 = 0 selects the 3-instruction form.
+// Pins four integers in registers as they are: without it the compiler re-derives the forward differences of
+// csmain_accumulate's RNG state as a dozen separate induction variables (8 adds per sample instead of 3.5).
+__device__ __forceinline__ void keep_form(uint32_t &a, uint32_t &b, uint32_t &c, uint32_t &d)
+{
+    asm("" : "+r"(a), "+r"(b), "+r"(c), "+r"(d));
+}
+
+__device__ __forceinline__ uint32_t add_on_fma(uint32_t a, uint32_t b, uint32_t one)
+{
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(one), "r"(b));
+    return d;
+}
+
+template <bool DIV2>
+__device__ __forceinline__ F2 screen_uv_axes(F2 p, F2 dn, F2 dh, F2 dl)
+{
+    if (DIV2) return ffma2(ffma2(p, dh, fmul2(p, dl)), splat(2.0f), splat(-1.0f));
+    return ffma2(div_rn_uniform2(p, dn, dh), splat(2.0f), splat(-1.0f));
+}
+
 // ---- 1 spp frame, 4 pixels per thread, one STG.128 of packed RGBA8 per thread -------------
 // Requires width % 4 == 0 (16 B aligned rows).  Block (32,8): a warp covers 128 consecutive
 // pixels of one row = 512 contiguous bytes of RGBA8.
@@ -481,7 +507,7 @@ cudaError_t launch_csmain_frame(const FrameK &k, const Buffers &b, cudaStream_t 
 // block on a 32x4 tile (hit/miss is spatially coherent, so few warps diverge).
 // RNG: pcg3d keyed (pixel, sample, seed); the pixel and seed lanes of its first LCG step are
 // loop-invariant and hoisted.
-template <int MODE, bool JITTER>
+template <int MODE, bool JITTER, bool DIV2>
 __global__ void __launch_bounds__(256) csmain_accumulate(const FrameK k, float4 *__restrict__ accum,
                                                          uint32_t first_sample, uint32_t n_samples, uint32_t seed,
                                                          uint32_t *__restrict__ out8, float spp_total, int bgra)
@@ -501,66 +527,84 @@ __global__ void __launch_bounds__(256) csmain_accumulate(const FrameK k, float4 
     uint32_t i = 0;
     constexpr bool FAST = ModeTraits<MODE>::fast;
     const bool lean = FAST && certain_miss(k, fx, fy);   // every sample of this pixel misses
-    if (FAST && JITTER && lean) {
-        // certain-miss pixels (most of the frame): their own loop, so that the per-pixel invariant `lean` is not tested
-        // per iteration; Test.hlsl:36 for both samples, nothing else to evaluate.  Same operations, same order.
-#pragma unroll 2
-        for (; i + 2 <= n_samples; i += 2) {
-            uint32_t ax = vx0, ay = (first_sample + i) * 1664525u + 1013904223u, az = vz0;
-            uint32_t bx = vx0, by = ay + 1664525u, bz = vz0;
-            ax += ay * az;
-            bx += by * bz;
-            ay += az * ax;
-            by += bz * bx;
-            az += ax * ay;
-            bz += bx * by;
-            ax ^= ax >> 16;
-            bx ^= bx >> 16;
-            ay ^= ay >> 16;
-            by ^= by >> 16;
-            az ^= az >> 16;
-            bz ^= bz >> 16;
-            ax += ay * az;
-            bx += by * bz;
-            ay += az * ax;
-            by += bz * bx;
-            const F2 px = fadd2(splat(fxm1), make_float2(bits_to_unit_plus_one(ax), bits_to_unit_plus_one(bx)));
-            const F2 py = fadd2(splat(fym1), make_float2(bits_to_unit_plus_one(ay), bits_to_unit_plus_one(by)));
-            const F2 uvx2 = screen_uv2(px, k.div_x, k.inv_div_x), uvy2 = screen_uv2(py, k.div_y, k.inv_div_y);
-            sr = fadd(fadd(sr, uvx2.x), uvx2.y);
-            sg = fadd(fadd(sg, uvy2.x), uvy2.y);
-        }
-    }
     if (FAST && JITTER) {
-        // two samples per iteration in FP32x2 lanes; the sums stay sequential in sample order
-        for (; i + 2 <= n_samples; i += 2) {
-            uint32_t ax = vx0, ay = (first_sample + i) * 1664525u + 1013904223u, az = vz0;
-            uint32_t bx = vx0, by = ay + 1664525u, bz = vz0;
-            ax += ay * az;
-            bx += by * bz;
-            ay += az * ax;
-            by += bz * bx;
-            az += ax * ay;
-            bz += bx * by;
-            ax ^= ax >> 16;
-            bx ^= bx >> 16;
-            ay ^= ay >> 16;
-            by ^= by >> 16;
-            az ^= az >> 16;
-            bz ^= bz >> 16;
-            ax += ay * az;
-            bx += by * bz;
-            ay += az * ax;
-            by += bz * bx;
-            const F2 px = fadd2(splat(fxm1), make_float2(bits_to_unit_plus_one(ax), bits_to_unit_plus_one(bx)));
-            const F2 py = fadd2(splat(fym1), make_float2(bits_to_unit_plus_one(ay), bits_to_unit_plus_one(by)));
-            const F2 uvx2 = screen_uv2(px, k.div_x, k.inv_div_x), uvy2 = screen_uv2(py, k.div_y, k.inv_div_y);
-            F2 r, g, b;
-            bool h0, h1;
-            csmain_shade2<MODE>(k, uvx2, uvy2, r, g, b, h0, h1);
-            sr = fadd(fadd(sr, r.x), r.y);
-            sg = fadd(fadd(sg, g.x), g.y);
-            sb = fadd(fadd(sb, b.x), b.y);   // a miss adds +0.0 to a sum that is never -0.0: identity
+        // ---- pcg3d's first round by forward differences -----------------------------------------------------------
+        // The RNG key is (pixel, sample, seed): across the samples of ONE pixel only the middle word moves, linearly
+        // (y0(s) = s*A + C), and the z word starts from the launch constant z0.  Hence, all mod 2^32,
+        //   x1(s) = x0 + y0(s)*z0          is linear in s,      slope alpha = A*z0
+        //   y1(s) = y0(s) + z0*x1(s)       is linear in s,      slope beta  = A + z0*alpha
+        //   z1(s) = z0 + x1(s)*y1(s)       is quadratic in s:   z1(s+1) - z1(s) = D(s),  D(s+1) = D(s) + 2*alpha*beta
+        // so the three multiply-adds of the round (plus the one of y0) become four integer ADDs per sample.  The integer
+        // multiply-adds share the FMA-heavy pipe with the FP32x2 arithmetic — the pipe ncu shows saturated
+        // (math_pipe_throttle) — while the ALU pipe the adds go to had room.  Same 32-bit values, bit for bit.
+        const uint32_t A = 1664525u, C = 1013904223u;
+        const uint32_t z0 = vz0, alpha = A * z0, beta = A + z0 * alpha, ab2 = 2u * alpha * beta;      // launch-uniform
+        const uint32_t y0 = (first_sample + i) * A + C;
+        uint32_t ax = vx0 + y0 * z0;
+        uint32_t ay = y0 + z0 * ax;
+        uint32_t az = z0 + ax * ay;
+        uint32_t dz = ax * beta + ay * alpha + alpha * beta;                                          // D(s)
+        uint32_t alpha2 = 2u * alpha, beta2 = 2u * beta, ab4 = 2u * ab2;
+        keep_form(alpha2, beta2, ab4, dz);
+        if (lean) {
+            // certain-miss pixels (most of the frame): Test.hlsl:36 for every sample, nothing else to evaluate.  The two
+            // FP32x2 lanes carry the x and the y AXIS of one sample, so the sums (sr, sg) are one packed add per sample —
+            // still sequential in sample order, the same additions as the scalar form.
+            const F2 base = make_float2(fxm1, fym1), dn = make_float2(-k.div_x, -k.div_y);
+            const F2 dh = make_float2(k.inv_div_x, k.inv_div_y), dl = make_float2(k.dl_x, k.dl_y);
+            F2 sum = make_float2(0.0f, 0.0f);
+            const uint32_t one = k.one;   // 1, from the parameter block so that ptxas keeps the multiply-add form
+            const uint32_t pairs = (n_samples - i) >> 1;
+            i += 2u * pairs;
+#pragma unroll 4
+            for (uint32_t pr = pairs; pr != 0; --pr) {
+                // The x/y adds go out as multiply-adds by a register holding 1: the ALU pipe (shifts, xors, the float
+                // assembly, 16 lanes per scheduler) is the busier one in this loop, the FMA pipes have room.
+                uint32_t bx = add_on_fma(ax, alpha, one), by = add_on_fma(ay, beta, one), bz = az + dz;   // sample s + 1
+                uint32_t px = ax, py = ay, pz = az, qx = bx, qy = by, qz = bz;
+                ax = add_on_fma(ax, alpha2, one);                             // sample s + 2
+                ay = add_on_fma(ay, beta2, one);
+                az = bz + dz + ab2;
+                dz += ab4;
+                keep_form(ax, ay, az, dz);
+                px ^= px >> 16; py ^= py >> 16; pz ^= pz >> 16;
+                qx ^= qx >> 16; qy ^= qy >> 16; qz ^= qz >> 16;
+                px += py * pz; qx += qy * qz;
+                py += pz * px; qy += qz * qx;
+                const F2 pa = fadd2(base, make_float2(bits_to_unit_plus_one(px), bits_to_unit_plus_one(py)));
+                const F2 pb = fadd2(base, make_float2(bits_to_unit_plus_one(qx), bits_to_unit_plus_one(qy)));
+                sum = fadd2(sum, screen_uv_axes<DIV2>(pa, dn, dh, dl));
+                sum = fadd2(sum, screen_uv_axes<DIV2>(pb, dn, dh, dl));
+            }
+            sr = sum.x;
+            sg = sum.y;
+        } else {
+            // two samples per iteration in FP32x2 lanes; the sums stay sequential in sample order
+            const uint32_t pairs = (n_samples - i) >> 1;
+            i += 2u * pairs;
+            for (uint32_t pr = pairs; pr != 0; --pr) {
+                uint32_t bx = ax + alpha, by = ay + beta, bz = az + dz;
+                uint32_t px = ax, py = ay, pz = az, qx = bx, qy = by, qz = bz;
+                ax += alpha2;
+                ay += beta2;
+                az = bz + dz + ab2;
+                dz += ab4;
+                keep_form(ax, ay, az, dz);
+                px ^= px >> 16; py ^= py >> 16; pz ^= pz >> 16;
+                qx ^= qx >> 16; qy ^= qy >> 16; qz ^= qz >> 16;
+                px += py * pz; qx += qy * qz;
+                py += pz * px; qy += qz * qx;
+                const F2 sx = fadd2(splat(fxm1), make_float2(bits_to_unit_plus_one(px), bits_to_unit_plus_one(qx)));
+                const F2 sy = fadd2(splat(fym1), make_float2(bits_to_unit_plus_one(py), bits_to_unit_plus_one(qy)));
+                const F2 uvx2 = screen_uv_axes<DIV2>(sx, splat(-k.div_x), splat(k.inv_div_x), splat(k.dl_x));
+                const F2 uvy2 = screen_uv_axes<DIV2>(sy, splat(-k.div_y), splat(k.inv_div_y), splat(k.dl_y));
+                F2 r, g, b;
+                bool h0, h1;
+                csmain_shade2<MODE>(k, uvx2, uvy2, r, g, b, h0, h1);
+                sr = fadd(fadd(sr, r.x), r.y);
+                sg = fadd(fadd(sg, g.x), g.y);
+                sb = fadd(fadd(sb, b.x), b.y);   // a miss adds +0.0 to a sum that is never -0.0: identity
+            }
         }
     }
     for (; i < n_samples; ++i) {
@@ -727,8 +771,10 @@ static cudaError_t launch_acc_t(const FrameK &k, float4 *accum, uint32_t first, 
     }();
     const dim3 block(32, by);
     const dim3 grid((k.width + 31) / 32, (shard_rows(k) + by - 1) / by);
-    if (jitter) csmain_accumulate<MODE, true><<<grid, block, 0, s>>>(k, accum, first, n, seed, out8, spp_total, bgra ? 1 : 0);
-    else csmain_accumulate<MODE, false><<<grid, block, 0, s>>>(k, accum, first, n, seed, out8, spp_total, bgra ? 1 : 0);
+    if (jitter && k.div2 && ModeTraits<MODE>::fast)
+        csmain_accumulate<MODE, true, true><<<grid, block, 0, s>>>(k, accum, first, n, seed, out8, spp_total, bgra ? 1 : 0);
+    else if (jitter) csmain_accumulate<MODE, true, false><<<grid, block, 0, s>>>(k, accum, first, n, seed, out8, spp_total, bgra ? 1 : 0);
+    else csmain_accumulate<MODE, false, false><<<grid, block, 0, s>>>(k, accum, first, n, seed, out8, spp_total, bgra ? 1 : 0);
     return cudaGetLastError();
 }
 

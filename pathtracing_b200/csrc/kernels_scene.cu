@@ -415,6 +415,7 @@ struct WaveArgs {
     float4 *slices;
     int jitter;
     int tail;                 // 1: finish every path of this launch in-kernel (bounce loop, no more queues)
+    uint32_t refill;          // bounce_kernel: walkers pause for a refill when fewer than this many lanes of the warp walk
     float4 *accum;
     int32_t *hit_ids;
     SceneStatsDev *stats;
@@ -423,8 +424,22 @@ struct WaveArgs {
 
 constexpr uint32_t PIX_BITS = 26u, PIX_MASK = (1u << PIX_BITS) - 1u;
 
+// Test.hlsl:7 for pixel (x, y), sample `s_local` of the wave (jittered inside the pixel when the wave asks for it)
+__device__ __forceinline__ void camera_uv(const SceneK &k, const WaveArgs &w, uint32_t x, uint32_t y, uint32_t s_local, float &uvx,
+                                          float &uvy)
+{
+    float fx = (float)x, fy = (float)y;
+    if (w.jitter) {
+        const U3 v = pcg3d(y * k.width + x, w.sample + s_local, k.seed);
+        fx = fx + bits_to_unit(v.x);
+        fy = fy + bits_to_unit(v.y);
+    }
+    uvx = (fx / k.div_x) * 2.0f - 1.0f;
+    uvy = (fy / k.div_y) * 2.0f - 1.0f;
+}
+
 template <bool DEPTH0, bool STATS>
-__global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(const SceneK k, const WaveArgs w)
+__global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel_chunk(const SceneK k, const WaveArgs w)
 {
     const unsigned lane = threadIdx.x & 31u;
     const uint32_t n_in = DEPTH0 ? w.n0 : *w.n_in;
@@ -588,6 +603,294 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
     }
 }
 
+// ---- the per-bounce kernel, per-lane refill ----------------------------------------------------------------------------
+// Same work as bounce_kernel_chunk above, other schedule.  There a warp takes 32 paths and keeps them until the longest walk
+// among them has ended: behind the first bounce the walks of one warp differ several-fold in length and the kernel ran at
+// 7-12 active threads per instruction (profiles/r01_c3_bounce_ncu.txt).  Here every LANE owns a path: when fewer than
+// w.refill lanes of the warp are still walking, the walkers pause (their traversal state — current reference, stack, closest
+// hit — simply stays where it is), the lanes whose walk has ended shade and scatter their paths together, fetch new paths
+// from the cursor (one atomicAdd per warp for all its free lanes) and the warp goes back to walking with all lanes busy
+// (Aila & Laine 2009, "persistent while-while with dynamic fetch").  In tail mode a path that scatters stays in its lane and
+// starts its next walk at once, so the tail launch is a persistent path tracer with no idle lanes until the cursor runs dry.
+// The traversal stack's first SS_N levels live in shared memory, one 4-byte column per thread ([level][thread]: whatever
+// the lanes' depths, one access is one conflict-free wavefront); deeper levels spill to local memory.
+// Which lane traces a path and in which order the queues fill changes nothing in any result: every path's arithmetic is
+// its own, radiance goes to the path's own slot (or its pixel's only live path), ties go to the smaller id.
+#ifndef PTB_REFILL_DEFAULT
+#define PTB_REFILL_DEFAULT 20
+#endif
+#ifndef PTB_SHORT_STACK
+#define PTB_SHORT_STACK 12
+#endif
+constexpr int SS_N = PTB_SHORT_STACK;
+
+template <bool DEPTH0, bool STATS>
+__global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(const SceneK k, const WaveArgs w)
+{
+    __shared__ int s_stack[SS_N][256];
+    __shared__ int s_live[8];
+    const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    const uint32_t n_in = DEPTH0 ? w.n0 : *w.n_in;
+    const int first_cls = k.sph_root != EMPTY_REF ? 0 : 1;
+    const int first_root = k.sph_root != EMPTY_REF ? k.sph_root : k.tri_root;      // EMPTY_REF: a scene without primitives
+    const float INF = __int_as_float(0x7F800000);
+    Counters cn;
+    uint32_t n_rays = 0, n_scatter = 0;
+    int lstack[STACK_N - SS_N];
+    bool has = false;                  // this lane holds a path (walking, or walked and not shaded yet)
+    bool exhausted = false;            // warp-uniform: the cursor has run past the queue
+    int cur = EMPTY_REF, sp = 0, cls = 0;
+    RayT r;
+    make_ray(r, 0.f, 0.f, 0.f, 0.f, 0.f, 1.f);
+    Best best;
+    best.t = INF; best.t_cull = INF; best.id = -1; best.pos = 0; best.cls = 0;
+    float tr = 1.0f, tg = 1.0f, tb = 1.0f;
+    uint32_t idw = 0;                  // shard-local pixel index | sample of the wave << PIX_BITS
+    uint32_t depth = w.depth;
+
+#define PTB_PUSH(v)                                                                                                    \
+    do {                                                                                                               \
+        if (sp < SS_N) s_stack[sp][tid] = (v);                                                                         \
+        else if (sp < STACK_N) lstack[sp - SS_N] = (v);                                                                \
+        if (sp < STACK_N) {                                                                                            \
+            ++sp;                                                                                                      \
+            if (STATS) cn.max_stack = max(cn.max_stack, (uint32_t)sp);                                                 \
+        } else {                                                                                                       \
+            atomicOr(w.error_flag, 1u);                                                                                \
+        }                                                                                                              \
+    } while (0)
+#define PTB_POP()                                                                                                      \
+    do {                                                                                                               \
+        if (sp > 0) {                                                                                                  \
+            --sp;                                                                                                      \
+            cur = sp < SS_N ? s_stack[sp][tid] : lstack[sp - SS_N];                                                    \
+        } else {                                                                                                       \
+            cur = EMPTY_REF;                                                                                           \
+        }                                                                                                              \
+    } while (0)
+#define PTB_START_WALK()                                                                                               \
+    do {                                                                                                               \
+        best.t = INF; best.t_cull = INF; best.id = -1; best.pos = 0; best.cls = 0;                                     \
+        cur = first_root; cls = first_cls; sp = 0;                                                                     \
+    } while (0)
+
+    for (;;) {
+        // ---- refill: every lane without a path takes the next one of the queue ----
+        const unsigned idle = __ballot_sync(FULL, !has);
+        if (idle != 0u && !exhausted) {                      // warp-uniform
+            const uint32_t n = (uint32_t)__popc(idle);
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(w.cursor, n);
+            base = __shfl_sync(FULL, base, 0);
+            exhausted = base >= n_in || n_in - base <= n;
+            const uint32_t i = base + (uint32_t)__popc(idle & lt);
+            if (!has && i < n_in) {
+                if (DEPTH0) {
+                    // path i = lane (i & 31) of 8x4 pixel tile (i >> 5): primary rays fetched together stay close in BOTH
+                    // image axes (32x1 strips were measurably less coherent on the 4K terrain), and the compacted queues
+                    // inherit the locality
+                    uint32_t tile = i >> 5, s_local = 0;
+                    if (w.batch > 1u) {                      // launch-uniform
+                        s_local = tile / w.tiles;
+                        tile -= s_local * w.tiles;
+                    }
+                    const uint32_t x = (tile % w.tiles_x) * 8u + (i & 7u), yy = (tile / w.tiles_x) * 4u + ((i >> 3) & 3u);
+                    if (x < k.width && yy < w.rows) {
+                        const uint32_t y = shard_row(k.row_offset, k.row_stride, k.row_block, yy);
+                        float uvx, uvy;
+                        camera_uv(k, w, x, y, s_local, uvx, uvy);
+                        float dx = (uvx * k.cam_u[0] + uvy * k.cam_v[0]) + k.cam_w[0];   // Test.hlsl:10 with a camera basis
+                        float dy = (uvx * k.cam_u[1] + uvy * k.cam_v[1]) + k.cam_w[1];
+                        float dz = (uvx * k.cam_u[2] + uvy * k.cam_v[2]) + k.cam_w[2];
+                        normalize3f(dx, dy, dz);
+                        make_ray(r, k.cam_o[0], k.cam_o[1], k.cam_o[2], dx, dy, dz);     // Test.hlsl:8
+                        idw = (yy * k.width + x) | (s_local << PIX_BITS);
+                        tr = tg = tb = 1.0f;
+                        has = true;
+                    }
+                } else {
+                    // streaming (evict-first) access: the path state is touched once per bounce and must not
+                    // push the hierarchy out of L2
+                    const float4 s0 = __ldcs(&w.in.s0[i]), s1 = __ldcs(&w.in.s1[i]);
+                    const float2 s2 = __ldcs(&w.in.s2[i]);
+                    make_ray(r, s0.x, s0.y, s0.z, s1.x, s1.y, s1.z);
+                    idw = __float_as_uint(s0.w);
+                    tr = s1.w; tg = s2.x; tb = s2.y;
+                    has = true;
+                }
+                if (has) {
+                    depth = w.depth;
+                    PTB_START_WALK();
+                }
+            }
+        }
+        const bool walking = has && cur != EMPTY_REF;
+        const unsigned walkers = __ballot_sync(FULL, walking);
+        if (__ballot_sync(FULL, has) == 0u) {
+            if (exhausted) break;
+            continue;                                        // depth 0: a fetch of tile padding only
+        }
+
+        // ---- walk: until this lane's closest hit is known, or too few lanes of the warp are still walking ----
+        const int live0 = __popc(walkers);
+        // pausing pays only if the paused warp can do something else: shade-and-continue (tail) or fetch (queue not dry)
+        const int pause_below = (exhausted && !w.tail) ? 0 : min((int)w.refill, live0);
+        if (lane == 0) s_live[warp] = live0;
+        __syncwarp();
+        if (walking) {
+            for (;;) {
+                const BvhNode *__restrict__ nodes = cls == 0 ? k.sph_nodes : k.tri_nodes;
+                while (cur >= 0) {
+                    const float4 na = __ldg(&nodes[cur].a), nb = __ldg(&nodes[cur].b), nc = __ldg(&nodes[cur].c);
+                    const int4 nd = __ldg(&nodes[cur].d);
+                    if (STATS) ++cn.nodes;
+                    float tn0, tn1;
+                    const bool h0 = slab<true>(na.x, na.y, na.z, na.w, nc.x, nc.y, r, k.t_min, best.t_cull, tn0);
+                    const bool h1 = slab<true>(nb.x, nb.y, nb.z, nb.w, nc.z, nc.w, r, k.t_min, best.t_cull, tn1) && nd.y != EMPTY_REF;
+                    if (h0 && h1) {
+                        const bool swap = tn1 < tn0;
+                        cur = swap ? nd.y : nd.x;
+                        PTB_PUSH(swap ? nd.x : nd.y);
+                    } else if (h0) {
+                        cur = nd.x;
+                    } else if (h1) {
+                        cur = nd.y;
+                    } else {
+                        PTB_POP();
+                    }
+                }
+                if (cur != EMPTY_REF) {
+                    uint32_t prims = 0;
+                    if (cls == 0) test_leaf<0, false>(k, cur, r, k.t_min, INF, best, prims);
+                    else test_leaf<1, false>(k, cur, r, k.t_min, INF, best, prims);
+                    if (STATS) cn.prims += prims;
+                    PTB_POP();
+                }
+                if (cur == EMPTY_REF) {
+                    if (cls == 0 && k.tri_root != EMPTY_REF) {       // spheres done: the triangle hierarchy next
+                        cls = 1;
+                        cur = k.tri_root;
+                        continue;
+                    }
+                    atomicSub(&s_live[warp], 1);
+                    break;
+                }
+                if (*(volatile int *)&s_live[warp] < pause_below) break;
+            }
+        }
+        __syncwarp();
+
+        // ---- shade and scatter the paths whose walk has ended ----
+        bool cont = false;                                   // goes to the next bounce's queue
+        float Px = 0, Py = 0, Pz = 0;
+        if (has && cur == EMPTY_REF) {
+            const bool hit = best.id >= 0;
+            const uint32_t s_local = w.batch > 1u ? idw >> PIX_BITS : 0u;
+            const uint32_t loc = w.batch > 1u ? idw & PIX_MASK : idw;
+            const uint32_t yy = loc / k.width, x = loc - yy * k.width;
+            const uint32_t y = shard_row(k.row_offset, k.row_stride, k.row_block, yy);
+            const uint32_t pix = y * k.width + x;
+            float cr = 0.0f, cg = 0.0f, cb = 0.0f;           // radiance this path adds now
+            bool add = false, alive = true;
+            if (STATS) ++n_rays;
+            if (DEPTH0 && w.hit_ids) w.hit_ids[pix] = hit ? best.id : -1;
+            float nx = 0, ny = 0, nz = 0;
+            uint32_t mat = 0;
+            float dx = r.dx, dy = r.dy, dz = r.dz;
+            if (hit) {
+                Px = r.ox + best.t * dx; Py = r.oy + best.t * dy; Pz = r.oz + best.t * dz;      // Test.hlsl:28
+                hit_frame(k, best, Px, Py, Pz, nx, ny, nz, mat);
+            }
+            if (k.shade_mode == PTB_SHADE_NORMALS) {
+                if (hit) {
+                    cr = nx * 0.5f + 0.5f; cg = ny * 0.5f + 0.5f; cb = nz * 0.5f + 0.5f;         // Test.hlsl:31
+                } else {
+                    camera_uv(k, w, x, y, s_local, cr, cg);                                      // Test.hlsl:36
+                    cb = 0.0f;
+                }
+                add = true;
+                alive = false;
+            } else if (!hit) {
+                const float a = (dy + 1.0f) * 0.5f;
+                cr = tr * ((1.0f - a) * k.sky_h[0] + a * k.sky_z[0]);
+                cg = tg * ((1.0f - a) * k.sky_h[1] + a * k.sky_z[1]);
+                cb = tb * ((1.0f - a) * k.sky_h[2] + a * k.sky_z[2]);
+                add = true;
+                alive = false;
+            } else if (depth == k.max_depth) {
+                alive = false;                               // bounce budget spent: contributes nothing
+            } else {
+                const ptb_material m = k.materials[mat < k.n_materials ? mat : 0u];
+                const U3 v = pcg3d(pix, w.sample + s_local, k.seed + (depth + 1u) * 0x9E3779B9u);
+                if (STATS) ++n_scatter;
+                if (scatter(m, dx, dy, dz, nx, ny, nz, bits_to_unit(v.x), bits_to_unit(v.y), bits_to_unit(v.z))) {
+                    tr = tr * m.albedo[0]; tg = tg * m.albedo[1]; tb = tb * m.albedo[2];
+                } else {
+                    alive = false;
+                }
+            }
+            if (w.slices) {                                  // launch-uniform: batched wave
+                // every path stores its slot at depth 0 (zero radiance while it is still alive) and once more when it ends
+                if (DEPTH0 || add) __stcs(&w.slices[(size_t)s_local * w.n0_pixels + loc], make_float4(cr, cg, cb, 1.0f));
+            } else if (DEPTH0) {
+                float4 acc = w.accum[pix];
+                acc.x = acc.x + cr; acc.y = acc.y + cg; acc.z = acc.z + cb; acc.w = acc.w + 1.0f;
+                w.accum[pix] = acc;
+            } else if (add) {
+                float4 acc = w.accum[pix];
+                acc.x = acc.x + cr; acc.y = acc.y + cg; acc.z = acc.z + cb;
+                w.accum[pix] = acc;
+            }
+            if (!alive) {
+                has = false;
+            } else if (!DEPTH0 && w.tail) {                  // launch-uniform: the path stays in this lane
+                make_ray(r, Px, Py, Pz, dx, dy, dz);
+                ++depth;
+                PTB_START_WALK();
+            } else {
+                r.dx = dx; r.dy = dy; r.dz = dz;
+                cont = true;
+                has = false;
+            }
+        }
+        // queue compaction: warp ballot + prefix popcount, one atomic per warp
+        const unsigned outm = __ballot_sync(FULL, cont);
+        if (outm != 0u) {
+            uint32_t obase = 0;
+            if (lane == 0) obase = atomicAdd(w.n_out, (uint32_t)__popc(outm));
+            obase = __shfl_sync(FULL, obase, 0);
+            if (cont) {
+                const uint32_t o = obase + (uint32_t)__popc(outm & lt);
+                __stcs(&w.out.s0[o], make_float4(Px, Py, Pz, __uint_as_float(idw)));
+                __stcs(&w.out.s1[o], make_float4(r.dx, r.dy, r.dz, tr));
+                __stcs(&w.out.s2[o], make_float2(tg, tb));
+            }
+        }
+    }
+#undef PTB_PUSH
+#undef PTB_POP
+#undef PTB_START_WALK
+    if (STATS) {
+        unsigned long long v[4] = {cn.nodes, cn.prims, n_rays, n_scatter};
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int o = 16; o; o >>= 1) v[j] += __shfl_xor_sync(FULL, v[j], o);
+        uint32_t ms = cn.max_stack;
+#pragma unroll
+        for (int o = 16; o; o >>= 1) ms = max(ms, __shfl_xor_sync(FULL, ms, o));
+        if (lane == 0) {
+            atomicAdd(&w.stats->nodes_visited, v[0]);
+            atomicAdd(&w.stats->prims_tested, v[1]);
+            atomicAdd(&w.stats->rays, v[2]);
+            atomicAdd(&w.stats->scatters, v[3]);
+            atomicMax(&w.stats->max_stack, (unsigned long long)ms);
+            if (DEPTH0 && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&w.stats->paths, (unsigned long long)w.n0_pixels * w.batch);
+        }
+    }
+}
+
 // ---- upload helpers -------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) sphere_bounds_kernel(const float4 *__restrict__ sph, uint32_t n, float4 *lo, float4 *hi)
 {
@@ -685,21 +988,29 @@ __global__ void __launch_bounds__(256) trace_rays_kernel(const SceneK k, uint64_
     }
 }
 
-int g_wave_blocks[2][2] = {{0, 0}, {0, 0}};
+int g_wave_blocks[2][2][2] = {};
 
-template <bool DEPTH0, bool STATS>
+template <bool DEPTH0, bool STATS, bool CHUNK>
 int wave_blocks()
 {
-    int &cached = g_wave_blocks[DEPTH0][STATS];
+    int &cached = g_wave_blocks[DEPTH0][STATS][CHUNK];
     if (cached == 0) {
         int per_sm = 0, dev = 0, sms = 148;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bounce_kernel<DEPTH0, STATS>, 256, 0) != cudaSuccess || per_sm < 1)
-            per_sm = 1;
+        const cudaError_t e = CHUNK ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bounce_kernel_chunk<DEPTH0, STATS>, 256, 0)
+                                    : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bounce_kernel<DEPTH0, STATS>, 256, 0);
+        if (e != cudaSuccess || per_sm < 1) per_sm = 1;
         cached = per_sm * sms;
     }
     return cached;
+}
+
+template <bool DEPTH0, bool STATS>
+void launch_bounce(const SceneK &k, const WaveArgs &w, bool chunk, cudaStream_t s)
+{
+    if (chunk) bounce_kernel_chunk<DEPTH0, STATS><<<wave_blocks<DEPTH0, STATS, true>(), 256, 0, s>>>(k, w);
+    else bounce_kernel<DEPTH0, STATS><<<wave_blocks<DEPTH0, STATS, false>(), 256, 0, s>>>(k, w);
 }
 
 }  // namespace
@@ -738,7 +1049,8 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
     if (n0_pixels == 0) return cudaSuccess;
     const uint32_t tiles_x = (k.width + 7u) / 8u, tiles_y = (rows + 3u) / 4u;
     const uint64_t n0_64 = (uint64_t)tiles_x * tiles_y * 32u * batch;
-    if (n0_64 > 0xFFFFFFFFull) return cudaErrorInvalidValue;      // scene.cu sizes waves so that this cannot happen
+    if (n0_64 > 0xFFF00000ull) return cudaErrorInvalidValue;      // scene.cu sizes waves so that this cannot happen (the
+                                                                  // margin: every warp runs the cursor past the end once)
     const uint32_t n0 = (uint32_t)n0_64;
     const uint32_t depths = k.shade_mode == PTB_SHADE_NORMALS ? 1u : k.max_depth + 1u;
     // bounces >= tail_depth run inside ONE launch (0 disables): queues that deep are too small to fill the GPU, unless the
@@ -748,6 +1060,12 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
         const char *e = std::getenv("PTB200_TAIL_DEPTH");
         return e ? std::atoi(e) : -1;
     }();
+    // A/B switches for profiling runs: PTB200_BOUNCE=chunk selects the 32-paths-per-warp schedule, PTB200_REFILL the number
+    // of walking lanes below which a warp pauses to shade and refetch (0: never).
+    const char *e_bounce = std::getenv("PTB200_BOUNCE"), *e_refill = std::getenv("PTB200_REFILL");
+    const bool chunk = e_bounce && e_bounce[0] == 'c';
+    const int refill_i = e_refill ? std::atoi(e_refill) : PTB_REFILL_DEFAULT;
+    const uint32_t refill = (uint32_t)(refill_i < 0 ? 0 : refill_i > 32 ? 32 : refill_i);
     const uint32_t tail_depth = tail_env >= 0 ? (uint32_t)tail_env : ((uint64_t)n0_pixels * batch >= (8u << 20) ? 6u : 4u);
     // counters: [0, depths] queue sizes, [depths+1, 2*depths+1] work cursors
     cudaError_t e = cudaMemsetAsync(st->counts, 0, sizeof(uint32_t) * st->counts_len, s);
@@ -774,12 +1092,13 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
         w.hit_ids = hit_ids;
         w.stats = st->stats;
         w.error_flag = st->error_flag;
+        w.refill = refill;
         if (d == 0) {
-            if (st->count_stats) bounce_kernel<true, true><<<wave_blocks<true, true>(), 256, 0, s>>>(k, w);
-            else bounce_kernel<true, false><<<wave_blocks<true, false>(), 256, 0, s>>>(k, w);
+            if (st->count_stats) launch_bounce<true, true>(k, w, chunk, s);
+            else launch_bounce<true, false>(k, w, chunk, s);
         } else {
-            if (st->count_stats) bounce_kernel<false, true><<<wave_blocks<false, true>(), 256, 0, s>>>(k, w);
-            else bounce_kernel<false, false><<<wave_blocks<false, false>(), 256, 0, s>>>(k, w);
+            if (st->count_stats) launch_bounce<false, true>(k, w, chunk, s);
+            else launch_bounce<false, false>(k, w, chunk, s);
         }
         if (launches) ++*launches;
         if (w.tail) break;

@@ -27,6 +27,9 @@ struct FrameK {
     float radius;
     // derived on the device:
     float inv_div_x, inv_div_y;   // RN(1/div)
+    float dl_x, dl_y;             // RN(1/div - RN(1/div)): low part of the reciprocal (host, from binary64)
+    uint32_t div2;                // 1: the 2-instruction constant division is verified for both divisors
+    uint32_t one;                 // always 1 (csmain_accumulate: integer adds issued as multiply-adds on the FMA pipe)
     float oc[3];                  // :16 cam - centre
     float c;                      // :19 dot(oc,oc) - r*r
     float c4;                     // 4*c (exact scaling)
@@ -76,10 +79,13 @@ cudaError_t selftest_row_span(const FrameK &k, const uint2 *row_span, unsigned l
                               cudaStream_t s);
 // selftest.cu — exhaustive proofs of the short exact sequences in ptb_math.cuh
 //   which: 0 = sqrt_rn_fast over [2^-20,2^24), 1 = rcp_rn_fast over [2^-12,2^12),
-//          2 = div_rn_uniform(v, D) for v in {0} U [2^-24, 2^17)
+//          2 = div_rn_uniform(v, D) for v in {0} U [2^-24, 2^17), 5 = the split-reciprocal form fma(v, dh, v*dl) likewise
 cudaError_t selftest_exact(int which, float D, unsigned long long *mismatches, unsigned long long *tested,
                            cudaStream_t s);
-bool uniform_divisor_verified(float D, cudaStream_t s);      // cached per (device, D)
+// cached per (device, D); bit 0: the one-correction (3-instruction) division is exact for D, bit 1: so is the
+// 2-instruction split-reciprocal form
+int uniform_divisor_verified(float D, cudaStream_t s);
+float reciprocal_low(float D);                               // RN(1/D - RN(1/D)), evaluated in binary64
 
 // kernels_image.cu
 cudaError_t image_tables_init();   // sRGB tables -> __constant__ (once per device)

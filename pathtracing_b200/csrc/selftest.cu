@@ -22,7 +22,7 @@ struct SelfCounts {
 };
 
 template <int WHICH>
-__global__ void __launch_bounds__(256) selftest_kernel(uint32_t lo_bits, uint32_t hi_bits, float D, float Dh,
+__global__ void __launch_bounds__(256) selftest_kernel(uint32_t lo_bits, uint32_t hi_bits, float D, float Dh, float Dl,
                                                        SelfCounts *out)
 {
     unsigned long long bad = 0, n = 0;
@@ -36,8 +36,11 @@ __global__ void __launch_bounds__(256) selftest_kernel(uint32_t lo_bits, uint32_
         } else if (WHICH == 1) {
             got = rcp_rn_fast(v);
             ref = __frcp_rn(v);
-        } else {
+        } else if (WHICH == 2) {
             got = div_rn_uniform(v, D, Dh);
+            ref = __fdiv_rn(v, D);
+        } else {
+            got = ffma(v, Dh, fmul(v, Dl));       // the split-reciprocal division of kernels_csmain.cu screen_uv_axes<true>
             ref = __fdiv_rn(v, D);
         }
         bad += (__float_as_uint(got) != __float_as_uint(ref));
@@ -61,6 +64,12 @@ static uint32_t f2u(float f)
     return u;
 }
 
+float reciprocal_low(float D)
+{
+    const float dh = 1.0f / D;
+    return (float)(1.0 / (double)D - (double)dh);
+}
+
 cudaError_t selftest_exact(int which, float D, unsigned long long *mismatches, unsigned long long *tested,
                            cudaStream_t s)
 {
@@ -71,13 +80,15 @@ cudaError_t selftest_exact(int which, float D, unsigned long long *mismatches, u
     const int grid = 148 * 8, block = 256;
     if (e == cudaSuccess) {
         if (which == 0) {
-            selftest_kernel<0><<<grid, block, 0, s>>>(f2u(9.5367431640625e-7f) /*2^-20*/, f2u(16777216.0f), 0.f, 0.f, d);
+            selftest_kernel<0><<<grid, block, 0, s>>>(f2u(9.5367431640625e-7f) /*2^-20*/, f2u(16777216.0f), 0.f, 0.f, 0.f, d);
         } else if (which == 1) {
-            selftest_kernel<1><<<grid, block, 0, s>>>(f2u(2.44140625e-4f) /*2^-12*/, f2u(4096.0f), 0.f, 0.f, d);
+            selftest_kernel<1><<<grid, block, 0, s>>>(f2u(2.44140625e-4f) /*2^-12*/, f2u(4096.0f), 0.f, 0.f, 0.f, d);
         } else {
             const float Dh = 1.0f / D;   // RN(1/D): IEEE binary32 division on the host == __frcp_rn(D) on the device
             // v = 0 is covered analytically (0*Dh = 0, fma(-0,D,0) = 0, fma(0,Dh,0) = 0 == 0/D for finite D != 0)
-            selftest_kernel<2><<<grid, block, 0, s>>>(f2u(5.9604644775390625e-8f) /*2^-24*/, f2u(131072.0f), D, Dh, d);
+            const float Dl = reciprocal_low(D);
+            if (which == 2) selftest_kernel<2><<<grid, block, 0, s>>>(f2u(5.9604644775390625e-8f) /*2^-24*/, f2u(131072.0f), D, Dh, Dl, d);
+            else selftest_kernel<5><<<grid, block, 0, s>>>(f2u(5.9604644775390625e-8f) /*2^-24*/, f2u(131072.0f), D, Dh, Dl, d);
         }
         e = cudaGetLastError();
     }
@@ -89,22 +100,25 @@ cudaError_t selftest_exact(int which, float D, unsigned long long *mismatches, u
     return e;
 }
 
-bool uniform_divisor_verified(float D, cudaStream_t s)
+int uniform_divisor_verified(float D, cudaStream_t s)
 {
     static std::mutex mu;
-    static std::map<std::pair<int, uint32_t>, bool> cache;
-    // the sequence is sign-symmetric and exponent-shift invariant only away from under/overflow,
+    static std::map<std::pair<int, uint32_t>, int> cache;
+    // the sequences are sign-symmetric and exponent-shift invariant only away from under/overflow,
     // so each distinct D in the supported magnitude window is verified on its own.
     const float a = D < 0 ? -D : D;
-    if (!(a >= 1.0f / 1048576.0f && a <= 1048576.0f)) return false;   // also rejects NaN/inf/0
+    if (!(a >= 1.0f / 1048576.0f && a <= 1048576.0f)) return 0;   // also rejects NaN/inf/0
     int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return false;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
     std::lock_guard<std::mutex> lock(mu);
     const auto key = std::make_pair(dev, f2u(D));
     auto it = cache.find(key);
     if (it != cache.end()) return it->second;
     unsigned long long bad = 1, n = 0;
-    const bool ok = selftest_exact(2, D, &bad, &n, s) == cudaSuccess && bad == 0 && n > 0;
+    int ok = (selftest_exact(2, D, &bad, &n, s) == cudaSuccess && bad == 0 && n > 0) ? 1 : 0;
+    bad = 1;
+    n = 0;
+    if (ok && selftest_exact(5, D, &bad, &n, s) == cudaSuccess && bad == 0 && n > 0) ok |= 2;
     cache[key] = ok;
     return ok;
 }
