@@ -1,6 +1,6 @@
 """ncu target for the bounce kernels: one warm-up wave and one profiled wave per schedule, in ONE process.
    python experiments/prof_scene.py c3|c4 [samples per wave]
-Launch order: [chunk warm-up: d0..tail][chunk: d0..tail][refill warm-up][refill]; with waves of >= 8 Mi camera rays the tail
+Launch order: [chunk warm-up: d0..tail][chunk: d0..tail][queue warm-up][queue]; with waves of >= 8 Mi camera rays the tail
 starts at depth 6, i.e. 7 bounce launches per wave."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -15,7 +15,7 @@ else:
 with NativeTracer(w, h, max_depth=8) as t:
     t.upload_scene(sc)
     t.set_wave_samples(pw)
-    for mode in ("chunk", "refill"):
+    for mode in ("chunk", "queue"):
         os.environ["PTB200_BOUNCE"] = mode
         for rep in range(2):
             t.timer_begin(); t.render_samples(rep * pw, pw); ms = t.timer_end()

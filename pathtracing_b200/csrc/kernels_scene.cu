@@ -603,34 +603,70 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel_chun
     }
 }
 
-// ---- the per-bounce kernel, per-lane refill ----------------------------------------------------------------------------
-// Same work as bounce_kernel_chunk above, other schedule.  There a warp takes 32 paths and keeps them until the longest walk
-// among them has ended: behind the first bounce the walks of one warp differ several-fold in length and the kernel ran at
-// 7-12 active threads per instruction (profiles/r01_c3_bounce_ncu.txt).  Here every LANE owns a path: when fewer than
-// w.refill lanes of the warp are still walking, the walkers pause (their traversal state — current reference, stack, closest
-// hit — simply stays where it is), the lanes whose walk has ended shade and scatter their paths together, fetch new paths
-// from the cursor (one atomicAdd per warp for all its free lanes) and the warp goes back to walking with all lanes busy
-// (Aila & Laine 2009, "persistent while-while with dynamic fetch").  In tail mode a path that scatters stays in its lane and
-// starts its next walk at once, so the tail launch is a persistent path tracer with no idle lanes until the cursor runs dry.
+// ---- the per-bounce kernel: lockstep node steps, per-warp leaf queue, per-lane refill ----------------------------------
+// Same work as bounce_kernel_chunk above, other schedule.  There every lane walks its hierarchy on its own: at any moment some
+// lanes of a warp test boxes, some test primitives, some have finished, and behind the first bounce the kernel ran at 6-12
+// active threads per instruction — boxes at 16, primitives at 6.5 (profiles/r02_notes.md).  Here
+//   * a walk is a sequence of NODE STEPS taken by the whole warp together: every walking lane fetches its node, tests the two
+//     child boxes, descends / pushes / pops.  A child that is a leaf is not visited: it goes, as a (lane, class, leaf)
+//     word, into a queue the warp keeps in shared memory (slots by ballot + popcount: the warp is converged there);
+//   * whenever the queue holds 32 leaves the warp tests 32 leaves at once, one per lane, whatever path they belong to:
+//     the lane reads the owner's ray from shared memory and folds its leaf's best hit into the owner's closest-hit word with
+//     one shared-memory atomicMin on (t bits << 32 | primitive id) — t > t_min >= 0, so the integer order is the order of
+//     (t, id) and the tie rule "equal t: the smaller id wins" comes for free.  The owner meanwhile walks on with the culling
+//     distance it knew (a stale distance only visits more nodes; what is found is the minimum over a superset);
+//   * every LANE owns a path: when fewer than w.refill lanes are still walking, the queue is flushed, the lanes whose walk has
+//     ended shade and scatter their paths together, take new paths from the cursor (one atomicAdd per warp for all its free
+//     lanes) and the warp walks on with all lanes busy (Aila & Laine 2009, dynamic fetch).  In tail mode a path that
+//     scatters stays in its lane and starts its next walk at once: a persistent path tracer until the cursor runs dry.
 // The traversal stack's first SS_N levels live in shared memory, one 4-byte column per thread ([level][thread]: whatever
 // the lanes' depths, one access is one conflict-free wavefront); deeper levels spill to local memory.
-// Which lane traces a path and in which order the queues fill changes nothing in any result: every path's arithmetic is
-// its own, radiance goes to the path's own slot (or its pixel's only live path), ties go to the smaller id.
+// Which lane traces a path, in which order primitives are tested and the queues fill changes nothing in any result: every
+// path's arithmetic is its own, its radiance goes to its own slot (or its pixel's only live path), the closest hit is a
+// minimum.
 #ifndef PTB_REFILL_DEFAULT
-#define PTB_REFILL_DEFAULT 20
+#define PTB_REFILL_DEFAULT 8
 #endif
 #ifndef PTB_SHORT_STACK
 #define PTB_SHORT_STACK 12
 #endif
+#ifndef PTB_QUEUE_MIN_BLOCKS
+#define PTB_QUEUE_MIN_BLOCKS 4
+#endif
 constexpr int SS_N = PTB_SHORT_STACK;
+constexpr uint32_t Q_CAP = 32u + 32u * 2u;                     // < 32 leaves waiting + two per lane and node step
+constexpr unsigned long long NO_HIT = 0x7F800000FFFFFFFFull;   // t = +inf, id = -1
+
+// What a lane keeps of its ray while it walks: the slab form only.  Origin, direction and the two sphere constants live in
+// shared memory (s_ray), where the lane that tests one of this path's leaves reads them; throughput, pixel and depth are
+// needed again only when the path is shaded and stay in local memory.
+struct WalkRay {
+    float ix, iy, iz, px, py, pz;
+};
+
+// the FMA form of slab<> on the six numbers a walking lane keeps in registers
+__device__ __forceinline__ bool slab_walk(float lox, float hix, float loy, float hiy, float loz, float hiz, const WalkRay &r,
+                                          float t_min, float t_far, float &t_near)
+{
+    const float ax = fmaf(lox, r.ix, r.px), bx = fmaf(hix, r.ix, r.px);
+    const float ay = fmaf(loy, r.iy, r.py), by = fmaf(hiy, r.iy, r.py);
+    const float az = fmaf(loz, r.iz, r.pz), bz = fmaf(hiz, r.iz, r.pz);
+    t_near = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
+    const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_far));
+    return t_near <= fmaf(fabsf(tf), 1.9073486e-6f, tf);     // widened away from zero whatever the sign of tf
+}
 
 template <bool DEPTH0, bool STATS>
-__global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(const SceneK k, const WaveArgs w)
+__global__ void __launch_bounds__(256, PTB_QUEUE_MIN_BLOCKS) bounce_kernel(const SceneK k, const WaveArgs w)
 {
     __shared__ int s_stack[SS_N][256];
-    __shared__ int s_live[8];
-    const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    __shared__ float s_ray[8][256];                    // o.xyz, d.xyz, 2 d.d, 4 d.d of the path in each lane
+    __shared__ unsigned long long s_best[256];         // its closest hit so far: t bits << 32 | id
+    __shared__ uint32_t s_pos[256];                    // ... leaf-order position | class << 31
+    __shared__ unsigned long long s_queue[8][Q_CAP];   // per warp: lane << 59 | class << 58 | ~(leaf reference)
+    const unsigned tid = threadIdx.x, lane = tid & 31u, wbase = tid & ~31u;
     const unsigned lt = (1u << lane) - 1u;
+    unsigned long long *const queue = s_queue[tid >> 5];
     const uint32_t n_in = DEPTH0 ? w.n0 : *w.n_in;
     const int first_cls = k.sph_root != EMPTY_REF ? 0 : 1;
     const int first_root = k.sph_root != EMPTY_REF ? k.sph_root : k.tri_root;      // EMPTY_REF: a scene without primitives
@@ -638,42 +674,69 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
     Counters cn;
     uint32_t n_rays = 0, n_scatter = 0;
     int lstack[STACK_N - SS_N];
+    uint32_t cold_[5] = {0u, 0u, 0u, 0u, 0u};          // throughput r, g, b, id word, depth
+    volatile uint32_t *const cold = cold_;
     bool has = false;                  // this lane holds a path (walking, or walked and not shaded yet)
+    bool walking = false;
     bool exhausted = false;            // warp-uniform: the cursor has run past the queue
     int cur = EMPTY_REF, sp = 0, cls = 0;
-    RayT r;
-    make_ray(r, 0.f, 0.f, 0.f, 0.f, 0.f, 1.f);
-    Best best;
-    best.t = INF; best.t_cull = INF; best.id = -1; best.pos = 0; best.cls = 0;
-    float tr = 1.0f, tg = 1.0f, tb = 1.0f;
-    uint32_t idw = 0;                  // shard-local pixel index | sample of the wave << PIX_BITS
-    uint32_t depth = w.depth;
+    WalkRay r = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    float t_cull = INF;                // culling distance: the closest hit known at the last queue flush, widened
+    uint32_t qn = 0;                   // warp-uniform: leaves waiting in the queue
 
-#define PTB_PUSH(v)                                                                                                    \
-    do {                                                                                                               \
-        if (sp < SS_N) s_stack[sp][tid] = (v);                                                                         \
-        else if (sp < STACK_N) lstack[sp - SS_N] = (v);                                                                \
-        if (sp < STACK_N) {                                                                                            \
-            ++sp;                                                                                                      \
-            if (STATS) cn.max_stack = max(cn.max_stack, (uint32_t)sp);                                                 \
-        } else {                                                                                                       \
-            atomicOr(w.error_flag, 1u);                                                                                \
-        }                                                                                                              \
-    } while (0)
-#define PTB_POP()                                                                                                      \
-    do {                                                                                                               \
-        if (sp > 0) {                                                                                                  \
-            --sp;                                                                                                      \
-            cur = sp < SS_N ? s_stack[sp][tid] : lstack[sp - SS_N];                                                    \
-        } else {                                                                                                       \
-            cur = EMPTY_REF;                                                                                           \
-        }                                                                                                              \
-    } while (0)
-#define PTB_START_WALK()                                                                                               \
-    do {                                                                                                               \
-        best.t = INF; best.t_cull = INF; best.id = -1; best.pos = 0; best.cls = 0;                                     \
-        cur = first_root; cls = first_cls; sp = 0;                                                                     \
-    } while (0)
+    // a new ray for the path in this lane: slab form to registers, the rest to shared memory, walk state reset
+    auto start_walk = [&](float ox, float oy, float oz, float dx, float dy, float dz) {
+        RayT f;
+        make_ray(f, ox, oy, oz, dx, dy, dz);
+        r.ix = f.ix; r.iy = f.iy; r.iz = f.iz; r.px = f.px; r.py = f.py; r.pz = f.pz;
+        s_ray[0][tid] = ox; s_ray[1][tid] = oy; s_ray[2][tid] = oz;
+        s_ray[3][tid] = dx; s_ray[4][tid] = dy; s_ray[5][tid] = dz;
+        s_ray[6][tid] = f.a2; s_ray[7][tid] = f.a4;
+        s_best[tid] = NO_HIT;
+        t_cull = INF;
+        cur = first_root; cls = first_cls; sp = 0;
+        walking = true;
+    };
+
+    // tests the primitives of the top `nb` (<= 32) leaves of the queue, one leaf per lane; every lane of the warp calls it
+    auto test_batch = [&](uint32_t nb) {
+        __syncwarp();                                        // queue words and rays other lanes have just written
+        const bool act = lane < nb;
+        const unsigned long long e = act ? queue[qn - nb + lane] : ((unsigned long long)lane << 59);
+        const unsigned own = wbase + (unsigned)(e >> 59);
+        RayT er;
+        er.ox = s_ray[0][own]; er.oy = s_ray[1][own]; er.oz = s_ray[2][own];
+        er.dx = s_ray[3][own]; er.dy = s_ray[4][own]; er.dz = s_ray[5][own];
+        er.a2 = s_ray[6][own]; er.a4 = s_ray[7][own];
+        const uint32_t c = (uint32_t)(e >> 58) & 1u, q = (uint32_t)e;
+        const uint32_t first = q & LEAF_FIRST_MASK, count = act ? (q >> LEAF_COUNT_SHIFT) + 1u : 0u;
+        unsigned long long key = NO_HIT;
+        uint32_t pos = 0;
+        for (uint32_t i = first; i < first + count; ++i) {
+            float t;
+            int id;
+            if (c == 0u) {
+                const float4 cr = __ldg(&k.sph[i]);
+                if (!hit_sphere(cr, er, k.t_min, INF, t)) continue;
+                id = (int)__ldg(&k.sph_meta[i]).x;
+            } else {
+                const float4 v0 = __ldg(&k.tri[3 * (size_t)i]), e1 = __ldg(&k.tri[3 * (size_t)i + 1]),
+                             e2 = __ldg(&k.tri[3 * (size_t)i + 2]);
+                if (!hit_triangle(v0, e1, e2, er, k.t_min, INF, t)) continue;
+                id = __float_as_int(v0.w);
+            }
+            const unsigned long long kk = ((unsigned long long)__float_as_uint(t) << 32) | (uint32_t)id;
+            if (kk < key) {
+                key = kk;
+                pos = i;
+            }
+        }
+        const bool hit = key < *(volatile unsigned long long *)&s_best[own];
+        if (hit) atomicMin(&s_best[own], key);
+        __syncwarp();
+        if (hit && *(volatile unsigned long long *)&s_best[own] == key) s_pos[own] = pos | (c << 31);
+        qn -= nb;
+    };
 
     for (;;) {
         // ---- refill: every lane without a path takes the next one of the queue ----
@@ -704,9 +767,9 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
                         float dy = (uvx * k.cam_u[1] + uvy * k.cam_v[1]) + k.cam_w[1];
                         float dz = (uvx * k.cam_u[2] + uvy * k.cam_v[2]) + k.cam_w[2];
                         normalize3f(dx, dy, dz);
-                        make_ray(r, k.cam_o[0], k.cam_o[1], k.cam_o[2], dx, dy, dz);     // Test.hlsl:8
-                        idw = (yy * k.width + x) | (s_local << PIX_BITS);
-                        tr = tg = tb = 1.0f;
+                        start_walk(k.cam_o[0], k.cam_o[1], k.cam_o[2], dx, dy, dz);      // Test.hlsl:8
+                        cold[0] = cold[1] = cold[2] = __float_as_uint(1.0f);
+                        cold[3] = (yy * k.width + x) | (s_local << PIX_BITS);
                         has = true;
                     }
                 } else {
@@ -714,78 +777,106 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
                     // push the hierarchy out of L2
                     const float4 s0 = __ldcs(&w.in.s0[i]), s1 = __ldcs(&w.in.s1[i]);
                     const float2 s2 = __ldcs(&w.in.s2[i]);
-                    make_ray(r, s0.x, s0.y, s0.z, s1.x, s1.y, s1.z);
-                    idw = __float_as_uint(s0.w);
-                    tr = s1.w; tg = s2.x; tb = s2.y;
+                    start_walk(s0.x, s0.y, s0.z, s1.x, s1.y, s1.z);
+                    cold[0] = __float_as_uint(s1.w); cold[1] = __float_as_uint(s2.x); cold[2] = __float_as_uint(s2.y);
+                    cold[3] = __float_as_uint(s0.w);
                     has = true;
                 }
-                if (has) {
-                    depth = w.depth;
-                    PTB_START_WALK();
-                }
+                if (has) cold[4] = w.depth;
             }
         }
-        const bool walking = has && cur != EMPTY_REF;
-        const unsigned walkers = __ballot_sync(FULL, walking);
+        const unsigned walkers0 = __ballot_sync(FULL, walking);
         if (__ballot_sync(FULL, has) == 0u) {
             if (exhausted) break;
             continue;                                        // depth 0: a fetch of tile padding only
         }
 
-        // ---- walk: until this lane's closest hit is known, or too few lanes of the warp are still walking ----
-        const int live0 = __popc(walkers);
+        // ---- walk, in node steps of the whole warp, until too few lanes are still walking ----
         // pausing pays only if the paused warp can do something else: shade-and-continue (tail) or fetch (queue not dry)
-        const int pause_below = (exhausted && !w.tail) ? 0 : min((int)w.refill, live0);
-        if (lane == 0) s_live[warp] = live0;
-        __syncwarp();
-        if (walking) {
-            for (;;) {
-                const BvhNode *__restrict__ nodes = cls == 0 ? k.sph_nodes : k.tri_nodes;
-                while (cur >= 0) {
+        const int pause_below = (exhausted && !w.tail) ? 0 : min((int)w.refill, __popc(walkers0));
+        for (;;) {
+            int leaf0 = EMPTY_REF, leaf1 = EMPTY_REF;        // leaves this step sends to the queue
+            const unsigned long long tag = ((unsigned long long)(lane << 1 | (unsigned)cls)) << 58;
+            if (walking) {
+                int c0 = cur, c1 = EMPTY_REF;                // cur < 0: a hierarchy that is one leaf
+                if (cur >= 0) {
+                    const BvhNode *__restrict__ nodes = cls == 0 ? k.sph_nodes : k.tri_nodes;
                     const float4 na = __ldg(&nodes[cur].a), nb = __ldg(&nodes[cur].b), nc = __ldg(&nodes[cur].c);
-                    const int4 nd = __ldg(&nodes[cur].d);
+                    const int2 nd = __ldg((const int2 *)&nodes[cur].d);
                     if (STATS) ++cn.nodes;
                     float tn0, tn1;
-                    const bool h0 = slab<true>(na.x, na.y, na.z, na.w, nc.x, nc.y, r, k.t_min, best.t_cull, tn0);
-                    const bool h1 = slab<true>(nb.x, nb.y, nb.z, nb.w, nc.z, nc.w, r, k.t_min, best.t_cull, tn1) && nd.y != EMPTY_REF;
-                    if (h0 && h1) {
-                        const bool swap = tn1 < tn0;
-                        cur = swap ? nd.y : nd.x;
-                        PTB_PUSH(swap ? nd.x : nd.y);
-                    } else if (h0) {
-                        cur = nd.x;
-                    } else if (h1) {
-                        cur = nd.y;
+                    const bool h0 = slab_walk(na.x, na.y, na.z, na.w, nc.x, nc.y, r, k.t_min, t_cull, tn0);
+                    const bool h1 = slab_walk(nb.x, nb.y, nb.z, nb.w, nc.z, nc.w, r, k.t_min, t_cull, tn1);
+                    const bool swap = h0 && h1 && tn1 < tn0;
+                    const int r0 = h0 ? nd.x : EMPTY_REF, r1 = h1 ? nd.y : EMPTY_REF;   // nd.y == EMPTY_REF: no second child
+                    c0 = swap ? r1 : r0;                     // the nearer child first when both are hit
+                    c1 = swap ? r0 : r1;
+                }
+                // children that are leaves go to the queue (EMPTY_REF is negative too and stays what it is), nodes to the walk
+                leaf0 = c0 < 0 ? c0 : EMPTY_REF;
+                leaf1 = c1 < 0 ? c1 : EMPTY_REF;
+                const int n0 = c0 >= 0 ? c0 : EMPTY_REF, n1 = c1 >= 0 ? c1 : EMPTY_REF;
+                if (n0 >= 0 && n1 >= 0) {
+                    if (sp < SS_N) s_stack[sp][tid] = n1;
+                    else if (sp < STACK_N) lstack[sp - SS_N] = n1;
+                    if (sp < STACK_N) {
+                        ++sp;
+                        if (STATS) cn.max_stack = max(cn.max_stack, (uint32_t)sp);
                     } else {
-                        PTB_POP();
+                        atomicOr(w.error_flag, 1u);
                     }
                 }
-                if (cur != EMPTY_REF) {
-                    uint32_t prims = 0;
-                    if (cls == 0) test_leaf<0, false>(k, cur, r, k.t_min, INF, best, prims);
-                    else test_leaf<1, false>(k, cur, r, k.t_min, INF, best, prims);
-                    if (STATS) cn.prims += prims;
-                    PTB_POP();
+                cur = n0 >= 0 ? n0 : n1;
+                if (cur == EMPTY_REF && sp > 0) {
+                    --sp;
+                    cur = sp < SS_N ? s_stack[sp][tid] : lstack[sp - SS_N];
                 }
                 if (cur == EMPTY_REF) {
                     if (cls == 0 && k.tri_root != EMPTY_REF) {       // spheres done: the triangle hierarchy next
                         cls = 1;
                         cur = k.tri_root;
-                        continue;
+                    } else {
+                        walking = false;
                     }
-                    atomicSub(&s_live[warp], 1);
-                    break;
                 }
-                if (*(volatile int *)&s_live[warp] < pause_below) break;
             }
+            // the warp is converged here: queue slots by ballot, no atomics
+            const bool l0 = leaf0 != EMPTY_REF, l1 = leaf1 != EMPTY_REF;
+            const unsigned m0 = __ballot_sync(FULL, l0), m1 = __ballot_sync(FULL, l1);
+            if (l0) queue[qn + __popc(m0 & lt)] = tag | (uint32_t)~leaf0;
+            if (l1) queue[qn + __popc(m0) + __popc(m1 & lt)] = tag | (uint32_t)~leaf1;
+            qn += __popc(m0) + __popc(m1);
+            if (STATS) cn.prims += (l0 ? ((uint32_t)~leaf0 >> LEAF_COUNT_SHIFT) + 1u : 0u) + (l1 ? ((uint32_t)~leaf1 >> LEAF_COUNT_SHIFT) + 1u : 0u);
+            if (qn >= 32u) {                                 // warp-uniform
+                do {
+                    test_batch(32u);
+                } while (qn >= 32u);
+                __syncwarp();
+                const float tb_ = __uint_as_float((uint32_t)(*(volatile unsigned long long *)&s_best[tid] >> 32));
+                t_cull = fmaf(fabsf(tb_), 1.9073486e-6f, tb_);
+            }
+            const unsigned wk = __ballot_sync(FULL, walking);
+            if (wk == 0u || __popc(wk) < pause_below) break;
         }
+        if (qn != 0u) test_batch(qn);                        // flush: the paths about to be shaded need every result
         __syncwarp();
 
         // ---- shade and scatter the paths whose walk has ended ----
         bool cont = false;                                   // goes to the next bounce's queue
-        float Px = 0, Py = 0, Pz = 0;
-        if (has && cur == EMPTY_REF) {
+        float Px = 0, Py = 0, Pz = 0, dx = 0, dy = 0, dz = 0, tr = 0, tg = 0, tb = 0;
+        uint32_t idw = 0;
+        if (has && !walking) {
+            Best best;
+            const unsigned long long bk = s_best[tid];
+            best.t = __uint_as_float((uint32_t)(bk >> 32));
+            best.t_cull = best.t;
+            best.id = (int)(uint32_t)bk;
+            best.pos = (int)(s_pos[tid] & 0x7FFFFFFFu);
+            best.cls = (int)(s_pos[tid] >> 31);
             const bool hit = best.id >= 0;
+            tr = __uint_as_float(cold[0]); tg = __uint_as_float(cold[1]); tb = __uint_as_float(cold[2]);
+            idw = cold[3];
+            const uint32_t depth = cold[4];
             const uint32_t s_local = w.batch > 1u ? idw >> PIX_BITS : 0u;
             const uint32_t loc = w.batch > 1u ? idw & PIX_MASK : idw;
             const uint32_t yy = loc / k.width, x = loc - yy * k.width;
@@ -797,9 +888,9 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
             if (DEPTH0 && w.hit_ids) w.hit_ids[pix] = hit ? best.id : -1;
             float nx = 0, ny = 0, nz = 0;
             uint32_t mat = 0;
-            float dx = r.dx, dy = r.dy, dz = r.dz;
+            dx = s_ray[3][tid]; dy = s_ray[4][tid]; dz = s_ray[5][tid];
             if (hit) {
-                Px = r.ox + best.t * dx; Py = r.oy + best.t * dy; Pz = r.oz + best.t * dz;      // Test.hlsl:28
+                Px = s_ray[0][tid] + best.t * dx; Py = s_ray[1][tid] + best.t * dy; Pz = s_ray[2][tid] + best.t * dz;   // Test.hlsl:28
                 hit_frame(k, best, Px, Py, Pz, nx, ny, nz, mat);
             }
             if (k.shade_mode == PTB_SHADE_NORMALS) {
@@ -845,11 +936,10 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
             if (!alive) {
                 has = false;
             } else if (!DEPTH0 && w.tail) {                  // launch-uniform: the path stays in this lane
-                make_ray(r, Px, Py, Pz, dx, dy, dz);
-                ++depth;
-                PTB_START_WALK();
+                start_walk(Px, Py, Pz, dx, dy, dz);
+                cold[0] = __float_as_uint(tr); cold[1] = __float_as_uint(tg); cold[2] = __float_as_uint(tb);
+                cold[4] = depth + 1u;
             } else {
-                r.dx = dx; r.dy = dy; r.dz = dz;
                 cont = true;
                 has = false;
             }
@@ -863,14 +953,11 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel(cons
             if (cont) {
                 const uint32_t o = obase + (uint32_t)__popc(outm & lt);
                 __stcs(&w.out.s0[o], make_float4(Px, Py, Pz, __uint_as_float(idw)));
-                __stcs(&w.out.s1[o], make_float4(r.dx, r.dy, r.dz, tr));
+                __stcs(&w.out.s1[o], make_float4(dx, dy, dz, tr));
                 __stcs(&w.out.s2[o], make_float2(tg, tb));
             }
         }
     }
-#undef PTB_PUSH
-#undef PTB_POP
-#undef PTB_START_WALK
     if (STATS) {
         unsigned long long v[4] = {cn.nodes, cn.prims, n_rays, n_scatter};
 #pragma unroll
@@ -1063,7 +1150,8 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
     // A/B switches for profiling runs: PTB200_BOUNCE=chunk selects the 32-paths-per-warp schedule, PTB200_REFILL the number
     // of walking lanes below which a warp pauses to shade and refetch (0: never).
     const char *e_bounce = std::getenv("PTB200_BOUNCE"), *e_refill = std::getenv("PTB200_REFILL");
-    const bool chunk = e_bounce && e_bounce[0] == 'c';
+    const bool chunk = !(e_bounce && e_bounce[0] == 'q');      // default: the chunk schedule (measured faster so far)
+    const bool chunk_d0 = chunk || !std::getenv("PTB200_D0_QUEUE");
     const int refill_i = e_refill ? std::atoi(e_refill) : PTB_REFILL_DEFAULT;
     const uint32_t refill = (uint32_t)(refill_i < 0 ? 0 : refill_i > 32 ? 32 : refill_i);
     const uint32_t tail_depth = tail_env >= 0 ? (uint32_t)tail_env : ((uint64_t)n0_pixels * batch >= (8u << 20) ? 6u : 4u);
@@ -1094,8 +1182,9 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
         w.error_flag = st->error_flag;
         w.refill = refill;
         if (d == 0) {
-            if (st->count_stats) launch_bounce<true, true>(k, w, chunk, s);
-            else launch_bounce<true, false>(k, w, chunk, s);
+            // camera rays are coherent: the chunk schedule already runs them at 28 of 32 lanes, without the queue's overheads
+            if (st->count_stats) launch_bounce<true, true>(k, w, chunk_d0, s);
+            else launch_bounce<true, false>(k, w, chunk_d0, s);
         } else {
             if (st->count_stats) launch_bounce<false, true>(k, w, chunk, s);
             else launch_bounce<false, false>(k, w, chunk, s);
