@@ -619,23 +619,52 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel_chun
 //     ended shade and scatter their paths together, take new paths from the cursor (one atomicAdd per warp for all its free
 //     lanes) and the warp walks on with all lanes busy (Aila & Laine 2009, dynamic fetch).  In tail mode a path that
 //     scatters stays in its lane and starts its next walk at once: a persistent path tracer until the cursor runs dry.
-// The traversal stack's first SS_N levels live in shared memory, one 4-byte column per thread ([level][thread]: whatever
-// the lanes' depths, one access is one conflict-free wavefront); deeper levels spill to local memory.
 // Which lane traces a path, in which order primitives are tested and the queues fill changes nothing in any result: every
 // path's arithmetic is its own, its radiance goes to its own slot (or its pixel's only live path), the closest hit is a
 // minimum.
 #ifndef PTB_REFILL_DEFAULT
 #define PTB_REFILL_DEFAULT 8
 #endif
-#ifndef PTB_SHORT_STACK
-#define PTB_SHORT_STACK 12
-#endif
 #ifndef PTB_QUEUE_MIN_BLOCKS
 #define PTB_QUEUE_MIN_BLOCKS 4
 #endif
-constexpr int SS_N = PTB_SHORT_STACK;
-constexpr uint32_t Q_CAP = 32u + 32u * 2u;                     // < 32 leaves waiting + two per lane and node step
 constexpr unsigned long long NO_HIT = 0x7F800000FFFFFFFFull;   // t = +inf, id = -1
+
+// Shared memory of bounce_kernel, addressed through 32-bit shared-window addresses and explicit ld/st.shared: left to itself
+// the compiler re-derives every address from %tid and the CTA's shared window inside the walk loop (S2R, 6 instructions
+// per access) rather than keep a base in a register.
+struct QueueShared {
+    float ray[8][256];                         // o.xyz, d.xyz, 2 d.d, 4 d.d of the path in each lane
+    unsigned long long best[256];              // its closest hit so far: t bits << 32 | id
+    uint32_t pos[256];                         // ... leaf-order position | class << 31
+    unsigned long long queue[8][32u + 64u];    // per warp: lane << 59 | class << 58 | ~(leaf reference)
+};
+__device__ __forceinline__ uint32_t lds32(uint32_t a)
+{
+    uint32_t v;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ float ldsf(uint32_t a) { return __uint_as_float(lds32(a)); }
+__device__ __forceinline__ void sts32(uint32_t a, uint32_t v) { asm volatile("st.shared.b32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ unsigned long long lds64(uint32_t a)
+{
+    unsigned long long v;
+    asm volatile("ld.shared.b64 %0, [%1];" : "=l"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts64(uint32_t a, unsigned long long v) { asm volatile("st.shared.b64 [%0], %1;" ::"r"(a), "l"(v) : "memory"); }
+__device__ __forceinline__ unsigned long long pack64(uint32_t hi, uint32_t lo)
+{
+    unsigned long long v;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(v) : "r"(lo), "r"(hi));
+    return v;
+}
+__device__ __forceinline__ void atom_min64(uint32_t a, unsigned long long v)
+{
+    unsigned long long old;
+    asm volatile("atom.shared.min.u64 %0, [%1], %2;" : "=l"(old) : "r"(a), "l"(v) : "memory");
+}
 
 // What a lane keeps of its ray while it walks: the slab form only.  Origin, direction and the two sphere constants live in
 // shared memory (s_ray), where the lane that tests one of this path's leaves reads them; throughput, pixel and depth are
@@ -659,25 +688,28 @@ __device__ __forceinline__ bool slab_walk(float lox, float hix, float loy, float
 template <bool DEPTH0, bool STATS>
 __global__ void __launch_bounds__(256, PTB_QUEUE_MIN_BLOCKS) bounce_kernel(const SceneK k, const WaveArgs w)
 {
-    __shared__ int s_stack[SS_N][256];
-    __shared__ float s_ray[8][256];                    // o.xyz, d.xyz, 2 d.d, 4 d.d of the path in each lane
-    __shared__ unsigned long long s_best[256];         // its closest hit so far: t bits << 32 | id
-    __shared__ uint32_t s_pos[256];                    // ... leaf-order position | class << 31
-    __shared__ unsigned long long s_queue[8][Q_CAP];   // per warp: lane << 59 | class << 58 | ~(leaf reference)
-    const unsigned tid = threadIdx.x, lane = tid & 31u, wbase = tid & ~31u;
+    __shared__ QueueShared S;
+    uint32_t tid = threadIdx.x;
+    uint32_t sa = (uint32_t)__cvta_generic_to_shared(&S);
+    asm volatile("" : "+r"(tid), "+r"(sa));            // keep both in registers (see QueueShared)
+    const unsigned lane = tid & 31u;
     const unsigned lt = (1u << lane) - 1u;
-    unsigned long long *const queue = s_queue[tid >> 5];
+    const uint32_t sa_ray = sa + (uint32_t)offsetof(QueueShared, ray), sa_best = sa + (uint32_t)offsetof(QueueShared, best);
+    const uint32_t sa_pos = sa + (uint32_t)offsetof(QueueShared, pos);
+    const uint32_t sa_queue = sa + (uint32_t)offsetof(QueueShared, queue) + (tid >> 5) * (uint32_t)sizeof(S.queue[0]);
+    const uint32_t wbase = tid & ~31u;
     const uint32_t n_in = DEPTH0 ? w.n0 : *w.n_in;
     const int first_cls = k.sph_root != EMPTY_REF ? 0 : 1;
     const int first_root = k.sph_root != EMPTY_REF ? k.sph_root : k.tri_root;      // EMPTY_REF: a scene without primitives
+    const int tri_after = first_cls == 0 ? k.tri_root : EMPTY_REF;                 // where a walk goes when the spheres are done
     const float INF = __int_as_float(0x7F800000);
     Counters cn;
     uint32_t n_rays = 0, n_scatter = 0;
-    int lstack[STACK_N - SS_N];
+    int stack[STACK_N];                                // local memory, as in the chunk schedule (a shared-memory short stack
+                                                       // was measured: no faster, and its 12 KB per block come out of L1)
     uint32_t cold_[5] = {0u, 0u, 0u, 0u, 0u};          // throughput r, g, b, id word, depth
     volatile uint32_t *const cold = cold_;
     bool has = false;                  // this lane holds a path (walking, or walked and not shaded yet)
-    bool walking = false;
     bool exhausted = false;            // warp-uniform: the cursor has run past the queue
     int cur = EMPTY_REF, sp = 0, cls = 0;
     WalkRay r = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -689,26 +721,28 @@ __global__ void __launch_bounds__(256, PTB_QUEUE_MIN_BLOCKS) bounce_kernel(const
         RayT f;
         make_ray(f, ox, oy, oz, dx, dy, dz);
         r.ix = f.ix; r.iy = f.iy; r.iz = f.iz; r.px = f.px; r.py = f.py; r.pz = f.pz;
-        s_ray[0][tid] = ox; s_ray[1][tid] = oy; s_ray[2][tid] = oz;
-        s_ray[3][tid] = dx; s_ray[4][tid] = dy; s_ray[5][tid] = dz;
-        s_ray[6][tid] = f.a2; s_ray[7][tid] = f.a4;
-        s_best[tid] = NO_HIT;
+        const uint32_t ra = sa_ray + tid * 4u;
+        sts32(ra, __float_as_uint(ox)); sts32(ra + 1024u, __float_as_uint(oy)); sts32(ra + 2048u, __float_as_uint(oz));
+        sts32(ra + 3072u, __float_as_uint(dx)); sts32(ra + 4096u, __float_as_uint(dy)); sts32(ra + 5120u, __float_as_uint(dz));
+        sts32(ra + 6144u, __float_as_uint(f.a2)); sts32(ra + 7168u, __float_as_uint(f.a4));
+        sts64(sa_best + tid * 8u, NO_HIT);
         t_cull = INF;
         cur = first_root; cls = first_cls; sp = 0;
-        walking = true;
     };
 
     // tests the primitives of the top `nb` (<= 32) leaves of the queue, one leaf per lane; every lane of the warp calls it
     auto test_batch = [&](uint32_t nb) {
         __syncwarp();                                        // queue words and rays other lanes have just written
         const bool act = lane < nb;
-        const unsigned long long e = act ? queue[qn - nb + lane] : ((unsigned long long)lane << 59);
-        const unsigned own = wbase + (unsigned)(e >> 59);
+        const unsigned long long e = act ? lds64(sa_queue + (qn - nb + lane) * 8u) : pack64(lane << 27, 0u);
+        const uint32_t ehi = (uint32_t)(e >> 32);
+        const unsigned own = wbase + (ehi >> 27);
+        const uint32_t ra = sa_ray + own * 4u;
         RayT er;
-        er.ox = s_ray[0][own]; er.oy = s_ray[1][own]; er.oz = s_ray[2][own];
-        er.dx = s_ray[3][own]; er.dy = s_ray[4][own]; er.dz = s_ray[5][own];
-        er.a2 = s_ray[6][own]; er.a4 = s_ray[7][own];
-        const uint32_t c = (uint32_t)(e >> 58) & 1u, q = (uint32_t)e;
+        er.ox = ldsf(ra); er.oy = ldsf(ra + 1024u); er.oz = ldsf(ra + 2048u);
+        er.dx = ldsf(ra + 3072u); er.dy = ldsf(ra + 4096u); er.dz = ldsf(ra + 5120u);
+        er.a2 = ldsf(ra + 6144u); er.a4 = ldsf(ra + 7168u);
+        const uint32_t c = (ehi >> 26) & 1u, q = (uint32_t)e;
         const uint32_t first = q & LEAF_FIRST_MASK, count = act ? (q >> LEAF_COUNT_SHIFT) + 1u : 0u;
         unsigned long long key = NO_HIT;
         uint32_t pos = 0;
@@ -731,10 +765,10 @@ __global__ void __launch_bounds__(256, PTB_QUEUE_MIN_BLOCKS) bounce_kernel(const
                 pos = i;
             }
         }
-        const bool hit = key < *(volatile unsigned long long *)&s_best[own];
-        if (hit) atomicMin(&s_best[own], key);
+        const bool hit = key < lds64(sa_best + own * 8u);
+        if (hit) atom_min64(sa_best + own * 8u, key);
         __syncwarp();
-        if (hit && *(volatile unsigned long long *)&s_best[own] == key) s_pos[own] = pos | (c << 31);
+        if (hit && lds64(sa_best + own * 8u) == key) sts32(sa_pos + own * 4u, pos | (c << 31));
         qn -= nb;
     };
 
@@ -785,7 +819,7 @@ __global__ void __launch_bounds__(256, PTB_QUEUE_MIN_BLOCKS) bounce_kernel(const
                 if (has) cold[4] = w.depth;
             }
         }
-        const unsigned walkers0 = __ballot_sync(FULL, walking);
+        const unsigned walkers0 = __ballot_sync(FULL, cur != EMPTY_REF);
         if (__ballot_sync(FULL, has) == 0u) {
             if (exhausted) break;
             continue;                                        // depth 0: a fetch of tile padding only
@@ -795,67 +829,63 @@ __global__ void __launch_bounds__(256, PTB_QUEUE_MIN_BLOCKS) bounce_kernel(const
         // pausing pays only if the paused warp can do something else: shade-and-continue (tail) or fetch (queue not dry)
         const int pause_below = (exhausted && !w.tail) ? 0 : min((int)w.refill, __popc(walkers0));
         for (;;) {
-            int leaf0 = EMPTY_REF, leaf1 = EMPTY_REF;        // leaves this step sends to the queue
-            const unsigned long long tag = ((unsigned long long)(lane << 1 | (unsigned)cls)) << 58;
-            if (walking) {
-                int c0 = cur, c1 = EMPTY_REF;                // cur < 0: a hierarchy that is one leaf
-                if (cur >= 0) {
-                    const BvhNode *__restrict__ nodes = cls == 0 ? k.sph_nodes : k.tri_nodes;
-                    const float4 na = __ldg(&nodes[cur].a), nb = __ldg(&nodes[cur].b), nc = __ldg(&nodes[cur].c);
-                    const int2 nd = __ldg((const int2 *)&nodes[cur].d);
-                    if (STATS) ++cn.nodes;
-                    float tn0, tn1;
-                    const bool h0 = slab_walk(na.x, na.y, na.z, na.w, nc.x, nc.y, r, k.t_min, t_cull, tn0);
-                    const bool h1 = slab_walk(nb.x, nb.y, nb.z, nb.w, nc.z, nc.w, r, k.t_min, t_cull, tn1);
-                    const bool swap = h0 && h1 && tn1 < tn0;
-                    const int r0 = h0 ? nd.x : EMPTY_REF, r1 = h1 ? nd.y : EMPTY_REF;   // nd.y == EMPTY_REF: no second child
-                    c0 = swap ? r1 : r0;                     // the nearer child first when both are hit
-                    c1 = swap ? r0 : r1;
-                }
-                // children that are leaves go to the queue (EMPTY_REF is negative too and stays what it is), nodes to the walk
-                leaf0 = c0 < 0 ? c0 : EMPTY_REF;
-                leaf1 = c1 < 0 ? c1 : EMPTY_REF;
-                const int n0 = c0 >= 0 ? c0 : EMPTY_REF, n1 = c1 >= 0 ? c1 : EMPTY_REF;
-                if (n0 >= 0 && n1 >= 0) {
-                    if (sp < SS_N) s_stack[sp][tid] = n1;
-                    else if (sp < STACK_N) lstack[sp - SS_N] = n1;
+            // a lane walks while cur != EMPTY_REF.  c0 / c1: what this step found — cur itself when it is a leaf (a hierarchy
+            // that is one leaf), else the children whose boxes the ray hits, the nearer one first
+            int c0 = cur, c1 = EMPTY_REF;
+            const uint32_t tag = (lane << 27) | ((uint32_t)cls << 26);
+            if (cur >= 0) {
+                const BvhNode *__restrict__ nodes = cls == 0 ? k.sph_nodes : k.tri_nodes;
+                const float4 na = __ldg(&nodes[cur].a), nb = __ldg(&nodes[cur].b), nc = __ldg(&nodes[cur].c);
+                const int2 nd = __ldg((const int2 *)&nodes[cur].d);
+                if (STATS) ++cn.nodes;
+                float tn0, tn1;
+                const bool h0 = slab_walk(na.x, na.y, na.z, na.w, nc.x, nc.y, r, k.t_min, t_cull, tn0);
+                const bool h1 = slab_walk(nb.x, nb.y, nb.z, nb.w, nc.z, nc.w, r, k.t_min, t_cull, tn1);
+                const bool swap = h0 && h1 && tn1 < tn0;
+                const int r0 = h0 ? nd.x : EMPTY_REF, r1 = h1 ? nd.y : EMPTY_REF;   // nd.y == EMPTY_REF: no second child
+                c0 = swap ? r1 : r0;
+                c1 = swap ? r0 : r1;
+            }
+            // children that are leaves go to the queue, nodes to the walk.  As unsigned numbers node indices lie below
+            // EMPTY_REF (0x80000000) and leaf references above it.
+            const uint32_t u0 = (uint32_t)c0, u1 = (uint32_t)c1;
+            const bool l0 = u0 > 0x80000000u, l1 = u1 > 0x80000000u;
+            const int n0 = (int)min(u0, 0x80000000u), n1 = (int)min(u1, 0x80000000u);     // the node, or EMPTY_REF
+            if (cur != EMPTY_REF) {
+                if ((n0 | n1) >= 0) {                        // two nodes: the farther one waits on the stack
                     if (sp < STACK_N) {
-                        ++sp;
+                        stack[sp++] = n1;
                         if (STATS) cn.max_stack = max(cn.max_stack, (uint32_t)sp);
                     } else {
                         atomicOr(w.error_flag, 1u);
                     }
                 }
                 cur = n0 >= 0 ? n0 : n1;
-                if (cur == EMPTY_REF && sp > 0) {
-                    --sp;
-                    cur = sp < SS_N ? s_stack[sp][tid] : lstack[sp - SS_N];
-                }
                 if (cur == EMPTY_REF) {
-                    if (cls == 0 && k.tri_root != EMPTY_REF) {       // spheres done: the triangle hierarchy next
+                    if (sp > 0) {
+                        cur = stack[--sp];
+                    } else if (cls == 0) {                   // spheres done: the triangle hierarchy next (or EMPTY_REF: finished)
                         cls = 1;
-                        cur = k.tri_root;
-                    } else {
-                        walking = false;
+                        cur = tri_after;
                     }
                 }
             }
             // the warp is converged here: queue slots by ballot, no atomics
-            const bool l0 = leaf0 != EMPTY_REF, l1 = leaf1 != EMPTY_REF;
             const unsigned m0 = __ballot_sync(FULL, l0), m1 = __ballot_sync(FULL, l1);
-            if (l0) queue[qn + __popc(m0 & lt)] = tag | (uint32_t)~leaf0;
-            if (l1) queue[qn + __popc(m0) + __popc(m1 & lt)] = tag | (uint32_t)~leaf1;
+            const uint32_t at0 = qn + __popc(m0 & lt), at1 = qn + __popc(m0) + __popc(m1 & lt);
+            if (l0) sts64(sa_queue + at0 * 8u, pack64(tag, ~u0));
+            if (l1) sts64(sa_queue + at1 * 8u, pack64(tag, ~u1));
             qn += __popc(m0) + __popc(m1);
-            if (STATS) cn.prims += (l0 ? ((uint32_t)~leaf0 >> LEAF_COUNT_SHIFT) + 1u : 0u) + (l1 ? ((uint32_t)~leaf1 >> LEAF_COUNT_SHIFT) + 1u : 0u);
+            if (STATS) cn.prims += (l0 ? (~u0 >> LEAF_COUNT_SHIFT) + 1u : 0u) + (l1 ? (~u1 >> LEAF_COUNT_SHIFT) + 1u : 0u);
             if (qn >= 32u) {                                 // warp-uniform
                 do {
                     test_batch(32u);
                 } while (qn >= 32u);
                 __syncwarp();
-                const float tb_ = __uint_as_float((uint32_t)(*(volatile unsigned long long *)&s_best[tid] >> 32));
+                const float tb_ = ldsf(sa_best + tid * 8u + 4u);
                 t_cull = fmaf(fabsf(tb_), 1.9073486e-6f, tb_);
             }
-            const unsigned wk = __ballot_sync(FULL, walking);
+            const unsigned wk = __ballot_sync(FULL, cur != EMPTY_REF);
             if (wk == 0u || __popc(wk) < pause_below) break;
         }
         if (qn != 0u) test_batch(qn);                        // flush: the paths about to be shaded need every result
@@ -865,14 +895,15 @@ __global__ void __launch_bounds__(256, PTB_QUEUE_MIN_BLOCKS) bounce_kernel(const
         bool cont = false;                                   // goes to the next bounce's queue
         float Px = 0, Py = 0, Pz = 0, dx = 0, dy = 0, dz = 0, tr = 0, tg = 0, tb = 0;
         uint32_t idw = 0;
-        if (has && !walking) {
+        if (has && cur == EMPTY_REF) {
             Best best;
-            const unsigned long long bk = s_best[tid];
+            const unsigned long long bk = lds64(sa_best + tid * 8u);
+            const uint32_t bp = lds32(sa_pos + tid * 4u);
             best.t = __uint_as_float((uint32_t)(bk >> 32));
             best.t_cull = best.t;
             best.id = (int)(uint32_t)bk;
-            best.pos = (int)(s_pos[tid] & 0x7FFFFFFFu);
-            best.cls = (int)(s_pos[tid] >> 31);
+            best.pos = (int)(bp & 0x7FFFFFFFu);
+            best.cls = (int)(bp >> 31);
             const bool hit = best.id >= 0;
             tr = __uint_as_float(cold[0]); tg = __uint_as_float(cold[1]); tb = __uint_as_float(cold[2]);
             idw = cold[3];
@@ -888,9 +919,10 @@ __global__ void __launch_bounds__(256, PTB_QUEUE_MIN_BLOCKS) bounce_kernel(const
             if (DEPTH0 && w.hit_ids) w.hit_ids[pix] = hit ? best.id : -1;
             float nx = 0, ny = 0, nz = 0;
             uint32_t mat = 0;
-            dx = s_ray[3][tid]; dy = s_ray[4][tid]; dz = s_ray[5][tid];
+            const uint32_t ra = sa_ray + tid * 4u;
+            dx = ldsf(ra + 3072u); dy = ldsf(ra + 4096u); dz = ldsf(ra + 5120u);
             if (hit) {
-                Px = s_ray[0][tid] + best.t * dx; Py = s_ray[1][tid] + best.t * dy; Pz = s_ray[2][tid] + best.t * dz;   // Test.hlsl:28
+                Px = ldsf(ra) + best.t * dx; Py = ldsf(ra + 1024u) + best.t * dy; Pz = ldsf(ra + 2048u) + best.t * dz;   // Test.hlsl:28
                 hit_frame(k, best, Px, Py, Pz, nx, ny, nz, mat);
             }
             if (k.shade_mode == PTB_SHADE_NORMALS) {
@@ -1140,21 +1172,24 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
                                                                   // margin: every warp runs the cursor past the end once)
     const uint32_t n0 = (uint32_t)n0_64;
     const uint32_t depths = k.shade_mode == PTB_SHADE_NORMALS ? 1u : k.max_depth + 1u;
-    // bounces >= tail_depth run inside ONE launch (0 disables): queues that deep are too small to fill the GPU, unless the
-    // wave is a big batched one (>= 8 Mi camera rays), whose queues stay large two bounces longer (c3: tail at 4 costs 6 %
-    // there).  PTB200_TAIL_DEPTH overrides for A/B runs.
-    static const int tail_env = [] {
-        const char *e = std::getenv("PTB200_TAIL_DEPTH");
-        return e ? std::atoi(e) : -1;
-    }();
+    // bounces >= tail_depth run inside ONE launch (0 disables): queues that deep are too small to fill the GPU.  With the
+    // queue schedule in the tail launch (default) the tail starts at bounce 3 (c3: 2, 3, 4, 6 -> 4,147 / 4,149 / 4,128 / 4,061
+    // Msamples/s); with the chunk schedule there, at 4, or 6 for big batched waves (>= 8 Mi camera rays), whose queues stay
+    // large two bounces longer.  PTB200_TAIL_DEPTH overrides for A/B runs.
+    const char *e_tail = std::getenv("PTB200_TAIL_DEPTH");
+    const int tail_env = e_tail ? std::atoi(e_tail) : -1;
     // A/B switches for profiling runs: PTB200_BOUNCE=chunk selects the 32-paths-per-warp schedule, PTB200_REFILL the number
     // of walking lanes below which a warp pauses to shade and refetch (0: never).
     const char *e_bounce = std::getenv("PTB200_BOUNCE"), *e_refill = std::getenv("PTB200_REFILL");
-    const bool chunk = !(e_bounce && e_bounce[0] == 'q');      // default: the chunk schedule (measured faster so far)
-    const bool chunk_d0 = chunk || !std::getenv("PTB200_D0_QUEUE");
+    // PTB200_BOUNCE: "chunk" = every launch with the chunk schedule, "queue" = bounces >= 1 with the queue schedule,
+    // "tail" = only the tail launch with the queue schedule
+    // (the default: it wins there — a path that scatters stays in its lane — and loses 1-5 % on the big early bounces,
+    // where its node step costs 2.4x the instructions of the chunk schedule's for 1.5-2x the active lanes; profiles/r02_notes.md)
+    const bool q_all = e_bounce && e_bounce[0] == 'q', q_tail = !e_bounce || q_all || e_bounce[0] == 't';
+    const bool chunk_d0 = !q_all || !std::getenv("PTB200_D0_QUEUE");
     const int refill_i = e_refill ? std::atoi(e_refill) : PTB_REFILL_DEFAULT;
     const uint32_t refill = (uint32_t)(refill_i < 0 ? 0 : refill_i > 32 ? 32 : refill_i);
-    const uint32_t tail_depth = tail_env >= 0 ? (uint32_t)tail_env : ((uint64_t)n0_pixels * batch >= (8u << 20) ? 6u : 4u);
+    const uint32_t tail_depth = tail_env >= 0 ? (uint32_t)tail_env : (q_tail ? 3u : ((uint64_t)n0_pixels * batch >= (8u << 20) ? 6u : 4u));
     // counters: [0, depths] queue sizes, [depths+1, 2*depths+1] work cursors
     cudaError_t e = cudaMemsetAsync(st->counts, 0, sizeof(uint32_t) * st->counts_len, s);
     if (e != cudaSuccess) return e;
@@ -1186,6 +1221,7 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
             if (st->count_stats) launch_bounce<true, true>(k, w, chunk_d0, s);
             else launch_bounce<true, false>(k, w, chunk_d0, s);
         } else {
+            const bool chunk = w.tail ? !q_tail : !q_all;
             if (st->count_stats) launch_bounce<false, true>(k, w, chunk, s);
             else launch_bounce<false, false>(k, w, chunk, s);
         }

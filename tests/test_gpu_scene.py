@@ -388,6 +388,38 @@ def test_samples_per_wave_is_scheduling_only(S, make, w, h, depth):
         assert_images_equal(got[per_wave, "shard"], got[1, "shard"], f"{per_wave} samples per wave, row shard")
 
 
+@pytest.mark.parametrize("make,w,h,depth", [
+    (lambda w, h: scenes.mixed_small(width=w, height=h), 160, 90, 6),                  # spheres AND triangles: both hierarchies
+    (lambda w, h: scenes.random_spheres(200, width=w, height=h), 211, 97, 8),
+    (lambda w, h: scenes.triangle_terrain(24, 2, width=w, height=h), 192, 108, 5),
+])
+def test_bounce_schedule_is_scheduling_only(S, make, w, h, depth, monkeypatch):
+    """n5/n7: the chunk schedule (32 paths per warp, every lane walks on its own), the queue schedule (lockstep node steps,
+    per-warp leaf queue, per-lane refill) on every bounce or only in the tail launch, any refill threshold, any tail depth:
+    the same accumulation buffer bit for bit, equal to the oracle; also with one-sample waves and the counting build."""
+    sc = make(w, h)
+    ref = S.SceneOracle(sc, w, h, max_depth=depth).accumulate(0, 5, seed=9)
+    cases = [dict(PTB200_BOUNCE="chunk"), dict(PTB200_BOUNCE="queue", PTB200_REFILL="0"),
+             dict(PTB200_BOUNCE="queue", PTB200_REFILL="8"), dict(PTB200_BOUNCE="queue", PTB200_REFILL="31", PTB200_D0_QUEUE="1"),
+             dict(PTB200_BOUNCE="queue", PTB200_REFILL="20", PTB200_TAIL_DEPTH="1"), dict(PTB200_BOUNCE="tail", PTB200_TAIL_DEPTH="2"),
+             dict(PTB200_BOUNCE="tail", PTB200_TAIL_DEPTH="0"), dict()]
+    for env in cases:
+        for k in ("PTB200_BOUNCE", "PTB200_REFILL", "PTB200_TAIL_DEPTH", "PTB200_D0_QUEUE"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        for per_wave, stats in ((0, False), (1, True)):
+            with NativeTracer(w, h, seed=9, max_depth=depth) as t:
+                t.upload_scene(sc, count_stats=stats)
+                t.set_wave_samples(per_wave)
+                t.render_samples(0, 3)
+                t.render_samples(3, 2)
+                assert_images_equal(t.read_accum(), ref, f"{env} per_wave={per_wave}")
+                if stats:
+                    st = t.scene_stats()
+                    assert st["paths"] == 5 * w * h and st["rays"] >= st["paths"] and st["prims_tested"] > 0
+
+
 def test_furnace_and_energy_bounds():
     """White sky, albedo-1 Lambert sphere: every path returns exactly the sky radiance times 1 (white furnace)."""
     w, h = 96, 54
