@@ -1,6 +1,7 @@
 """Small pass over every kernel family, meant to be run under compute-sanitizer on the GPU box:
    compute-sanitizer --tool memcheck|racecheck|initcheck|synccheck python experiments/sanitize.py
-(compute-sanitizer is closed on the shared GPU pool, where this only serves as a functional pass.)"""
+Kernel launches are serialised under the sanitizer, so the cross-GPU rendezvous (a kernel that spins until its peers' kernels
+have run) is left out; the peer MERGE kernel is driven directly."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
@@ -16,7 +17,12 @@ with NativeTracer(w, h, seed=3, keep_f32=True, keep_hit_ids=True) as t:
     t.write_accum(acc, 7); t.resolve(); t.wait()
     assert np.array_equal(t.read_rgba8(), img)
     t.present(); t.wait(); t.read_present()
+    t.accum_reset(); t.render_resolve(0, 6, 6); t.render_resolve(6, 3, 9); t.wait(); t.read_rgba8()
+    t.compute_frames(3); t.wait(); t.read_rgba8()
     print("csmain ok", flush=True)
+with NativeTracer(w, h, seed=3, spirv_arith=True) as t:
+    t.compute_frame(); t.render_samples(0, 3); t.resolve(); t.wait(); t.read_rgba8()
+    print("spirv arithmetic ok", flush=True)
 
 for name, sc, depth in (("mixed", scenes.mixed_small(width=w, height=h), 6),
                         ("spheres", scenes.random_spheres(60, width=w, height=h), 8),
@@ -27,8 +33,21 @@ for name, sc, depth in (("mixed", scenes.mixed_small(width=w, height=h), 6),
         t.compute_frame(); t.wait()
         for per_wave in (0, 1, 3):
             t.set_wave_samples(per_wave)
-            t.render_samples(0, 5)
+            for mode in ("chunk", "queue", "tail"):      # every bounce schedule (kernels_scene.cu launch_scene_wave)
+                os.environ["PTB200_BOUNCE"] = mode
+                t.render_samples(0, 5)
+        os.environ["PTB200_D0_QUEUE"] = "1"; os.environ["PTB200_BOUNCE"] = "queue"; os.environ["PTB200_REFILL"] = "24"
+        t.render_samples(5, 3)
+        for k in ("PTB200_D0_QUEUE", "PTB200_BOUNCE", "PTB200_REFILL"):
+            del os.environ[k]
         t.set_row_shard(2, 3, 4); t.render_samples(5, 4); t.set_row_shard(0, 1)
+        if depth:                                        # next-event estimation: shadow rays in both schedules
+            t.set_sun([0.35, 1.0, 0.25], [2.0, 1.75, 1.5])
+            for mode in ("chunk", "queue"):
+                os.environ["PTB200_BOUNCE"] = mode
+                t.render_samples(9, 3)
+            del os.environ["PTB200_BOUNCE"]
+            t.set_sun([0, 1, 0], [0, 0, 0])
         t.resolve(); t.wait()
         rng = np.random.Generator(np.random.PCG64(2))
         o = rng.uniform(-4, 4, (3000, 3)).astype(np.float32); d = rng.normal(size=(3000, 3)).astype(np.float32)

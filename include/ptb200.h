@@ -249,6 +249,13 @@ int ptb_scene_stats_reset(ptb_context *ctx);
  * accumulation buffer receives the samples' radiance in sample order whatever the wave size — results do not change
  * by a bit (tests/test_gpu_scene.py). */
 int ptb_scene_set_wave_samples(ptb_context *ctx, uint32_t samples_per_wave);
+/* Next-event estimation towards ONE directional light ("sun"; no reference counterpart — Test.hlsl has no light): at every
+ * hit that scatters on a PTB_MAT_LAMBERT material the path tracer casts a shadow ray (ANY-HIT traversal of both
+ * hierarchies, (t_min, +inf)) along `dir_to_light` (used as given; pass a unit vector) and, when nothing occludes it
+ * and c = n.dir > 0 for the normal turned against the incoming ray, adds (throughput*albedo)*(radiance*c) to the
+ * path's radiance.  The sky does not contain the sun, so nothing is counted twice.  radiance = (0,0,0) switches it off
+ * (the state after ptb_upload_scene).  Spec: oracle/pt_scene_oracle.h "sun"; results are bit-identical to it. */
+int ptb_scene_set_sun(ptb_context *ctx, const float dir_to_light[3], const float radiance[3]);
 /* Live paths entering each bounce of the LAST wave rendered (out[0] = camera rays, out[d] = paths that survived d
  * scatters); writes min(cap, max_depth + 1) entries and their number to *n.  Synchronises. */
 int ptb_scene_queue_sizes(ptb_context *ctx, uint32_t *out, uint32_t cap, uint32_t *n);

@@ -479,7 +479,8 @@ static int32_t scene_sample_core(const pto_scene *s, const pto_accel *a, uint32_
             float w = (d[1] + 1.0f) * 0.5f;
             for (int k = 0; k < 3; ++k) {
                 float c = (1.0f - w) * s->sky_horizon[k] + w * s->sky_zenith[k];
-                rgb[k] = thr[k] * c;
+                if (s->sun_on) rgb[k] = rgb[k] + thr[k] * c;
+                else rgb[k] = thr[k] * c;
             }
             return primary;
         }
@@ -490,6 +491,13 @@ static int32_t scene_sample_core(const pto_scene *s, const pto_accel *a, uint32_
         pto_pcg3d(v);
         float u1 = pto_bits_to_unit(v[0]), u2 = pto_bits_to_unit(v[1]), u3 = pto_bits_to_unit(v[2]);
         float dn[3], att[3];
+        if (s->sun_on && m->type == PTO_MAT_LAMBERT) {          /* next-event estimation (spec: pt_scene_oracle.h "sun") */
+            int front = dot3(d, n_out) < 0.0f;
+            float n[3] = { front ? n_out[0] : -n_out[0], front ? n_out[1] : -n_out[1], front ? n_out[2] : -n_out[2] };
+            float c = dot3(n, s->sun_dir);
+            if (c > 0.0f && !pto_any_hit(s, a, P, s->sun_dir, s->t_min, INFINITY))
+                for (int k = 0; k < 3; ++k) rgb[k] = rgb[k] + (thr[k] * m->albedo[k]) * (s->sun_rad[k] * c);
+        }
         if (!pto_scatter(m, d, n_out, u1, u2, u3, dn, att)) return primary;
         for (int k = 0; k < 3; ++k) { thr[k] = thr[k] * att[k]; o[k] = P[k]; d[k] = dn[k]; }
     }

@@ -33,6 +33,14 @@
  *   radiance   sky-lit: a path that escapes adds throughput*sky(d) to the pixel; a path that
  *              is absorbed or still alive after max_depth scatters adds nothing.  Each sample
  *              adds (L.r, L.g, L.b, 1) to the pixel's float4 accumulator, in sample order.
+ *   sun        (optional, sun_on != 0; no reference counterpart) next-event estimation towards one
+ *              directional light: at every hit that scatters on a LAMBERT material, with n the
+ *              normal turned against the incoming ray, c = n.sun_dir (sun_dir used as given);
+ *              if c > 0 and pto_any_hit(P, sun_dir, t_min, +inf) finds nothing, the path's radiance
+ *              gains L_k = L_k + (thr_k*albedo_k)*(sun_rad_k*c), thr = the throughput BEFORE this
+ *              scatter.  With the sun on, L starts at +0 and every contribution (also the sky term
+ *              of the escaping segment) is L = L + x, in path order; the sky does not contain the
+ *              sun, so nothing is counted twice.  Metal and dielectric hits get no sun term.
  */
 #ifndef PT_SCENE_ORACLE_H
 #define PT_SCENE_ORACLE_H
@@ -75,6 +83,8 @@ typedef struct pto_scene {
     const uint32_t *tri_mat;       /* n_tris */
     uint32_t n_materials;
     const pto_material *materials;
+    uint32_t sun_on;               /* next-event estimation towards a directional light */
+    float    sun_dir[3], sun_rad[3];
 } pto_scene;
 
 typedef struct pto_accel pto_accel;   /* CPU BVH (median split); NULL everywhere = brute force */

@@ -27,6 +27,7 @@ class SceneC(C.Structure):
         ("n_spheres", C.c_uint32), ("spheres", C.c_void_p), ("sphere_mat", C.c_void_p),
         ("n_tris", C.c_uint32), ("tris", C.c_void_p), ("tri_mat", C.c_void_p),
         ("n_materials", C.c_uint32), ("materials", C.c_void_p),
+        ("sun_on", C.c_uint32), ("sun_dir", C.c_float * 3), ("sun_rad", C.c_float * 3),
     ]
 
 
@@ -91,6 +92,10 @@ class SceneOracle:
         c.tri_mat = scene.tri_material.ctypes.data
         c.n_materials = len(scene.materials)
         c.materials = scene.materials.ctypes.data
+        c.sun_on = 1 if getattr(scene, "sun_on", False) else 0
+        if c.sun_on:
+            c.sun_dir[:] = [float(v) for v in scene.sun_dir]
+            c.sun_rad[:] = [float(v) for v in scene.sun_radiance]
         self.c = c
         self._accel = lib().pto_accel_build(C.byref(c), max_leaf) if accel == "bvh" else None
 

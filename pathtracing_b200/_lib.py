@@ -151,6 +151,7 @@ SIGNATURES = {
     "ptb_render_resolve": (C.c_int, [_CTX, C.c_uint32, C.c_uint32, C.c_int, C.c_uint32]),
     "ptb_set_row_shard": (C.c_int, [_CTX, C.c_uint32, C.c_uint32]),
     "ptb_scene_set_wave_samples": (C.c_int, [_CTX, C.c_uint32]),
+    "ptb_scene_set_sun": (C.c_int, [_CTX, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "ptb_set_row_shard_bands": (C.c_int, [_CTX, C.c_uint32, C.c_uint32, C.c_uint32]),
     "ptb_upload_scene": (C.c_int, [_CTX, _P(SceneDesc)]),
     "ptb_clear_scene": (C.c_int, [_CTX]),

@@ -80,6 +80,7 @@ public sealed unsafe class NativeTracer : IDisposable
     [DllImport(Lib)] private static extern int ptb_upload_scene(IntPtr ctx, SceneDesc* desc);
     [DllImport(Lib)] private static extern int ptb_clear_scene(IntPtr ctx);
     [DllImport(Lib)] private static extern int ptb_scene_set_wave_samples(IntPtr ctx, uint samplesPerWave);
+    [DllImport(Lib)] private static extern int ptb_scene_set_sun(IntPtr ctx, float[] dirToLight, float[] radiance);
     [DllImport(Lib)] private static extern int ptb_trace_rays(IntPtr ctx, ulong nRays, float* origins, float* dirs, float tMin,
                                                               float tMax, int mode, int* outPrim, float* outT);
 
@@ -203,6 +204,8 @@ public sealed unsafe class NativeTracer : IDisposable
     public void ClearScene() => Check(_ctx, ptb_clear_scene(_ctx));
     /// Samples of every pixel one wave of the scene path carries (0 = as many as fit the path queues). Scheduling only.
     public void SetWaveSamples(uint samplesPerWave) => Check(_ctx, ptb_scene_set_wave_samples(_ctx, samplesPerWave));
+    /// <summary>Directional light sampled by next-event estimation (any-hit shadow rays) at Lambert hits; radiance 0 = off.</summary>
+    public void SetSun(float[] dirToLight, float[] radiance) => Check(_ctx, ptb_scene_set_sun(_ctx, dirToLight, radiance));
 
     public void TraceRays(ReadOnlySpan<float> origins, ReadOnlySpan<float> dirs, float tMin, float tMax, bool anyHit,
                           Span<int> prim, Span<float> t)

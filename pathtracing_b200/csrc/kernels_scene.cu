@@ -438,7 +438,56 @@ __device__ __forceinline__ void camera_uv(const SceneK &k, const WaveArgs &w, ui
     uvy = (fy / k.div_y) * 2.0f - 1.0f;
 }
 
-template <bool DEPTH0, bool STATS>
+// Sun term of a hit that is about to scatter (spec: oracle/pt_scene_oracle.h "sun"): for a Lambert material lit from its
+// front side, c = (throughput * albedo) * (radiance * n.l) with the throughput BEFORE this scatter; returns whether a shadow
+// ray has to confirm it.  d = incoming direction, n_out = outward normal.
+template <bool SUN>
+__device__ __forceinline__ bool sun_term(const SceneK &k, const ptb_material &m, float dx, float dy, float dz, float nox, float noy,
+                                         float noz, float tr, float tg, float tb, float &cr, float &cg, float &cb)
+{
+    if (!SUN || m.type != PTB_MAT_LAMBERT) return false;
+    const bool front = dot3f(dx, dy, dz, nox, noy, noz) < 0.0f;
+    const float nx = front ? nox : -nox, ny = front ? noy : -noy, nz = front ? noz : -noz;
+    const float c = dot3f(nx, ny, nz, k.sun_dir[0], k.sun_dir[1], k.sun_dir[2]);
+    if (!(c > 0.0f)) return false;
+    cr = (tr * m.albedo[0]) * (k.sun_rad[0] * c);
+    cg = (tg * m.albedo[1]) * (k.sun_rad[1] * c);
+    cb = (tb * m.albedo[2]) * (k.sun_rad[2] * c);
+    return true;
+}
+
+// Radiance (cr, cg, cb) of one path segment into the path's slot / its pixel's accumulator.  Without the sun a path adds
+// radiance once, when it ends; with it (slices always in use) the slot is the path's running sum L = L + x from +0.
+template <bool DEPTH0, bool SUN>
+__device__ __forceinline__ void add_radiance(const SceneK &k, const WaveArgs &w, uint32_t s_local, uint32_t loc, uint32_t pix,
+                                             float cr, float cg, float cb, bool add)
+{
+    if (w.slices) {                                 // launch-uniform: batched wave
+        float4 *slot = &w.slices[(size_t)s_local * w.n0_pixels + loc];
+        if (SUN) {
+            if (DEPTH0) {
+                __stcs(slot, make_float4(0.0f + cr, 0.0f + cg, 0.0f + cb, 1.0f));
+            } else if (add) {
+                float4 v = *slot;
+                v.x = v.x + cr; v.y = v.y + cg; v.z = v.z + cb;
+                *slot = v;
+            }
+        } else if (DEPTH0 || add) {
+            // every path stores its slot at depth 0 (zero radiance while it is still alive) and once more when it ends
+            __stcs(slot, make_float4(cr, cg, cb, 1.0f));
+        }
+    } else if (DEPTH0) {
+        float4 acc = w.accum[pix];
+        acc.x = acc.x + cr; acc.y = acc.y + cg; acc.z = acc.z + cb; acc.w = acc.w + 1.0f;
+        w.accum[pix] = acc;
+    } else if (add) {
+        float4 acc = w.accum[pix];
+        acc.x = acc.x + cr; acc.y = acc.y + cg; acc.z = acc.z + cb;
+        w.accum[pix] = acc;
+    }
+}
+
+template <bool DEPTH0, bool STATS, bool SUN>
 __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel_chunk(const SceneK k, const WaveArgs w)
 {
     const unsigned lane = threadIdx.x & 31u;
@@ -512,6 +561,8 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel_chun
         Best best;
         const bool hit = closest_hit<STATS, true>(k, r, k.t_min, __int_as_float(0x7F800000) /* +inf */, alive, best, cn, w.error_flag);
         __syncwarp();
+        const bool shaded = alive;
+        bool need_shadow = false;                  // sun: this hit's direct light is added if the shadow ray finds nothing
         if (alive) {
             if (STATS) ++n_rays;
             if (DEPTH0 && w.hit_ids) w.hit_ids[pix] = hit ? best.id : -1;
@@ -539,6 +590,7 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel_chun
                 const ptb_material m = k.materials[mat < k.n_materials ? mat : 0u];
                 const U3 v = pcg3d(pix, w.sample + s_local, k.seed + (depth + 1u) * 0x9E3779B9u);
                 if (STATS) ++n_scatter;
+                need_shadow = sun_term<SUN>(k, m, dx, dy, dz, nx, ny, nz, tr, tg, tb, cr, cg, cb);
                 if (scatter(m, dx, dy, dz, nx, ny, nz, bits_to_unit(v.x), bits_to_unit(v.y), bits_to_unit(v.z))) {
                     tr = tr * m.albedo[0]; tg = tg * m.albedo[1]; tb = tb * m.albedo[2];
                     ox = Px; oy = Py; oz = Pz;
@@ -546,19 +598,20 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel_chun
                     alive = false;
                 }
             }
-            if (w.slices) {                             // launch-uniform: batched wave
-                // every path stores its slot at depth 0 (zero radiance while it is still alive) and once more when it ends
-                if (DEPTH0 || add) __stcs(&w.slices[(size_t)s_local * w.n0_pixels + loc], make_float4(cr, cg, cb, 1.0f));
-            } else if (DEPTH0) {
-                float4 acc = w.accum[pix];
-                acc.x = acc.x + cr; acc.y = acc.y + cg; acc.z = acc.z + cb; acc.w = acc.w + 1.0f;
-                w.accum[pix] = acc;
-            } else if (add) {
-                float4 acc = w.accum[pix];
-                acc.x = acc.x + cr; acc.y = acc.y + cg; acc.z = acc.z + cb;
-                w.accum[pix] = acc;
-            }
         }
+        if (SUN && __any_sync(FULL, need_shadow)) {       // shadow rays: any-hit walk, the whole warp takes part
+            RayT sr;
+            make_ray(sr, ox, oy, oz, k.sun_dir[0], k.sun_dir[1], k.sun_dir[2]);
+            Best sb;
+            sb.t = __int_as_float(0x7F800000); sb.t_cull = sb.t; sb.id = -1; sb.pos = 0; sb.cls = 0;
+            bool occluded = traverse<0, true, STATS, true>(k, sr, k.t_min, sb.t, need_shadow, sb, cn, w.error_flag);
+            occluded = traverse<1, true, STATS, true>(k, sr, k.t_min, sb.t, need_shadow && !occluded, sb, cn, w.error_flag) || occluded;
+            __syncwarp();
+            if (STATS && need_shadow) ++n_rays;
+            if (need_shadow && !occluded) add = true;
+            else if (need_shadow) cr = cg = cb = 0.0f;
+        }
+        if (shaded) add_radiance<DEPTH0, SUN>(k, w, s_local, loc, pix, cr, cg, cb, add);
         const unsigned live = __ballot_sync(FULL, alive);
         if (!DEPTH0 && w.tail) {
             // tail mode (launch-uniform): the few paths still alive at this depth finish here, bounce after bounce, with
@@ -685,7 +738,7 @@ __device__ __forceinline__ bool slab_walk(float lox, float hix, float loy, float
     return t_near <= fmaf(fabsf(tf), 1.9073486e-6f, tf);     // widened away from zero whatever the sign of tf
 }
 
-template <bool DEPTH0, bool STATS>
+template <bool DEPTH0, bool STATS, bool SUN>
 __global__ void __launch_bounds__(256, PTB_QUEUE_MIN_BLOCKS) bounce_kernel(const SceneK k, const WaveArgs w)
 {
     __shared__ QueueShared S;
@@ -707,9 +760,11 @@ __global__ void __launch_bounds__(256, PTB_QUEUE_MIN_BLOCKS) bounce_kernel(const
     uint32_t n_rays = 0, n_scatter = 0;
     int stack[STACK_N];                                // local memory, as in the chunk schedule (a shared-memory short stack
                                                        // was measured: no faster, and its 12 KB per block come out of L1)
-    uint32_t cold_[5] = {0u, 0u, 0u, 0u, 0u};          // throughput r, g, b, id word, depth
+    // throughput r, g, b, id word, depth; while a shadow ray is out: the scattered direction [5..7] and the sun term [8..10]
+    uint32_t cold_[11] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
     volatile uint32_t *const cold = cold_;
     bool has = false;                  // this lane holds a path (walking, or walked and not shaded yet)
+    bool shadow = false;               // ... and what it walks is the path's shadow ray towards the sun (any hit ends it)
     bool exhausted = false;            // warp-uniform: the cursor has run past the queue
     int cur = EMPTY_REF, sp = 0, cls = 0;
     WalkRay r = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -884,18 +939,41 @@ __global__ void __launch_bounds__(256, PTB_QUEUE_MIN_BLOCKS) bounce_kernel(const
                 __syncwarp();
                 const float tb_ = ldsf(sa_best + tid * 8u + 4u);
                 t_cull = fmaf(fabsf(tb_), 1.9073486e-6f, tb_);
+                if (SUN && shadow && tb_ < INF) cur = EMPTY_REF;     // any hit: the sun is occluded, nothing more to learn
             }
             const unsigned wk = __ballot_sync(FULL, cur != EMPTY_REF);
             if (wk == 0u || __popc(wk) < pause_below) break;
         }
         if (qn != 0u) test_batch(qn);                        // flush: the paths about to be shaded need every result
         __syncwarp();
+        if (SUN && shadow && cur != EMPTY_REF && ldsf(sa_best + tid * 8u + 4u) < INF) cur = EMPTY_REF;
 
         // ---- shade and scatter the paths whose walk has ended ----
         bool cont = false;                                   // goes to the next bounce's queue
         float Px = 0, Py = 0, Pz = 0, dx = 0, dy = 0, dz = 0, tr = 0, tg = 0, tb = 0;
         uint32_t idw = 0;
-        if (has && cur == EMPTY_REF) {
+        if (SUN && has && cur == EMPTY_REF && shadow) {
+            // the shadow ray of a Lambert hit has finished: add the sun term if nothing was hit, then the path goes on
+            // with the scattered ray that has been waiting (origin = the shadow ray's)
+            shadow = false;
+            idw = cold[3];
+            const uint32_t s_local = w.batch > 1u ? idw >> PIX_BITS : 0u;
+            const uint32_t loc = w.batch > 1u ? idw & PIX_MASK : idw;
+            if (STATS) ++n_rays;
+            if (lds64(sa_best + tid * 8u) == NO_HIT)
+                add_radiance<false, SUN>(k, w, s_local, loc, 0u, __uint_as_float(cold[8]), __uint_as_float(cold[9]), __uint_as_float(cold[10]), true);
+            const uint32_t ra = sa_ray + tid * 4u;
+            Px = ldsf(ra); Py = ldsf(ra + 1024u); Pz = ldsf(ra + 2048u);
+            dx = __uint_as_float(cold[5]); dy = __uint_as_float(cold[6]); dz = __uint_as_float(cold[7]);
+            tr = __uint_as_float(cold[0]); tg = __uint_as_float(cold[1]); tb = __uint_as_float(cold[2]);
+            if (!DEPTH0 && w.tail) {
+                start_walk(Px, Py, Pz, dx, dy, dz);
+                cold[4] = cold[4] + 1u;
+            } else {
+                cont = true;
+                has = false;
+            }
+        } else if (has && cur == EMPTY_REF) {
             Best best;
             const unsigned long long bk = lds64(sa_best + tid * 8u);
             const uint32_t bp = lds32(sa_pos + tid * 4u);
@@ -914,7 +992,8 @@ __global__ void __launch_bounds__(256, PTB_QUEUE_MIN_BLOCKS) bounce_kernel(const
             const uint32_t y = shard_row(k.row_offset, k.row_stride, k.row_block, yy);
             const uint32_t pix = y * k.width + x;
             float cr = 0.0f, cg = 0.0f, cb = 0.0f;           // radiance this path adds now
-            bool add = false, alive = true;
+            float sr = 0.0f, sg = 0.0f, sb = 0.0f;           // ... and may add once its shadow ray has come back empty
+            bool add = false, alive = true, need_shadow = false;
             if (STATS) ++n_rays;
             if (DEPTH0 && w.hit_ids) w.hit_ids[pix] = hit ? best.id : -1;
             float nx = 0, ny = 0, nz = 0;
@@ -947,26 +1026,22 @@ __global__ void __launch_bounds__(256, PTB_QUEUE_MIN_BLOCKS) bounce_kernel(const
                 const ptb_material m = k.materials[mat < k.n_materials ? mat : 0u];
                 const U3 v = pcg3d(pix, w.sample + s_local, k.seed + (depth + 1u) * 0x9E3779B9u);
                 if (STATS) ++n_scatter;
+                need_shadow = sun_term<SUN>(k, m, dx, dy, dz, nx, ny, nz, tr, tg, tb, sr, sg, sb);
                 if (scatter(m, dx, dy, dz, nx, ny, nz, bits_to_unit(v.x), bits_to_unit(v.y), bits_to_unit(v.z))) {
                     tr = tr * m.albedo[0]; tg = tg * m.albedo[1]; tb = tb * m.albedo[2];
                 } else {
                     alive = false;
                 }
             }
-            if (w.slices) {                                  // launch-uniform: batched wave
-                // every path stores its slot at depth 0 (zero radiance while it is still alive) and once more when it ends
-                if (DEPTH0 || add) __stcs(&w.slices[(size_t)s_local * w.n0_pixels + loc], make_float4(cr, cg, cb, 1.0f));
-            } else if (DEPTH0) {
-                float4 acc = w.accum[pix];
-                acc.x = acc.x + cr; acc.y = acc.y + cg; acc.z = acc.z + cb; acc.w = acc.w + 1.0f;
-                w.accum[pix] = acc;
-            } else if (add) {
-                float4 acc = w.accum[pix];
-                acc.x = acc.x + cr; acc.y = acc.y + cg; acc.z = acc.z + cb;
-                w.accum[pix] = acc;
-            }
+            add_radiance<DEPTH0, SUN>(k, w, s_local, loc, pix, cr, cg, cb, add);
             if (!alive) {
                 has = false;
+            } else if (need_shadow) {                        // the shadow ray first; the scattered ray waits in local memory
+                cold[0] = __float_as_uint(tr); cold[1] = __float_as_uint(tg); cold[2] = __float_as_uint(tb);
+                cold[5] = __float_as_uint(dx); cold[6] = __float_as_uint(dy); cold[7] = __float_as_uint(dz);
+                cold[8] = __float_as_uint(sr); cold[9] = __float_as_uint(sg); cold[10] = __float_as_uint(sb);
+                start_walk(Px, Py, Pz, k.sun_dir[0], k.sun_dir[1], k.sun_dir[2]);
+                shadow = true;
             } else if (!DEPTH0 && w.tail) {                  // launch-uniform: the path stays in this lane
                 start_walk(Px, Py, Pz, dx, dy, dz);
                 cold[0] = __float_as_uint(tr); cold[1] = __float_as_uint(tg); cold[2] = __float_as_uint(tb);
@@ -1107,29 +1182,36 @@ __global__ void __launch_bounds__(256) trace_rays_kernel(const SceneK k, uint64_
     }
 }
 
-int g_wave_blocks[2][2][2] = {};
+int g_wave_blocks[2][2][2][2] = {};
 
-template <bool DEPTH0, bool STATS, bool CHUNK>
+template <bool DEPTH0, bool STATS, bool SUN, bool CHUNK>
 int wave_blocks()
 {
-    int &cached = g_wave_blocks[DEPTH0][STATS][CHUNK];
+    int &cached = g_wave_blocks[DEPTH0][STATS][SUN][CHUNK];
     if (cached == 0) {
         int per_sm = 0, dev = 0, sms = 148;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        const cudaError_t e = CHUNK ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bounce_kernel_chunk<DEPTH0, STATS>, 256, 0)
-                                    : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bounce_kernel<DEPTH0, STATS>, 256, 0);
+        const cudaError_t e = CHUNK ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bounce_kernel_chunk<DEPTH0, STATS, SUN>, 256, 0)
+                                    : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bounce_kernel<DEPTH0, STATS, SUN>, 256, 0);
         if (e != cudaSuccess || per_sm < 1) per_sm = 1;
         cached = per_sm * sms;
     }
     return cached;
 }
 
+template <bool DEPTH0, bool STATS, bool SUN>
+void launch_bounce_t(const SceneK &k, const WaveArgs &w, bool chunk, cudaStream_t s)
+{
+    if (chunk) bounce_kernel_chunk<DEPTH0, STATS, SUN><<<wave_blocks<DEPTH0, STATS, SUN, true>(), 256, 0, s>>>(k, w);
+    else bounce_kernel<DEPTH0, STATS, SUN><<<wave_blocks<DEPTH0, STATS, SUN, false>(), 256, 0, s>>>(k, w);
+}
+
 template <bool DEPTH0, bool STATS>
 void launch_bounce(const SceneK &k, const WaveArgs &w, bool chunk, cudaStream_t s)
 {
-    if (chunk) bounce_kernel_chunk<DEPTH0, STATS><<<wave_blocks<DEPTH0, STATS, true>(), 256, 0, s>>>(k, w);
-    else bounce_kernel<DEPTH0, STATS><<<wave_blocks<DEPTH0, STATS, false>(), 256, 0, s>>>(k, w);
+    if (k.sun_on) launch_bounce_t<DEPTH0, STATS, true>(k, w, chunk, s);
+    else launch_bounce_t<DEPTH0, STATS, false>(k, w, chunk, s);
 }
 
 }  // namespace
@@ -1172,6 +1254,9 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
                                                                   // margin: every warp runs the cursor past the end once)
     const uint32_t n0 = (uint32_t)n0_64;
     const uint32_t depths = k.shade_mode == PTB_SHADE_NORMALS ? 1u : k.max_depth + 1u;
+    // per-path radiance slots: batched waves, and every wave when the sun is on (a path then adds radiance several times)
+    const bool use_slices = batch > 1u || k.sun_on;
+    if (use_slices && !st->slices) return cudaErrorInvalidValue;
     // bounces >= tail_depth run inside ONE launch (0 disables): queues that deep are too small to fill the GPU.  With the
     // queue schedule in the tail launch (default) the tail starts at bounce 3 (c3: 2, 3, 4, 6 -> 4,147 / 4,149 / 4,128 / 4,061
     // Msamples/s); with the chunk schedule there, at 4, or 6 for big batched waves (>= 8 Mi camera rays), whose queues stay
@@ -1208,7 +1293,7 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
         w.sample = sample;
         w.batch = batch;
         w.tiles = tiles_x * tiles_y;
-        w.slices = batch > 1u ? st->slices : nullptr;
+        w.slices = use_slices ? st->slices : nullptr;
         w.jitter = jitter ? 1 : 0;
         w.tail = (tail_depth > 0 && d >= tail_depth && d + 1u < depths) ? 1 : 0;
         w.accum = accum;
@@ -1228,7 +1313,7 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
         if (launches) ++*launches;
         if (w.tail) break;
     }
-    if (batch > 1u) {
+    if (use_slices) {
         const unsigned blocks = min((n0_pixels + 255u) / 256u, 148u * 8u);
         reduce_slices_kernel<<<blocks, 256, 0, s>>>(k, accum, st->slices, batch, n0_pixels);
         if (launches) ++*launches;

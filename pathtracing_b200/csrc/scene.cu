@@ -91,6 +91,11 @@ ptb::SceneK make_k(const ptb_context *ctx, const SceneState *st)
     k.tri_nodes = st->tri_bvh.nodes;
     k.tri_root = st->tri_bvh.root_ref;
     k.materials = st->materials;
+    k.sun_on = (st->sun_on && st->desc.shade_mode != PTB_SHADE_NORMALS) ? 1u : 0u;   // the normals mode has no light
+    for (int i = 0; i < 3; ++i) {
+        k.sun_dir[i] = st->sun_dir[i];
+        k.sun_rad[i] = st->sun_rad[i];
+    }
     return k;
 }
 
@@ -389,6 +394,28 @@ int ptb_scene_set_wave_samples(ptb_context *ctx, uint32_t samples_per_wave)
     if (!ctx) return ptb::fail_msg(nullptr, PTB_ERR_INVALID, "ptb_scene_set_wave_samples: ctx is NULL");
     if (!ctx->scene) return ptb::fail_msg(ctx, PTB_ERR_STATE, "ptb_scene_set_wave_samples: no scene resident");
     state(ctx)->wave_samples = samples_per_wave;
+    return PTB_OK;
+}
+
+int ptb_scene_set_sun(ptb_context *ctx, const float dir_to_light[3], const float radiance[3])
+{
+    if (!ctx) return ptb::fail_msg(nullptr, PTB_ERR_INVALID, "ptb_scene_set_sun: ctx is NULL");
+    if (!dir_to_light || !radiance) return ptb::fail_msg(ctx, PTB_ERR_INVALID, "ptb_scene_set_sun: NULL argument");
+    if (!ctx->scene) return ptb::fail_msg(ctx, PTB_ERR_STATE, "ptb_scene_set_sun: no scene resident");
+    bool finite = true, dir_nonzero = false, on = false;
+    for (int i = 0; i < 3; ++i) {
+        finite = finite && std::isfinite(dir_to_light[i]) && std::isfinite(radiance[i]);
+        dir_nonzero = dir_nonzero || dir_to_light[i] != 0.0f;
+        on = on || radiance[i] != 0.0f;
+    }
+    if (!finite) return ptb::fail_msg(ctx, PTB_ERR_INVALID, "ptb_scene_set_sun: direction and radiance must be finite");
+    if (on && !dir_nonzero) return ptb::fail_msg(ctx, PTB_ERR_INVALID, "ptb_scene_set_sun: the direction is the zero vector");
+    SceneState *st = state(ctx);
+    st->sun_on = on;
+    for (int i = 0; i < 3; ++i) {
+        st->sun_dir[i] = dir_to_light[i];
+        st->sun_rad[i] = radiance[i];
+    }
     return PTB_OK;
 }
 

@@ -62,6 +62,9 @@ struct SceneK {
     const BvhNode *tri_nodes;
     int tri_root;
     const ptb_material *materials;
+    // next-event estimation towards a directional light (ptb_scene_set_sun); sun_on = 0: none
+    uint32_t sun_on;
+    float sun_dir[3], sun_rad[3];
 };
 
 // Wavefront path state, structure of arrays, ping-pong (in/out) per bounce:
@@ -95,6 +98,8 @@ struct SceneState {
     uint32_t *error_flag = nullptr; // traversal stack overflow etc.
     bool count_stats = false;
     uint32_t last_n0 = 0;           // camera rays of the last wave
+    bool sun_on = false;            // ptb_scene_set_sun
+    float sun_dir[3] = {0.f, 1.f, 0.f}, sun_rad[3] = {0.f, 0.f, 0.f};
 };
 
 // scene_build.cu: builds one hierarchy from per-primitive boxes (lo/hi as float4, w unused).

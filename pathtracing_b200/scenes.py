@@ -44,6 +44,10 @@ class Scene:
     t_min: float = 1e-3
     shade_mode: int = SHADE_PATH
     name: str = "scene"
+    # optional directional light sampled by next-event estimation at Lambert hits (ptb_scene_set_sun); radiance 0 = off.
+    # sun_dir points TOWARDS the light and is used as given (set_sun() normalises).
+    sun_dir: np.ndarray = dataclasses.field(default_factory=lambda: _f3([0, 1, 0]))
+    sun_radiance: np.ndarray = dataclasses.field(default_factory=lambda: _f3([0, 0, 0]))
 
     def __post_init__(self):
         self.spheres = np.ascontiguousarray(self.spheres, np.float32).reshape(-1, 4)
@@ -54,8 +58,19 @@ class Scene:
         assert len(self.spheres) == len(self.sphere_material)
         assert len(self.triangles) == len(self.tri_material)
         assert len(self.materials) >= 1
-        for f in ("cam_origin", "cam_u", "cam_v", "cam_w", "sky_horizon", "sky_zenith"):
+        for f in ("cam_origin", "cam_u", "cam_v", "cam_w", "sky_horizon", "sky_zenith", "sun_dir", "sun_radiance"):
             setattr(self, f, _f3(getattr(self, f)))
+
+    @property
+    def sun_on(self) -> bool:
+        return bool(np.any(self.sun_radiance != 0))
+
+    def set_sun(self, direction, radiance) -> "Scene":
+        """Directional light: `direction` points towards it (normalised here in binary64, stored as float32)."""
+        d = np.asarray(direction, np.float64).reshape(3)
+        self.sun_dir = _f3(d / np.linalg.norm(d))
+        self.sun_radiance = _f3(radiance)
+        return self
 
     @property
     def n_spheres(self) -> int:
@@ -66,7 +81,7 @@ class Scene:
         return len(self.triangles)
 
     # -- scene files (the reference has none: its scene is literals in the shader) -------------
-    _VEC_FIELDS = ("cam_origin", "cam_u", "cam_v", "cam_w", "sky_horizon", "sky_zenith")
+    _VEC_FIELDS = ("cam_origin", "cam_u", "cam_v", "cam_w", "sky_horizon", "sky_zenith", "sun_dir", "sun_radiance")
 
     def to_dict(self) -> dict:
         """JSON-able description (lists of Python floats; float32 values survive the round trip exactly)."""
@@ -113,7 +128,7 @@ class Scene:
                 raise ValueError("not a ptb200 scene file")
             return cls(spheres=z["spheres"], sphere_material=z["sphere_material"], triangles=z["triangles"],
                        tri_material=z["tri_material"], materials=z["materials"], t_min=float(z["t_min"]),
-                       shade_mode=int(z["shade_mode"]), name=str(z["name"]), **{f: z[f] for f in cls._VEC_FIELDS})
+                       shade_mode=int(z["shade_mode"]), name=str(z["name"]), **{f: z[f] for f in cls._VEC_FIELDS if f in z})
 
     def look_at(self, look_from, look_at, vup, vfov_deg: float, width: int, height: int) -> "Scene":
         """Pinhole camera in the reference's screen convention (Test.hlsl:7: uv = p/H*2-1 on BOTH axes, no

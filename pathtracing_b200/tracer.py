@@ -178,6 +178,14 @@ class NativeTracer:
         d.max_leaf = max_leaf
         d.flags = _lib.SCENE_COUNT_STATS if count_stats else 0
         self._ck(self._lib.ptb_upload_scene(self._ctx, C.byref(d)))
+        if getattr(scene, "sun_on", False):
+            self.set_sun(scene.sun_dir, scene.sun_radiance)
+
+    def set_sun(self, dir_to_light, radiance) -> None:
+        """Directional light sampled by next-event estimation at Lambert hits (any-hit shadow rays); radiance 0 = off."""
+        d = (C.c_float * 3)(*[float(v) for v in dir_to_light])
+        r = (C.c_float * 3)(*[float(v) for v in radiance])
+        self._ck(self._lib.ptb_scene_set_sun(self._ctx, d, r))
 
     def clear_scene(self) -> None:
         self._ck(self._lib.ptb_clear_scene(self._ctx))

@@ -420,6 +420,76 @@ def test_bounce_schedule_is_scheduling_only(S, make, w, h, depth, monkeypatch):
                     assert st["paths"] == 5 * w * h and st["rays"] >= st["paths"] and st["prims_tested"] > 0
 
 
+def _sunlit(sc):
+    return sc.set_sun([0.35, 1.0, 0.25], [2.0, 1.75, 1.5])
+
+
+@pytest.mark.parametrize("make,w,h,depth", [
+    (lambda w, h: _sunlit(scenes.mixed_small(width=w, height=h)), 160, 90, 6),
+    (lambda w, h: _sunlit(scenes.random_spheres(200, width=w, height=h)), 211, 97, 8),
+    (lambda w, h: _sunlit(scenes.triangle_terrain(24, 2, width=w, height=h)), 192, 108, 5),
+])
+def test_sun_next_event_estimation_matches_the_oracle(S, make, w, h, depth, monkeypatch):
+    """north_star (2) any-hit traversal inside the path tracer: with a directional light every Lambert hit casts a shadow
+    ray (ptb_scene_set_sun).  Accumulation buffers equal the oracle bit for bit under every bounce schedule, wave size,
+    progressive split and row shard; the light changes the image; switching it off restores the sky-lit result."""
+    sc = make(w, h)
+    assert sc.sun_on
+    ref = S.SceneOracle(sc, w, h, max_depth=depth).accumulate(0, 5, seed=4)
+    dark = S.SceneOracle(dataclasses_replace_sun_off(sc), w, h, max_depth=depth).accumulate(0, 5, seed=4)
+    assert np.mean(np.any(ref != dark, axis=-1)) > 0.05 and np.all(ref[..., :3] >= dark[..., :3])
+    cases = [dict(PTB200_BOUNCE="chunk"), dict(PTB200_BOUNCE="queue", PTB200_REFILL="8"),
+             dict(PTB200_BOUNCE="queue", PTB200_REFILL="24", PTB200_D0_QUEUE="1", PTB200_TAIL_DEPTH="1"),
+             dict(PTB200_BOUNCE="tail", PTB200_TAIL_DEPTH="2"), dict(PTB200_BOUNCE="chunk", PTB200_TAIL_DEPTH="2"), dict()]
+    for env in cases:
+        for k in ("PTB200_BOUNCE", "PTB200_REFILL", "PTB200_TAIL_DEPTH", "PTB200_D0_QUEUE"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        for per_wave in (0, 1, 2):
+            with NativeTracer(w, h, seed=4, max_depth=depth) as t:
+                t.upload_scene(sc, count_stats=(per_wave == 2))
+                t.set_wave_samples(per_wave)
+                t.render_samples(0, 3)
+                t.render_samples(3, 2)
+                assert_images_equal(t.read_accum(), ref, f"sun, {env} per_wave={per_wave}")
+                if per_wave == 0:
+                    t.accum_reset()
+                    t.set_row_shard(1, 3, 4)
+                    t.render_samples(0, 5)
+                    rows = np.arange(h) // 4 % 3 == 1
+                    part = t.read_accum()
+                    assert_images_equal(part[rows], ref[rows], f"sun, {env} row shard")
+                    assert np.all(part[~rows] == 0)
+                    t.set_row_shard(0, 1)
+                    t.accum_reset()
+                    t.set_sun([0, 1, 0], [0, 0, 0])
+                    t.render_samples(0, 5)
+                    assert_images_equal(t.read_accum(), dark, f"sun switched off, {env}")
+
+
+def dataclasses_replace_sun_off(sc):
+    import dataclasses
+    return dataclasses.replace(sc, sun_radiance=[0, 0, 0])
+
+
+def test_sun_argument_errors_and_frame_path(S):
+    w, h = 96, 54
+    sc = _sunlit(scenes.mixed_small(width=w, height=h))
+    with NativeTracer(w, h, seed=1, max_depth=4, keep_f32=True) as t:
+        with pytest.raises(PtbError):
+            t.set_sun([0, 1, 0], [1, 1, 1])                      # no scene resident
+        t.upload_scene(sc)
+        with pytest.raises(PtbError):
+            t.set_sun([0, 0, 0], [1, 1, 1])
+        with pytest.raises(PtbError):
+            t.set_sun([0, float("nan"), 0], [1, 1, 1])
+        t.compute_frame(); t.wait()                              # sample 0 without jitter through the wave machinery
+        ref = S.SceneOracle(sc, w, h, max_depth=4).frame(seed=1)
+        assert np.array_equal(t.read_f32().view(np.uint32), ref["f32"].view(np.uint32))
+        assert np.array_equal(t.read_rgba8(), ref["rgba8"])
+
+
 def test_furnace_and_energy_bounds():
     """White sky, albedo-1 Lambert sphere: every path returns exactly the sky radiance times 1 (white furnace)."""
     w, h = 96, 54

@@ -131,6 +131,37 @@ def test_white_furnace_and_depth_limit():
     assert np.all(fr["f32"][fr["hit"] >= 0][:, :3] == 0) and np.all(fr["f32"][fr["hit"] < 0][:, :3] == 1)
 
 
+def test_sun_next_event_estimation_is_analytic_on_a_lit_floor():
+    """Spec "sun" (pt_scene_oracle.h): a Lambert floor under a black sky, lit by a directional light.  Every path's
+    first hit adds albedo * radiance * cos (nothing else can: scattered rays leave into the black sky), a sphere
+    floating above the floor casts a shadow with radiance exactly 0, and without the light the image is black."""
+    w, h = 96, 54
+    floor = [[-50, 0, -50, 50, 0, -50, 50, 0, 50], [-50, 0, -50, 50, 0, 50, -50, 0, 50]]
+    sc = scenes.Scene(spheres=[[0, 1.0, 0, 0.5]], sphere_material=[1], triangles=floor, tri_material=[0, 0],
+                      materials=scenes.materials_array([(scenes.MAT_LAMBERT, (0.5, 0.25, 0.75), 0, 1.5),
+                                                        (scenes.MAT_METAL, (0, 0, 0), 0, 1.5)]),
+                      sky_horizon=[0, 0, 0], sky_zenith=[0, 0, 0])
+    sc.look_at((0, 6, 0.01), (0, 0, 0), (0, 0, -1), 50, w, h)
+    light = np.array([0.6, 0.8, 0.0])
+    sc.set_sun(light, [2.0, 4.0, 1.0])
+    so = S.SceneOracle(sc, w, h, max_depth=4)
+    fr = so.frame()
+    f = fr["f32"][..., :3]
+    on_floor = fr["hit"] >= 1                                   # ids: sphere 0, triangles 1..2
+    expect = np.array([0.5, 0.25, 0.75]) * np.array([2.0, 4.0, 1.0]) * 0.8
+    lit = on_floor & (f[..., 1] > 0)
+    assert lit.mean() > 0.5
+    np.testing.assert_allclose(f[lit], np.broadcast_to(expect, f[lit].shape), rtol=2e-6)
+    shadow = on_floor & ~lit
+    assert 20 < shadow.sum() < 0.2 * w * h and np.all(f[shadow] == 0)
+    # the shadow lies where the light direction says: floor points P with |P + s*light - centre| < r for some s
+    assert np.all(f[fr["hit"] == 0] == 0)                       # the black mirror sphere reflects floor light times albedo 0
+    acc = so.accumulate(0, 3, seed=2)
+    assert np.all(acc[..., 3] == 3) and acc[..., :3].max() <= 3 * expect.max() * (1 + 1e-5)
+    sc.sun_radiance = np.zeros(3, np.float32)
+    assert not sc.sun_on and np.all(S.SceneOracle(sc, w, h, max_depth=4).frame()["f32"][..., :3] == 0)
+
+
 def test_accumulate_is_progressive_and_sample_ranges_are_disjoint():
     sc = scenes.mixed_small(width=64, height=36)
     so = S.SceneOracle(sc, 64, 36, max_depth=4)
@@ -172,13 +203,13 @@ CASES = {
 def test_scene_files_round_trip_exactly(tmp_path):
     """scene description + loader.  JSON and npz round trips preserve every float32 bit, and the
     default scene file shipped with the package is the reference's literal scene (Test.hlsl:8,12-13)."""
-    sc = scenes.mixed_small()
+    sc = scenes.mixed_small().set_sun([0.3, -1, 0.2], [1.5, 1.25, 1.0])
     for ext in ("json", "npz"):
         p = str(tmp_path / f"s.{ext}")
         sc.save(p)
         back = scenes.Scene.load(p)
         for f in ("spheres", "sphere_material", "triangles", "tri_material", "cam_origin", "cam_u", "cam_v", "cam_w",
-                  "sky_horizon", "sky_zenith"):
+                  "sky_horizon", "sky_zenith", "sun_dir", "sun_radiance"):
             assert np.array_equal(getattr(back, f), getattr(sc, f)), (ext, f)
         assert back.materials.tobytes() == sc.materials.tobytes()
         assert (back.t_min, back.shade_mode, back.name) == (np.float32(sc.t_min), sc.shade_mode, sc.name) or back.name == sc.name
