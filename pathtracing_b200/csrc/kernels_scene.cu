@@ -39,6 +39,22 @@ constexpr int STACK_N = 64;
 #endif
 constexpr unsigned FULL = 0xFFFFFFFFu;
 
+// compute-sanitizer is closed on the GPU pool this is developed on (profiles/r02_sanitizer.txt), so the indices the scene
+// kernels compute themselves are checked by a build of their own: -DPTB_BOUNDS_CHECK (experiments/build_variant.sh) turns
+// every PTB_CHK into a test that raises a bit of the scene's error word, which the next ptb_wait / read reports.  The
+// product build compiles them away.
+#ifdef PTB_BOUNDS_CHECK
+#define PTB_CHK(flagp, cond, bit)                                                                                      \
+    do {                                                                                                               \
+        if (!(cond)) atomicOr((flagp), (bit));                                                                         \
+    } while (0)
+#else
+#define PTB_CHK(flagp, cond, bit)                                                                                      \
+    do {                                                                                                               \
+    } while (0)
+#endif
+constexpr uint32_t CHK_NODE = 2u, CHK_PRIM = 4u, CHK_QUEUE_OUT = 8u, CHK_SLOT = 16u, CHK_LEAFQ = 32u, CHK_PIXEL = 64u, CHK_IN = 128u;
+
 struct Counters {
     uint32_t nodes = 0, prims = 0, max_stack = 0;
 };
@@ -166,11 +182,13 @@ __device__ __forceinline__ bool slab(float lox, float hix, float loy, float hiy,
 
 template <int CLS, bool ANY>
 __device__ __forceinline__ bool test_leaf(const SceneK &k, int leaf, const RayT &r, float t_min, float t_max, Best &best,
-                                          uint32_t &prims)
+                                          uint32_t &prims, uint32_t *error_flag)
 {
+    (void)error_flag;
     const uint32_t q = (uint32_t)~leaf;
     const uint32_t first = q & LEAF_FIRST_MASK, count = (q >> LEAF_COUNT_SHIFT) + 1u;
     prims += count;
+    PTB_CHK(error_flag, first + count <= (CLS == 0 ? k.n_spheres : k.n_tris), CHK_PRIM);
     for (uint32_t i = first; i < first + count; ++i) {
         float t;
         int id;
@@ -230,6 +248,7 @@ __device__ __forceinline__ bool traverse(const SceneK &k, const RayT &r, float t
 
     for (;;) {
         while (cur >= 0) {
+            PTB_CHK(error_flag, (uint32_t)cur < (CLS == 0 ? k.n_sph_nodes : k.n_tri_nodes), CHK_NODE);
             const float4 na = __ldg(&nodes[cur].a), nb = __ldg(&nodes[cur].b), nc = __ldg(&nodes[cur].c);
             const int4 nd = __ldg(&nodes[cur].d);
             if (STATS) ++cn.nodes;
@@ -255,7 +274,7 @@ __device__ __forceinline__ bool traverse(const SceneK &k, const RayT &r, float t
             }
         }
         if (cur == EMPTY_REF) break;
-        if (test_leaf<CLS, ANY>(k, cur, r, t_min, t_max, best, prims)) {
+        if (test_leaf<CLS, ANY>(k, cur, r, t_min, t_max, best, prims, error_flag)) {
             found = true;
             break;
         }
@@ -415,6 +434,7 @@ struct WaveArgs {
     float4 *slices;
     int jitter;
     int tail;                 // 1: finish every path of this launch in-kernel (bounce loop, no more queues)
+    uint32_t q_cap;           // capacity of the path queues and of the slices buffer (bounds-checked build)
     uint32_t refill;          // bounce_kernel: walkers pause for a refill when fewer than this many lanes of the warp walk
     float4 *accum;
     int32_t *hit_ids;
@@ -463,6 +483,7 @@ __device__ __forceinline__ void add_radiance(const SceneK &k, const WaveArgs &w,
                                              float cr, float cg, float cb, bool add)
 {
     if (w.slices) {                                 // launch-uniform: batched wave
+        PTB_CHK(w.error_flag, (size_t)s_local * w.n0_pixels + loc < w.q_cap && loc < w.n0_pixels, CHK_SLOT);
         float4 *slot = &w.slices[(size_t)s_local * w.n0_pixels + loc];
         if (SUN) {
             if (DEPTH0) {
@@ -477,10 +498,12 @@ __device__ __forceinline__ void add_radiance(const SceneK &k, const WaveArgs &w,
             __stcs(slot, make_float4(cr, cg, cb, 1.0f));
         }
     } else if (DEPTH0) {
+        PTB_CHK(w.error_flag, pix < k.width * k.height, CHK_PIXEL);
         float4 acc = w.accum[pix];
         acc.x = acc.x + cr; acc.y = acc.y + cg; acc.z = acc.z + cb; acc.w = acc.w + 1.0f;
         w.accum[pix] = acc;
     } else if (add) {
+        PTB_CHK(w.error_flag, pix < k.width * k.height, CHK_PIXEL);
         float4 acc = w.accum[pix];
         acc.x = acc.x + cr; acc.y = acc.y + cg; acc.z = acc.z + cb;
         w.accum[pix] = acc;
@@ -538,6 +561,7 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel_chun
             } else {
                 // streaming (evict-first) access: the path state is touched once per bounce and must not
                 // push the hierarchy out of L2
+                PTB_CHK(w.error_flag, i < w.q_cap, CHK_IN);
                 const float4 s0 = __ldcs(&w.in.s0[i]), s1 = __ldcs(&w.in.s1[i]);
                 const float2 s2 = __ldcs(&w.in.s2[i]);
                 ox = s0.x; oy = s0.y; oz = s0.z;
@@ -630,6 +654,7 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel_chun
             obase = __shfl_sync(FULL, obase, 0);
             if (alive) {
                 const uint32_t o = obase + (uint32_t)__popc(live & ((1u << lane) - 1u));
+                PTB_CHK(w.error_flag, o < w.q_cap, CHK_QUEUE_OUT);
                 __stcs(&w.out.s0[o], make_float4(ox, oy, oz, __uint_as_float(loc | (s_local << PIX_BITS))));
                 __stcs(&w.out.s1[o], make_float4(dx, dy, dz, tr));
                 __stcs(&w.out.s2[o], make_float2(tg, tb));
@@ -801,6 +826,7 @@ __global__ void __launch_bounds__(256, PTB_QUEUE_MIN_BLOCKS) bounce_kernel(const
         const uint32_t first = q & LEAF_FIRST_MASK, count = act ? (q >> LEAF_COUNT_SHIFT) + 1u : 0u;
         unsigned long long key = NO_HIT;
         uint32_t pos = 0;
+        PTB_CHK(w.error_flag, first + count <= (c == 0u ? k.n_spheres : k.n_tris) && own < 256u, CHK_PRIM);
         for (uint32_t i = first; i < first + count; ++i) {
             float t;
             int id;
@@ -864,7 +890,8 @@ __global__ void __launch_bounds__(256, PTB_QUEUE_MIN_BLOCKS) bounce_kernel(const
                 } else {
                     // streaming (evict-first) access: the path state is touched once per bounce and must not
                     // push the hierarchy out of L2
-                    const float4 s0 = __ldcs(&w.in.s0[i]), s1 = __ldcs(&w.in.s1[i]);
+                    PTB_CHK(w.error_flag, i < w.q_cap, CHK_IN);
+                const float4 s0 = __ldcs(&w.in.s0[i]), s1 = __ldcs(&w.in.s1[i]);
                     const float2 s2 = __ldcs(&w.in.s2[i]);
                     start_walk(s0.x, s0.y, s0.z, s1.x, s1.y, s1.z);
                     cold[0] = __float_as_uint(s1.w); cold[1] = __float_as_uint(s2.x); cold[2] = __float_as_uint(s2.y);
@@ -890,6 +917,7 @@ __global__ void __launch_bounds__(256, PTB_QUEUE_MIN_BLOCKS) bounce_kernel(const
             const uint32_t tag = (lane << 27) | ((uint32_t)cls << 26);
             if (cur >= 0) {
                 const BvhNode *__restrict__ nodes = cls == 0 ? k.sph_nodes : k.tri_nodes;
+                PTB_CHK(w.error_flag, (uint32_t)cur < (cls == 0 ? k.n_sph_nodes : k.n_tri_nodes), CHK_NODE);
                 const float4 na = __ldg(&nodes[cur].a), nb = __ldg(&nodes[cur].b), nc = __ldg(&nodes[cur].c);
                 const int2 nd = __ldg((const int2 *)&nodes[cur].d);
                 if (STATS) ++cn.nodes;
@@ -928,6 +956,7 @@ __global__ void __launch_bounds__(256, PTB_QUEUE_MIN_BLOCKS) bounce_kernel(const
             // the warp is converged here: queue slots by ballot, no atomics
             const unsigned m0 = __ballot_sync(FULL, l0), m1 = __ballot_sync(FULL, l1);
             const uint32_t at0 = qn + __popc(m0 & lt), at1 = qn + __popc(m0) + __popc(m1 & lt);
+            PTB_CHK(w.error_flag, (!l0 || at0 < 96u) && (!l1 || at1 < 96u) && (cur == EMPTY_REF || sp <= STACK_N), CHK_LEAFQ);
             if (l0) sts64(sa_queue + at0 * 8u, pack64(tag, ~u0));
             if (l1) sts64(sa_queue + at1 * 8u, pack64(tag, ~u1));
             qn += __popc(m0) + __popc(m1);
@@ -1059,6 +1088,7 @@ __global__ void __launch_bounds__(256, PTB_QUEUE_MIN_BLOCKS) bounce_kernel(const
             obase = __shfl_sync(FULL, obase, 0);
             if (cont) {
                 const uint32_t o = obase + (uint32_t)__popc(outm & lt);
+                PTB_CHK(w.error_flag, o < w.q_cap, CHK_QUEUE_OUT);
                 __stcs(&w.out.s0[o], make_float4(Px, Py, Pz, __uint_as_float(idw)));
                 __stcs(&w.out.s1[o], make_float4(dx, dy, dz, tr));
                 __stcs(&w.out.s2[o], make_float2(tg, tb));
@@ -1301,6 +1331,7 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
         w.stats = st->stats;
         w.error_flag = st->error_flag;
         w.refill = refill;
+        w.q_cap = st->q_cap;
         if (d == 0) {
             // camera rays are coherent: the chunk schedule already runs them at 28 of 32 lanes, without the queue's overheads
             if (st->count_stats) launch_bounce<true, true>(k, w, chunk_d0, s);

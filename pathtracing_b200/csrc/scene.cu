@@ -91,6 +91,8 @@ ptb::SceneK make_k(const ptb_context *ctx, const SceneState *st)
     k.tri_nodes = st->tri_bvh.nodes;
     k.tri_root = st->tri_bvh.root_ref;
     k.materials = st->materials;
+    k.n_sph_nodes = st->sph_bvh.n_nodes;
+    k.n_tri_nodes = st->tri_bvh.n_nodes;
     k.sun_on = (st->sun_on && st->desc.shade_mode != PTB_SHADE_NORMALS) ? 1u : 0u;   // the normals mode has no light
     for (int i = 0; i < 3; ++i) {
         k.sun_dir[i] = st->sun_dir[i];
@@ -121,6 +123,11 @@ int check_error_flag(ptb_context *ctx, SceneState *st)
     SC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     if (flag & 1u)
         return ptb::fail_msg(ctx, PTB_ERR_UNSUPPORTED, "scene traversal stack overflow (hierarchy deeper than 64): results invalid");
+    if (flag & ~1u) {                                   // only the -DPTB_BOUNDS_CHECK build sets these (kernels_scene.cu PTB_CHK)
+        char msg[128];
+        snprintf(msg, sizeof msg, "scene kernels: bounds check failed, flags 0x%x (see PTB_CHK in kernels_scene.cu)", flag);
+        return ptb::fail_msg(ctx, PTB_ERR_CUDA, msg);
+    }
     return PTB_OK;
 }
 

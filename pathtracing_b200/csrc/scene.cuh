@@ -62,6 +62,7 @@ struct SceneK {
     const BvhNode *tri_nodes;
     int tri_root;
     const ptb_material *materials;
+    uint32_t n_sph_nodes, n_tri_nodes;  // node counts (bounds-checked build)
     // next-event estimation towards a directional light (ptb_scene_set_sun); sun_on = 0: none
     uint32_t sun_on;
     float sun_dir[3], sun_rad[3];
