@@ -774,6 +774,19 @@ int ptb_peer_group_bind(ptb_context *ctx, uint32_t n_peers, uint32_t self_rank, 
     for (uint32_t q = 0; q < n_peers; ++q) {
         if (!partial0[q] || !partial1[q] || !flags[q] || ((uintptr_t)partial0[q] & 15u) || ((uintptr_t)partial1[q] & 15u))
             return fail(ctx, PTB_ERR_INVALID, "ptb_peer_group_bind: peer %u pointer is NULL or misaligned", q);
+        // peers of the SAME process on other devices (one host process driving several GPUs, as the reference's C# host
+        // would): plain device pointers, which need peer access switched on; IPC mappings already carry it
+        cudaPointerAttributes at{};
+        if (cudaPointerGetAttributes(&at, partial0[q]) == cudaSuccess && at.type == cudaMemoryTypeDevice && at.device != ctx->cfg.device) {
+            int can = 0;
+            PTB_CUDA(ctx, cudaDeviceCanAccessPeer(&can, ctx->cfg.device, at.device));
+            if (!can) return fail(ctx, PTB_ERR_UNSUPPORTED, "ptb_peer_group_bind: device %d cannot access peer %u's device %d", ctx->cfg.device, q, at.device);
+            const cudaError_t pe = cudaDeviceEnablePeerAccess(at.device, 0);
+            if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) PTB_CUDA(ctx, pe);
+            (void)cudaGetLastError();
+        } else {
+            (void)cudaGetLastError();
+        }
         pg->peer_partial[0][q] = partial0[q];
         pg->peer_partial[1][q] = partial1[q];
         pg->peer_flags[q] = flags[q];

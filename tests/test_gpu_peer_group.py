@@ -75,6 +75,38 @@ def test_pipelined_peer_frames_match_the_rank_ordered_oracle_sum(oracle, world, 
             t.destroy()
 
 
+def test_one_process_driving_several_devices(oracle):
+    """One host process, one context per GPU (the shape of the reference's single-process C# host): peers exchange plain
+    device pointers, ptb_peer_group_bind switches peer access on.  Skipped with fewer than two devices."""
+    import torch
+    n_dev = min(torch.cuda.device_count(), 4)
+    if n_dev < 2:
+        pytest.skip("needs at least two GPUs")
+    w, h, seed = 640, 360, 2
+    p = oracle.frame_params(w, h)
+    ranks = [NativeTracer(w, h, device=d, seed=seed) for d in range(n_dev)]
+    try:
+        for t in ranks:
+            t.peer_group_create()
+        ptrs = [t.peer_group_local() for t in ranks]
+        for r, t in enumerate(ranks):
+            t.peer_group_bind(r, 0, [q[0] for q in ptrs], [q[3] for q in ptrs], [q[2] for q in ptrs], ptrs[0][1], ptrs[0][4])
+        total = np.zeros((h, w, 4), np.float32)
+        spp = 0
+        for first, count in [(0, 8), (8, 8), (16, 5)]:
+            spp += count
+            for r, t in enumerate(ranks):
+                t.peer_frame(*sample_range(first, count, r, n_dev), spp)
+            parts = [oracle.accumulate(p, *sample_range(first, count, r, n_dev), seed, True) for r in range(n_dev)]
+            total = total + rank_order_sum(parts)
+        for t in ranks:
+            t.wait()
+        assert np.array_equal(ranks[0].read_rgba8(), oracle.resolve(total, spp))
+    finally:
+        for t in ranks:
+            t.destroy()
+
+
 def test_peer_frame_built_from_several_sample_ranges_and_reset(oracle):
     w, h, seed, world = 200, 64, 3, 2
     p = oracle.frame_params(w, h)
