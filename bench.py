@@ -381,6 +381,19 @@ def measure(cx, name, K, Wm, headline):
             step(s)
         if p2p:
             sr.finish()
+        fill_ms = 0.0
+        if pipelined and do_flush:
+            # the fills sit inside the one timed interval of a pipelined run; their own duration (alone on the GPU, median
+            # of 5) is taken off again, so that N > 1 and N = 1 (fills untimed, between the per-step intervals) measure the
+            # same thing.  What a merge adds while it shares the GPU with a fill stays in the interval.
+            fe = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(5)]
+            torch.cuda.synchronize()
+            for a, b in fe:
+                a.record(stream)
+                flush.fill_(7)
+                b.record(stream)
+            torch.cuda.synchronize()
+            fill_ms = sorted(a.elapsed_time(b) for a, b in fe)[2]
         barrier()
         clocks = ClockSampler(local)
         if rank == 0 and headline:
@@ -402,7 +415,7 @@ def measure(cx, name, K, Wm, headline):
         launches = t.launch_count - launches0
         step_ms = [a.elapsed_time(b) for a, b in ev[:K]]
         if pipelined:
-            total_ms = ev[0][0].elapsed_time(ev[K][1])
+            total_ms = ev[0][0].elapsed_time(ev[K][1]) - K * fill_ms
             kern_ms = step_ms                          # render launches only (the merge runs on its own stream)
         else:
             total_ms = sum(step_ms)
@@ -593,9 +606,10 @@ def measure(cx, name, K, Wm, headline):
         "step": ("ptb_render_resolve: accumulate + resolve in one launch" if fused else "ptb_compute_frame" if literal else
                  "ptb_peer_frame (render + pipelined fused peer merge)" if p2p else "ptb_render_samples + merge / ptb_resolve"),
         "l2": ("no flush: each step streams two 16 B/pixel partial buffers (> 126 MB L2) plus the peers' slabs" if (pipelined and big) else
-               "flushed between timed steps (" + ("160 MB fill INSIDE the timed interval)" if pipelined else "256 MB fill, untimed)")),
-        "timing": ("one CUDA-event interval over all K steps incl. the L2-flush fills and the drain of in-flight merges; max over ranks"
-                   if pipelined else "per-step CUDA events on the launching stream, summed; max over ranks")})
+               "flushed between timed steps (" + (f"160 MB fill inside the timed interval, its own {fill_ms * 1e3:.1f} us per step taken off again)"
+                                                  if pipelined else "256 MB fill, untimed)")),
+        "timing": ("one CUDA-event interval over all K steps and the drain of in-flight merges, minus K x the isolated duration of the "
+                   "L2-flush fill; max over ranks" if pipelined else "per-step CUDA events on the launching stream, summed; max over ranks")})
     res = {"config": cfg, "value": value, "unit": "Msamples/s", "ms_per_step": total_ms / K, "ms_per_frame": total_ms / K,
            "steps": K, "warmup": Wm, "scaling": wl["scaling"], "roofline": roof,
            "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": 128, "d2h_bytes_per_step": n_pix * 4,

@@ -14,7 +14,22 @@ for t in ranks:
 ptrs = [t.peer_group_local() for t in ranks]
 for r, t in enumerate(ranks):
     t.peer_group_bind(r, 0, [q[0] for q in ptrs], [q[3] for q in ptrs], [q[2] for q in ptrs], ptrs[0][1], ptrs[0][4])
-for rep in range(2):
+direct = os.environ.get("PROF_PEER_DIRECT")      # under ncu: kernel launches are serialised, so the rendezvous kernels (which spin
+                                                 # until the peer's kernel has run) would time out; drive the MERGE kernel directly
+if direct:
+    n = w * h
+    for f in range(frames):
+        for r, t in enumerate(ranks):
+            t.render_samples((f * G + r) * spp, spp)
+        for t in ranks:
+            t.wait()
+        for r, t in enumerate(ranks):            # rank r's slab of every partial -> resolved pixels into rank 0's image
+            first, count = r * n // G, (r + 1) * n // G - r * n // G
+            t.peer_merge([x.device_accum() for x in ranks], ranks[0].device_rgba8(), first, count, (f + 1) * G * spp)
+        for t in ranks:
+            t.wait()
+    print(f"{G} GPUs, direct merges ok", flush=True)
+for rep in range(0 if direct else 2):
     t0 = time.perf_counter()
     for f in range(frames):
         for r, t in enumerate(ranks):

@@ -1301,7 +1301,7 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
     // (the default: it wins there — a path that scatters stays in its lane — and loses 1-5 % on the big early bounces,
     // where its node step costs 2.4x the instructions of the chunk schedule's for 1.5-2x the active lanes; profiles/r02_notes.md)
     const bool q_all = e_bounce && e_bounce[0] == 'q', q_tail = !e_bounce || q_all || e_bounce[0] == 't';
-    const bool chunk_d0 = !q_all || !std::getenv("PTB200_D0_QUEUE");
+    const bool chunk_d0 = !std::getenv("PTB200_D0_QUEUE");
     const int refill_i = e_refill ? std::atoi(e_refill) : PTB_REFILL_DEFAULT;
     const uint32_t refill = (uint32_t)(refill_i < 0 ? 0 : refill_i > 32 ? 32 : refill_i);
     const uint32_t tail_depth = tail_env >= 0 ? (uint32_t)tail_env : (q_tail ? 3u : ((uint64_t)n0_pixels * batch >= (8u << 20) ? 6u : 4u));
