@@ -173,11 +173,7 @@ __device__ __forceinline__ bool slab(float lox, float hix, float loy, float hiy,
     }
     t_near = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
     const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_far));
-#ifdef PTB_SLAB_WIDEN_OLD
-    return t_near <= tf * 1.000002f;
-#else
     return t_near <= fmaf(fabsf(tf), 1.9073486e-6f, tf);     // widened away from zero whatever the sign of tf
-#endif
 }
 
 template <int CLS, bool ANY>
@@ -208,11 +204,7 @@ __device__ __forceinline__ bool test_leaf(const SceneK &k, int leaf, const RayT 
         }
         if (t < best.t || id < best.id || best.id < 0) {     // equal t: the smaller id wins (order independent)
             best.t = t;
-#ifdef PTB_SLAB_WIDEN_OLD
-            best.t_cull = t * 1.000002f;
-#else
             best.t_cull = fmaf(fabsf(t), 1.9073486e-6f, t);
-#endif
             best.id = id;
             best.pos = (int)i;
             best.cls = CLS;
