@@ -223,6 +223,14 @@ __device__ __forceinline__ bool test_leaf(const SceneK &k, int leaf, const RayT 
 // the closest hit had ruled out since (2-4 % fewer node visits, but twice the stack's L1 footprint — 2 x 128 B lines per
 // warp and stack level; c4 929 -> 1,050 without).  A stale entry is culled one level later by the box tests of its children.
 // Lanes without a ray pass active = false.  CLS 0 = spheres, 1 = triangles.  ANY: stop at the first hit.
+#ifdef PTB_CHUNK_SMEM_STACK
+__device__ __noinline__ int *short_stack_base()
+{
+    __shared__ int s[PTB_CHUNK_SMEM_STACK * 256];
+    return s;
+}
+#endif
+
 template <int CLS, bool ANY, bool STATS, bool FMA_SLAB>
 __device__ __forceinline__ bool traverse(const SceneK &k, const RayT &r, float t_min, float t_max, bool active, Best &best,
                                          Counters &cn, uint32_t *error_flag)
@@ -236,7 +244,16 @@ __device__ __forceinline__ bool traverse(const SceneK &k, const RayT &r, float t
     uint32_t prims = 0;
     bool found = false;
 
-#define PTB_POP() (cur = sp > 0 ? stack[--sp] : EMPTY_REF)
+    // A/B build (-DPTB_CHUNK_SMEM_STACK=N, experiments/build_variant.sh): the first N stack levels in shared memory, one
+    // 4-byte column per thread ([level][thread]: conflict-free whatever the lanes' depths), deeper levels in local memory
+    // as before.  Measured in round 2 (profiles/r02_notes.md section 5): no gain, so the product build keeps the local stack.
+#ifdef PTB_CHUNK_SMEM_STACK
+    int *const s_short = short_stack_base();            // one array for both hierarchies (they are walked one after the other)
+#define PTB_STACK_AT(i) (*((i) < PTB_CHUNK_SMEM_STACK ? &s_short[(i) * 256 + threadIdx.x] : &stack[(i)]))
+#else
+#define PTB_STACK_AT(i) stack[(i)]
+#endif
+#define PTB_POP() (cur = sp > 0 ? PTB_STACK_AT(sp - 1) : EMPTY_REF, sp = sp > 0 ? sp - 1 : 0)
 
     for (;;) {
         while (cur >= 0) {
@@ -252,7 +269,8 @@ __device__ __forceinline__ bool traverse(const SceneK &k, const RayT &r, float t
                 const bool swap = tn1 < tn0;
                 cur = swap ? nd.y : nd.x;
                 if (sp < STACK_N) {
-                    stack[sp++] = swap ? nd.x : nd.y;
+                    PTB_STACK_AT(sp) = swap ? nd.x : nd.y;
+                    ++sp;
                     if (STATS) cn.max_stack = max(cn.max_stack, (uint32_t)sp);
                 } else {
                     atomicOr(error_flag, 1u);
@@ -273,6 +291,7 @@ __device__ __forceinline__ bool traverse(const SceneK &k, const RayT &r, float t
         PTB_POP();
     }
 #undef PTB_POP
+#undef PTB_STACK_AT
     if (STATS) cn.prims += prims;
     return ANY ? found : best.id >= 0;
 }
