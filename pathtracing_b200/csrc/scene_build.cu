@@ -22,6 +22,12 @@
 namespace ptb {
 namespace {
 
+#ifndef PTB_ROTATE_DEFAULT
+#define PTB_ROTATE_DEFAULT 4
+#endif
+#ifndef PTB_MORTON_CUBIC_DEFAULT
+#define PTB_MORTON_CUBIC_DEFAULT true
+#endif
 constexpr float SAH_C_PRIM = 1.0f;       // one primitive test (+ its 16/48 B fetch)
 
 __device__ __forceinline__ uint32_t f2ord(float f)
@@ -81,18 +87,23 @@ __device__ __forceinline__ uint64_t spread21(uint32_t v)
     return x;
 }
 
+// cubic != 0: one cell size on all three axes (every axis is scaled by the LARGEST centroid extent), so that the code's
+// leading bits split space where it is actually wide: a terrain's height then only enters at the bit level where cells are
+// as small as its relief, instead of taking every third split from the top (which cuts a height field into interleaved,
+// overlapping halves).  cubic == 0: each axis scaled by its own extent.
 __global__ void __launch_bounds__(256) morton_kernel(const float4 *__restrict__ lo, const float4 *__restrict__ hi, uint32_t n,
-                                                     const uint32_t *__restrict__ cb, uint64_t *keys, uint32_t *vals)
+                                                     const uint32_t *__restrict__ cb, int cubic, uint64_t *keys, uint32_t *vals)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float4 a = lo[i], b = hi[i];
     const float c[3] = {0.5f * (a.x + b.x), 0.5f * (a.y + b.y), 0.5f * (a.z + b.z)};
+    const float ext_max = fmaxf(fmaxf(ord2f(cb[3]) - ord2f(cb[0]), ord2f(cb[4]) - ord2f(cb[1])), ord2f(cb[5]) - ord2f(cb[2]));
     uint32_t q[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         const float mn = ord2f(cb[k]), mx = ord2f(cb[3 + k]);
-        const float ext = mx - mn;
+        const float ext = cubic ? ext_max : mx - mn;
         float t = ext > 0.0f ? (c[k] - mn) / ext : 0.0f;
         t = fminf(fmaxf(t * 2097152.0f, 0.0f), 2097151.0f);
         q[k] = (uint32_t)t;
@@ -163,9 +174,105 @@ __device__ __forceinline__ float box_area(float4 lo, float4 hi)
 
 __device__ __forceinline__ float4 ldcg4(const float4 *p) { return __ldcg(p); }
 
+__device__ __forceinline__ float union_area(float4 alo, float4 ahi, float4 blo, float4 bhi)
+{
+    return box_area(make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), 0.0f),
+                    make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.0f));
+}
+
+// box and cost of child reference c (internal node or one primitive)
+__device__ __forceinline__ void child_box(int c, const float4 *__restrict__ prim_lo, const float4 *__restrict__ prim_hi,
+                                          const uint32_t *__restrict__ vals, const BuildTmp &t, float4 &lo, float4 &hi, float &cost)
+{
+    if (c >= 0) { lo = ldcg4(&t.nlo[c]); hi = ldcg4(&t.nhi[c]); cost = __ldcg(&t.ncost[c]); }
+    else { const uint32_t v = vals[~c]; lo = prim_lo[v]; hi = prim_hi[v]; cost = SAH_C_PRIM * box_area(lo, hi); }
+}
+
+// Tree rotation (Kensler 2008) at node `cur`, tried when its subtree is complete: swapping one child with one grandchild on
+// the other side leaves cur's box alone and changes only the box of the child that is rebuilt; the swap with the largest
+// drop in surface area is taken.  Only children holding more than 2 * max_leaf primitives are rebuilt, so the subtrees that
+// may collapse into leaves (which need their contiguous primitive ranges) are moved as wholes, never restructured.
+__device__ __forceinline__ void try_rotation(int cur, const float4 *__restrict__ prim_lo, const float4 *__restrict__ prim_hi,
+                                             const uint32_t *__restrict__ vals, uint32_t min_prims, float c_trav, BuildTmp &t)
+{
+    int side_best = -1, gc_best = 0;
+    float gain_best = 0.0f;
+    for (int side = 0; side < 2; ++side) {                 // side: the child that is rebuilt (0 = left, 1 = right)
+        const int b = side == 0 ? t.left[cur] : t.right[cur], a = side == 0 ? t.right[cur] : t.left[cur];
+        if (b < 0 || t.range_hi[b] - t.range_lo[b] + 1u <= min_prims || *(volatile uint8_t *)&t.marked[b]) continue;
+        float4 alo, ahi, glo[2], ghi[2];
+        float acost, gcost[2];
+        child_box(a, prim_lo, prim_hi, vals, t, alo, ahi, acost);
+        const int g[2] = {__ldcg(&t.left[b]), __ldcg(&t.right[b])};      // b's own rotation, by another thread, may have changed them
+        child_box(g[0], prim_lo, prim_hi, vals, t, glo[0], ghi[0], gcost[0]);
+        child_box(g[1], prim_lo, prim_hi, vals, t, glo[1], ghi[1], gcost[1]);
+        const float area_b = box_area(ldcg4(&t.nlo[b]), ldcg4(&t.nhi[b]));
+        for (int j = 0; j < 2; ++j) {                      // grandchild g[j] moves up, a takes its place next to g[1 - j]
+            const float gain = area_b - union_area(alo, ahi, glo[1 - j], ghi[1 - j]);
+            if (gain > gain_best) { gain_best = gain; side_best = side; gc_best = j; }
+        }
+    }
+    // grandchild <-> grandchild: cur = ((LL, LR), (RL, RR)) -> ((RL, LR), (LL, RR)) or ((RR, LR), (RL, LL)); both children are rebuilt
+    {
+        const int L = t.left[cur], R = t.right[cur];
+        if (L >= 0 && R >= 0 && t.range_hi[L] - t.range_lo[L] + 1u > min_prims && t.range_hi[R] - t.range_lo[R] + 1u > min_prims &&
+            !*(volatile uint8_t *)&t.marked[L] && !*(volatile uint8_t *)&t.marked[R]) {
+            const int g[4] = {__ldcg(&t.left[L]), __ldcg(&t.right[L]), __ldcg(&t.left[R]), __ldcg(&t.right[R])};
+            float4 glo[4], ghi[4];
+            float gcost[4];
+            for (int j = 0; j < 4; ++j) child_box(g[j], prim_lo, prim_hi, vals, t, glo[j], ghi[j], gcost[j]);
+            const float area_now = box_area(ldcg4(&t.nlo[L]), ldcg4(&t.nhi[L])) + box_area(ldcg4(&t.nlo[R]), ldcg4(&t.nhi[R]));
+            // partner of LL (g[0]) among R's children: RL (g[2]) or RR (g[3]) moves to L, LL moves to R
+            int pick = -1;
+            float gain_gg = gain_best;
+            for (int j = 2; j < 4; ++j) {
+                const int other = j == 2 ? 3 : 2;
+                const float area_new = union_area(glo[j], ghi[j], glo[1], ghi[1]) + union_area(glo[0], ghi[0], glo[other], ghi[other]);
+                if (area_now - area_new > gain_gg) { gain_gg = area_now - area_new; pick = j; }
+            }
+            if (pick >= 0) {
+                const int other = pick == 2 ? 3 : 2;
+                // L' = (g[pick], LR), R' = (LL, g[other])
+                t.left[L] = g[pick]; t.right[L] = g[1];
+                t.left[R] = g[0];    t.right[R] = g[other];
+                if (g[pick] >= 0) t.parent_int[g[pick]] = L; else t.parent_leaf[~g[pick]] = L;
+                if (g[0] >= 0) t.parent_int[g[0]] = R; else t.parent_leaf[~g[0]] = R;
+                const float4 llo = make_float4(fminf(glo[pick].x, glo[1].x), fminf(glo[pick].y, glo[1].y), fminf(glo[pick].z, glo[1].z), 0.0f);
+                const float4 lhi = make_float4(fmaxf(ghi[pick].x, ghi[1].x), fmaxf(ghi[pick].y, ghi[1].y), fmaxf(ghi[pick].z, ghi[1].z), 0.0f);
+                const float4 rlo = make_float4(fminf(glo[0].x, glo[other].x), fminf(glo[0].y, glo[other].y), fminf(glo[0].z, glo[other].z), 0.0f);
+                const float4 rhi = make_float4(fmaxf(ghi[0].x, ghi[other].x), fmaxf(ghi[0].y, ghi[other].y), fmaxf(ghi[0].z, ghi[other].z), 0.0f);
+                t.nlo[L] = llo; t.nhi[L] = lhi; t.ncost[L] = c_trav * box_area(llo, lhi) + gcost[pick] + gcost[1];
+                t.nlo[R] = rlo; t.nhi[R] = rhi; t.ncost[R] = c_trav * box_area(rlo, rhi) + gcost[0] + gcost[other];
+                __threadfence();
+                return;
+            }
+        }
+    }
+    if (side_best < 0 || !(gain_best > 0.0f)) return;
+    const int b = side_best == 0 ? t.left[cur] : t.right[cur], a = side_best == 0 ? t.right[cur] : t.left[cur];
+    const int bl = __ldcg(&t.left[b]), br = __ldcg(&t.right[b]);
+    const int up = gc_best == 0 ? bl : br, stay = gc_best == 0 ? br : bl;
+    // cur = (up, b'), b' = (a, stay)
+    t.left[b] = a;
+    t.right[b] = stay;
+    if (a >= 0) t.parent_int[a] = b; else t.parent_leaf[~a] = b;
+    if (up >= 0) t.parent_int[up] = cur; else t.parent_leaf[~up] = cur;
+    if (side_best == 0) t.right[cur] = up; else t.left[cur] = up;
+    float4 alo, ahi, slo, shi;
+    float acost, scost;
+    child_box(a, prim_lo, prim_hi, vals, t, alo, ahi, acost);
+    child_box(stay, prim_lo, prim_hi, vals, t, slo, shi, scost);
+    const float4 lo = make_float4(fminf(alo.x, slo.x), fminf(alo.y, slo.y), fminf(alo.z, slo.z), 0.0f);
+    const float4 hi = make_float4(fmaxf(ahi.x, shi.x), fmaxf(ahi.y, shi.y), fmaxf(ahi.z, shi.z), 0.0f);
+    t.nlo[b] = lo;
+    t.nhi[b] = hi;
+    t.ncost[b] = c_trav * box_area(lo, hi) + acost + scost;
+    __threadfence();
+}
+
 __global__ void __launch_bounds__(256) refit_kernel(const float4 *__restrict__ prim_lo, const float4 *__restrict__ prim_hi,
                                                     const uint32_t *__restrict__ vals, int n, uint32_t max_leaf,
-                                                    float SAH_C_TRAVERSE, BuildTmp t)
+                                                    float SAH_C_TRAVERSE, int rotate, BuildTmp t)
 {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
@@ -174,6 +281,7 @@ __global__ void __launch_bounds__(256) refit_kernel(const float4 *__restrict__ p
         __threadfence();
         if (atomicAdd(&t.arrive[cur], 1u) == 0u) return;      // the sibling subtree finishes this node
         __threadfence();
+        if (rotate) try_rotation(cur, prim_lo, prim_hi, vals, max_leaf * (uint32_t)rotate, SAH_C_TRAVERSE, t);
         const int lc = t.left[cur], rc = t.right[cur];
         float4 llo, lhi, rlo, rhi;
         float lcost, rcost;
@@ -281,6 +389,26 @@ float sah_c_traverse()
     return v;
 }
 
+// PTB200_ROTATE=0|1: tree rotations in the refit pass (A/B; profiles/r02_notes.md)
+bool morton_cubic()         // PTB200_MORTON=axis|cube (A/B)
+{
+    const char *e = std::getenv("PTB200_MORTON");
+    return e ? e[0] == 'c' : PTB_MORTON_CUBIC_DEFAULT;
+}
+
+int tree_rotations()        // number of refit passes that try rotations (0: none)
+{
+    const char *e = std::getenv("PTB200_ROTATE");
+    const int v = e ? std::atoi(e) : PTB_ROTATE_DEFAULT;
+    return v < 0 ? 0 : v > 16 ? 16 : v;
+}
+uint32_t rotate_min_factor()   // a child is rebuilt when it holds more than this many times max_leaf primitives
+{
+    const char *e = std::getenv("PTB200_ROTATE_MIN");
+    const int v = e ? std::atoi(e) : 1;
+    return (uint32_t)(v < 1 ? 1 : v);
+}
+
 template <typename T>
 cudaError_t dmalloc(T **p, size_t count)
 {
@@ -333,7 +461,7 @@ cudaError_t build_lbvh(const float4 *prim_lo, const float4 *prim_hi, uint32_t n,
 
     init_bounds_kernel<<<1, 32, 0, s>>>(cb);
     centroid_bounds_kernel<<<min(blocks_n, 148u * 8u), 256, 0, s>>>(prim_lo, prim_hi, n, cb);
-    morton_kernel<<<blocks_n, 256, 0, s>>>(prim_lo, prim_hi, n, cb, keys_a, vals_a);
+    morton_kernel<<<blocks_n, 256, 0, s>>>(prim_lo, prim_hi, n, cb, morton_cubic() ? 1 : 0, keys_a, vals_a);
     BK(cudaGetLastError());
 
     BK(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, keys_a, keys_b, vals_a, vals_b, (int)n, 0, 63, s));
@@ -370,7 +498,11 @@ cudaError_t build_lbvh(const float4 *prim_lo, const float4 *prim_hi, uint32_t n,
     BK(cudaMemsetAsync(t.arrive, 0, sizeof(uint32_t) * ni, s));
 
     karras_kernel<<<blocks_i, 256, 0, s>>>(keys_b, (int)n, t);
-    refit_kernel<<<blocks_n, 256, 0, s>>>(prim_lo, prim_hi, vals_b, (int)n, max_leaf, sah_c_traverse(), t);
+    refit_kernel<<<blocks_n, 256, 0, s>>>(prim_lo, prim_hi, vals_b, (int)n, max_leaf, sah_c_traverse(), tree_rotations() > 0 ? (int)rotate_min_factor() : 0, t);
+    for (int pass = 1; pass < tree_rotations(); ++pass) {      // further bottom-up passes over the rotated tree
+        BK(cudaMemsetAsync(t.arrive, 0, sizeof(uint32_t) * ni, s));
+        refit_kernel<<<blocks_n, 256, 0, s>>>(prim_lo, prim_hi, vals_b, (int)n, max_leaf, sah_c_traverse(), (int)rotate_min_factor(), t);
+    }
     survive_kernel<<<blocks_i, 256, 0, s>>>(ni, max_leaf, t);
     BK(cudaGetLastError());
     BK(cub::DeviceScan::ExclusiveSum(cub_tmp, scan_bytes, t.flags, t.compact, ni, s));
