@@ -25,7 +25,7 @@ c3|c4)
         python experiments/prof_scene.py $1 $PW > gpurun_out/r02_ncu_$1.log 2>&1 ;;
 peer)
     python experiments/prof_peer.py > gpurun_out/r02_plain_peer.log 2>&1 && PROF_PEER_DIRECT=1 python experiments/prof_peer.py >> gpurun_out/r02_plain_peer.log 2>&1 &&
-    PROF_PEER_DIRECT=1 ncu --set full --metrics nvlrx__bytes.sum,nvltx__bytes.sum --clock-control none -k regex:peer_merge -c 8 -f -o gpurun_out/r02_peer_merge \
+    PROF_PEER_DIRECT=1 ncu --set full --metrics nvlrx__bytes.sum,nvltx__bytes.sum --clock-control none -k regex:peer_merge -c 16 -f -o gpurun_out/r02_peer_merge_g$(nvidia-smi -L | wc -l) \
         python experiments/prof_peer.py > gpurun_out/r02_ncu_peer.log 2>&1 ;;
 esac
 echo "step $1 rc=$?"; tail -q -n 3 gpurun_out/r02_plain*.log gpurun_out/r02_ncu_*.log 2>/dev/null | tail -12

@@ -162,16 +162,19 @@ for wl, pw, pixels in (("c3", 4, 1920 * 1080), ("c4", 1, 3840 * 2160)):
             "source": f"profiles/r02_{wl}_bounce_ncu.txt"}
 
 # ---- fused peer merge ------------------------------------------------------------------------------------------------------
-ks = load("r02_peer_merge.ncu-rep")
-if ks:
-    write_kernels("r02_peer_merge_ncu.txt",
-                  "# ncu --set full --metrics nvlrx__bytes.sum,nvltx__bytes.sum --clock-control none -k regex:peer_merge -c 8\n"
-                  "#     python experiments/prof_peer.py   (ONE process, one context per GPU; 1920x1080, 64 spp per rank and frame)\n", ks)
+for G_ in (2, 8):
+    ks = load(f"r02_peer_merge_g{G_}.ncu-rep") or (load("r02_peer_merge.ncu-rep") if G_ == 2 else None)
+    if not ks:
+        continue
+    fn = "r02_peer_merge_ncu.txt" if G_ == 2 else f"r02_peer_merge_g{G_}_ncu.txt"
+    write_kernels(fn, "# ncu --set full --metrics nvlrx__bytes.sum,nvltx__bytes.sum --clock-control none -k regex:peer_merge\n"
+                      f"#     PROF_PEER_DIRECT=1 python experiments/prof_peer.py   (ONE process, {G_} GPUs, one context each; 1920x1080,\n"
+                      "#     64 spp per rank and frame; the merge kernel driven directly: ncu serialises launches, the rendezvous cannot run)\n", ks)
     d = ks[-1]
-    traffic["peer_merge_kernel"] = {"nvlink_rx_bytes_per_launch": val(d, "nvlrx__bytes.sum"), "nvlink_tx_bytes_per_launch": val(d, "nvltx__bytes.sum"),
-                                    "dram_read_bytes_per_launch": val(d, "dram__bytes_read.sum"),
-                                    "dram_write_bytes_per_launch": val(d, "dram__bytes_write.sum"),
-                                    "us_under_ncu": val(d, "gpu__time_duration.sum"), "source": "profiles/r02_peer_merge_ncu.txt"}
+    traffic["peer_merge_kernel" if G_ == 2 else f"peer_merge_kernel:g{G_}"] = {
+        "nvlink_rx_bytes_per_launch": val(d, "nvlrx__bytes.sum"), "nvlink_tx_bytes_per_launch": val(d, "nvltx__bytes.sum"),
+        "dram_read_bytes_per_launch": val(d, "dram__bytes_read.sum"), "dram_write_bytes_per_launch": val(d, "dram__bytes_write.sum"),
+        "us_under_ncu": val(d, "gpu__time_duration.sum"), "n_gpus": G_, "source": "profiles/" + fn}
 
 json.dump(traffic, open(os.path.join(P, "traffic.json"), "w"), indent=1)
 print("wrote", sorted(k for k in traffic if not k.startswith("_")))
