@@ -269,6 +269,19 @@ int ptb_scene_read_bvh(ptb_context *ctx, int which, void *nodes_out, uint32_t ca
  * (out_prim = 1/0, out_t may be NULL). */
 int ptb_trace_rays(ptb_context *ctx, uint64_t n_rays, const float *origins, const float *dirs, float t_min,
                    float t_max, int mode, int32_t *out_prim, float *out_t);
+/* ptb_trace_rays for callers that may not allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments, results and errors as ptb_trace_rays, but the device staging of the ray and result arrays
+ * (32 bytes per ray) lives in a static device array of the library (PTB_TRACE_RAYS_STATIC_MAX x 32 B = 2 MiB, held by
+ * every GPU that loads the library until the process exits) instead of four cudaMalloc'ed buffers: the call makes no
+ * cudaMalloc / cudaFree and calls no allocating library routine.  n_rays > PTB_TRACE_RAYS_STATIC_MAX is
+ * PTB_ERR_UNSUPPORTED (nothing is launched; split the batch or use ptb_trace_rays).
+ * All calls on one GPU share the array, which keeps the previous call's contents: the result part is cleared on
+ * the stream before each launch, and the call returns only after its results have been copied out, but two calls
+ * that overlap on one GPU (two contexts of that device driven from two host threads) race — serialise them. */
+#define PTB_TRACE_RAYS_STATIC_MAX 65536u
+int ptb_trace_rays_static(ptb_context *ctx, uint64_t n_rays, const float *origins, const float *dirs, float t_min,
+                          float t_max, int mode, int32_t *out_prim, float *out_t);
 
 /* ---- fused multi-GPU merge over NVLink peer memory (north_star stage n8; no reference counterpart) -------------
  * With sample-range sharding every GPU holds a partial accumulation buffer of the whole frame.  ptb_peer_merge, called

@@ -163,6 +163,8 @@ SIGNATURES = {
                                      _P(C.c_uint32)]),
     "ptb_trace_rays": (C.c_int, [_CTX, C.c_uint64, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_int, C.c_void_p,
                                  C.c_void_p]),
+    "ptb_trace_rays_static": (C.c_int, [_CTX, C.c_uint64, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_int, C.c_void_p,
+                                        C.c_void_p]),
     "ptb_accum_clear": (C.c_int, [_CTX]),
     "ptb_device_peer_flags": (C.c_void_p, [_CTX]),
     "ptb_peer_barrier": (C.c_int, [_CTX, C.c_uint32, _P(C.c_void_p), C.c_uint32, C.c_uint32, C.c_uint32]),

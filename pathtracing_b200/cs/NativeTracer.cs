@@ -83,6 +83,8 @@ public sealed unsafe class NativeTracer : IDisposable
     [DllImport(Lib)] private static extern int ptb_scene_set_sun(IntPtr ctx, float[] dirToLight, float[] radiance);
     [DllImport(Lib)] private static extern int ptb_trace_rays(IntPtr ctx, ulong nRays, float* origins, float* dirs, float tMin,
                                                               float tMax, int mode, int* outPrim, float* outT);
+    [DllImport(Lib)] private static extern int ptb_trace_rays_static(IntPtr ctx, ulong nRays, float* origins, float* dirs, float tMin,
+                                                                     float tMax, int mode, int* outPrim, float* outT);
 
     // ---- multi-GPU: row shards, external accumulation buffers, fused merge over NVLink peer memory
     [DllImport(Lib)] private static extern int ptb_set_row_shard_bands(IntPtr ctx, uint rowOffset, uint rowStride, uint rowsPerBand);
@@ -213,6 +215,16 @@ public sealed unsafe class NativeTracer : IDisposable
         fixed (float* o = origins, d = dirs, tt = t)
         fixed (int* pp = prim)
             Check(_ctx, ptb_trace_rays(_ctx, (ulong)prim.Length, o, d, tMin, tMax, anyHit ? 1 : 0, pp, anyHit ? null : tt));
+    }
+
+    /// ptb_trace_rays_static: same results with the device staging in the library's static array (no device allocation in the
+    /// call); at most 65,536 rays (PTB_TRACE_RAYS_STATIC_MAX), calls on one GPU must not overlap.
+    public void TraceRaysStatic(ReadOnlySpan<float> origins, ReadOnlySpan<float> dirs, float tMin, float tMax, bool anyHit,
+                                Span<int> prim, Span<float> t)
+    {
+        fixed (float* o = origins, d = dirs, tt = t)
+        fixed (int* pp = prim)
+            Check(_ctx, ptb_trace_rays_static(_ctx, (ulong)prim.Length, o, d, tMin, tMax, anyHit ? 1 : 0, pp, anyHit ? null : tt));
     }
 
     public void SetRowShard(uint rowOffset, uint rowStride, uint rowsPerBand = 1) =>

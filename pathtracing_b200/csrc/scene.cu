@@ -9,10 +9,19 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 
 #include "ptb_internal.h"
 #include "scene.cuh"
+
+// ---- ptb_trace_rays_static: staging that is never allocated --------------------------------------------------------
+// 32 B per ray: origins (12 B) | directions (12 B) | primitive ids (4 B) | distances (4 B), each part sized for the
+// maximum batch so that every part starts on a 256 B boundary.  The array's name is a host-side stand-in in host code,
+// not a device address: trace_static_scratch() asks the runtime for the address, once per device with that device
+// current, and only that pointer is handed to the kernel.
+#define PTB_TRACE_STATIC_BYTES ((size_t)PTB_TRACE_RAYS_STATIC_MAX * 32u)
+static __device__ __align__(256) unsigned char g_trace_static_scratch[PTB_TRACE_STATIC_BYTES];
 
 namespace {
 
@@ -128,6 +137,27 @@ int check_error_flag(ptb_context *ctx, SceneState *st)
         snprintf(msg, sizeof msg, "scene kernels: bounds check failed, flags 0x%x (see PTB_CHK in kernels_scene.cu)", flag);
         return ptb::fail_msg(ctx, PTB_ERR_CUDA, msg);
     }
+    return PTB_OK;
+}
+
+// Device address of g_trace_static_scratch on the context's device (which is current): looked up once per device.
+constexpr int MAX_STATIC_DEVICES = 64;
+unsigned char *g_trace_static_addr[MAX_STATIC_DEVICES] = {};
+std::mutex g_trace_static_mutex;
+
+int trace_static_scratch(ptb_context *ctx, unsigned char **out)
+{
+    const int dev = ctx->cfg.device;
+    if (dev < 0 || dev >= MAX_STATIC_DEVICES)
+        return ptb::fail_msg(ctx, PTB_ERR_UNSUPPORTED, "ptb_trace_rays_static: device index beyond the address table");
+    std::lock_guard<std::mutex> lock(g_trace_static_mutex);
+    if (!g_trace_static_addr[dev]) {
+        void *p = nullptr;
+        SC_CUDA(ctx, cudaGetSymbolAddress(&p, g_trace_static_scratch));
+        if (!p) return ptb::fail_msg(ctx, PTB_ERR_CUDA, "ptb_trace_rays_static: cudaGetSymbolAddress returned NULL");
+        g_trace_static_addr[dev] = static_cast<unsigned char *>(p);
+    }
+    *out = g_trace_static_addr[dev];
     return PTB_OK;
 }
 
@@ -501,6 +531,47 @@ int ptb_trace_rays(ptb_context *ctx, uint64_t n, const float *origins, const flo
     if (e != cudaSuccess) return ptb::fail_cuda(ctx, e, "ptb_trace_rays");
     rc = check_error_flag(ctx, st);
     return rc;
+}
+
+int ptb_trace_rays_static(ptb_context *ctx, uint64_t n, const float *origins, const float *dirs, float t_min, float t_max, int mode,
+                          int32_t *out_prim, float *out_t)
+{
+    if (!ctx) return ptb::fail_msg(nullptr, PTB_ERR_INVALID, "ptb_trace_rays_static: ctx is NULL");
+    if (!ctx->scene) return ptb::fail_msg(ctx, PTB_ERR_STATE, "ptb_trace_rays_static: no scene resident");
+    if (mode < 0 || mode > 1) return ptb::fail_msg(ctx, PTB_ERR_INVALID, "ptb_trace_rays_static: mode must be 0 (closest) or 1 (any)");
+    if (n == 0) return PTB_OK;
+    if (!origins || !dirs || !out_prim) return ptb::fail_msg(ctx, PTB_ERR_INVALID, "ptb_trace_rays_static: NULL array");
+    if (n > PTB_TRACE_RAYS_STATIC_MAX) {
+        char msg[160];
+        snprintf(msg, sizeof msg, "ptb_trace_rays_static: %llu rays exceed PTB_TRACE_RAYS_STATIC_MAX = %u (the static staging "
+                 "array); split the batch or use ptb_trace_rays", (unsigned long long)n, PTB_TRACE_RAYS_STATIC_MAX);
+        return ptb::fail_msg(ctx, PTB_ERR_UNSUPPORTED, msg);
+    }
+    if (!(t_min >= 0.0f) || !(t_max >= t_min))
+        return ptb::fail_msg(ctx, PTB_ERR_INVALID, "ptb_trace_rays_static: need 0 <= t_min <= t_max (the conservative culling "
+                             "interval is widened relative to non-negative distances)");
+    SC_CUDA(ctx, cudaSetDevice(ctx->cfg.device));
+    unsigned char *base = nullptr;
+    const int rc = trace_static_scratch(ctx, &base);
+    if (rc != PTB_OK) return rc;
+    SceneState *st = state(ctx);
+    const size_t cap = PTB_TRACE_RAYS_STATIC_MAX;
+    float *d_o = reinterpret_cast<float *>(base);
+    float *d_d = reinterpret_cast<float *>(base + cap * 12);
+    int32_t *d_p = reinterpret_cast<int32_t *>(base + cap * 24);
+    float *d_t = reinterpret_cast<float *>(base + cap * 28);
+    // the array keeps what the last call left: the results start from zero, the ray parts are overwritten up to n
+    SC_CUDA(ctx, cudaMemsetAsync(d_p, 0, n * 4, ctx->stream));
+    SC_CUDA(ctx, cudaMemsetAsync(d_t, 0, n * 4, ctx->stream));
+    SC_CUDA(ctx, cudaMemcpyAsync(d_o, origins, n * 12, cudaMemcpyHostToDevice, ctx->stream));
+    SC_CUDA(ctx, cudaMemcpyAsync(d_d, dirs, n * 12, cudaMemcpyHostToDevice, ctx->stream));
+    const ptb::SceneK k = make_k(ctx, st);
+    SC_CUDA(ctx, ptb::launch_trace_rays(k, st, n, d_o, d_d, t_min, t_max, mode, d_p, d_t, ctx->stream));
+    ctx->launches += 1;
+    SC_CUDA(ctx, cudaMemcpyAsync(out_prim, d_p, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_t && mode == 0) SC_CUDA(ctx, cudaMemcpyAsync(out_t, d_t, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    SC_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return check_error_flag(ctx, st);
 }
 
 }  // extern "C"

@@ -235,6 +235,20 @@ class NativeTracer:
                                           1 if any_hit else 0, prim.ctypes.data, t.ctypes.data))
         return (prim, None) if any_hit else (prim, t)
 
+    TRACE_RAYS_STATIC_MAX = 65536      # PTB_TRACE_RAYS_STATIC_MAX (include/ptb200.h)
+
+    def trace_rays_static(self, origins: np.ndarray, dirs: np.ndarray, t_min: float, t_max: float, any_hit: bool = False):
+        """trace_rays through ptb_trace_rays_static: same results, device staging in the library's static array (no
+        device allocation in the call); at most TRACE_RAYS_STATIC_MAX rays, calls on one GPU must not overlap."""
+        o = np.ascontiguousarray(origins, np.float32).reshape(-1, 3)
+        d = np.ascontiguousarray(dirs, np.float32).reshape(-1, 3)
+        assert o.shape == d.shape
+        prim = np.empty(len(o), np.int32)
+        t = np.zeros(len(o), np.float32)
+        self._ck(self._lib.ptb_trace_rays_static(self._ctx, len(o), o.ctypes.data, d.ctypes.data, t_min, t_max,
+                                                 1 if any_hit else 0, prim.ctypes.data, t.ctypes.data))
+        return (prim, None) if any_hit else (prim, t)
+
     # -- fused multi-GPU merge over peer memory ---------------------------------------------------
     def device_peer_flags(self) -> int:
         return int(self._lib.ptb_device_peer_flags(self._ctx) or 0)
