@@ -152,7 +152,7 @@ __device__ __forceinline__ bool hit_triangle(const float4 v0, const float4 e1, c
 }
 
 // Conservative slab test of one child box against [t_min, t_far].  FMA_SLAB: t = fma(plane, 1/d, -o/d)
-// (6 FFMA per box; its cancellation error is at most half an ulp of the ray origin in space, covered
+// (3 FFMA2 per box; its cancellation error is at most half an ulp of the ray origin in space, covered
 // by the 2^-18-of-scene-extent padding the boxes get at build time, which includes the camera);
 // otherwise t = (plane - o) * (1/d) for rays whose origin may lie far outside the scene
 // (ptb_trace_rays).  The interval is widened by 2^-19 of |t| (approximate reciprocal + 3 roundings),
@@ -163,9 +163,12 @@ __device__ __forceinline__ bool slab(float lox, float hix, float loy, float hiy,
 {
     float ax, bx, ay, by, az, bz;
     if (FMA_SLAB) {
-        ax = fmaf(lox, r.ix, r.px); bx = fmaf(hix, r.ix, r.px);
-        ay = fmaf(loy, r.iy, r.py); by = fmaf(hiy, r.iy, r.py);
-        az = fmaf(loz, r.iz, r.pz); bz = fmaf(hiz, r.iz, r.pz);
+        // both planes of an axis in one FFMA2 (two IEEE-rounded lanes per issue slot; the node's 16 B loads deliver the pair
+        // in adjacent registers and the ray's constants are broadcast operands): 6 instructions instead of 12, same values
+        const float2 tx = __ffma2_rn(make_float2(lox, hix), make_float2(r.ix, r.ix), make_float2(r.px, r.px));
+        const float2 ty = __ffma2_rn(make_float2(loy, hiy), make_float2(r.iy, r.iy), make_float2(r.py, r.py));
+        const float2 tz = __ffma2_rn(make_float2(loz, hiz), make_float2(r.iz, r.iz), make_float2(r.pz, r.pz));
+        ax = tx.x; bx = tx.y; ay = ty.x; by = ty.y; az = tz.x; bz = tz.y;
     } else {
         ax = (lox - r.ox) * r.ix; bx = (hix - r.ox) * r.ix;
         ay = (loy - r.oy) * r.iy; by = (hiy - r.oy) * r.iy;
@@ -766,9 +769,10 @@ struct WalkRay {
 __device__ __forceinline__ bool slab_walk(float lox, float hix, float loy, float hiy, float loz, float hiz, const WalkRay &r,
                                           float t_min, float t_far, float &t_near)
 {
-    const float ax = fmaf(lox, r.ix, r.px), bx = fmaf(hix, r.ix, r.px);
-    const float ay = fmaf(loy, r.iy, r.py), by = fmaf(hiy, r.iy, r.py);
-    const float az = fmaf(loz, r.iz, r.pz), bz = fmaf(hiz, r.iz, r.pz);
+    const float2 tx = __ffma2_rn(make_float2(lox, hix), make_float2(r.ix, r.ix), make_float2(r.px, r.px));   // see slab<>
+    const float2 ty = __ffma2_rn(make_float2(loy, hiy), make_float2(r.iy, r.iy), make_float2(r.py, r.py));
+    const float2 tz = __ffma2_rn(make_float2(loz, hiz), make_float2(r.iz, r.iz), make_float2(r.pz, r.pz));
+    const float ax = tx.x, bx = tx.y, ay = ty.x, by = ty.y, az = tz.x, bz = tz.y;
     t_near = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), t_min));
     const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), t_far));
     return t_near <= fmaf(fabsf(tf), 1.9073486e-6f, tf);     // widened away from zero whatever the sign of tf
