@@ -89,6 +89,23 @@ __device__ __forceinline__ float rcp_approx(float x)
     return r;
 }
 
+// One 64 B node in two 256-bit loads (sm_100 LDG.256) instead of four 128-bit ones.  The lanes of a warp read different
+// nodes, and the L1 data pipe spends one wavefront per lane and load instruction whatever its width: with 7-14 lanes active
+// the walk was as close to the limit of that pipe (76 % of peak on the 1 M-triangle scene) as to its issue slots.
+__device__ __forceinline__ void load_node(const BvhNode *__restrict__ n, float4 &a, float4 &b, float4 &c, int2 &d)
+{
+#ifndef PTB_NODE_LDG128
+    float d2, d3;
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(n));
+    asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(c.x), "=f"(c.y), "=f"(c.z), "=f"(c.w), "=r"(d.x), "=r"(d.y), "=f"(d2), "=f"(d3) : "l"(&n->c));
+#else
+    a = __ldg(&n->a); b = __ldg(&n->b); c = __ldg(&n->c);
+    d = __ldg(reinterpret_cast<const int2 *>(&n->d));
+#endif
+}
+
 __device__ __forceinline__ void make_ray(RayT &r, float ox, float oy, float oz, float dx, float dy, float dz)
 {
     r.ox = ox; r.oy = oy; r.oz = oz;
@@ -261,8 +278,9 @@ __device__ __forceinline__ bool traverse(const SceneK &k, const RayT &r, float t
     for (;;) {
         while (cur >= 0) {
             PTB_CHK(error_flag, (uint32_t)cur < (CLS == 0 ? k.n_sph_nodes : k.n_tri_nodes), CHK_NODE);
-            const float4 na = __ldg(&nodes[cur].a), nb = __ldg(&nodes[cur].b), nc = __ldg(&nodes[cur].c);
-            const int4 nd = __ldg(&nodes[cur].d);
+            float4 na, nb, nc;
+            int2 nd;
+            load_node(&nodes[cur], na, nb, nc, nd);
             if (STATS) ++cn.nodes;
             const float t_far = ANY ? t_max : best.t_cull;
             float tn0, tn1;
@@ -933,8 +951,9 @@ __global__ void __launch_bounds__(256, PTB_QUEUE_MIN_BLOCKS) bounce_kernel(const
             if (cur >= 0) {
                 const BvhNode *__restrict__ nodes = cls == 0 ? k.sph_nodes : k.tri_nodes;
                 PTB_CHK(w.error_flag, (uint32_t)cur < (cls == 0 ? k.n_sph_nodes : k.n_tri_nodes), CHK_NODE);
-                const float4 na = __ldg(&nodes[cur].a), nb = __ldg(&nodes[cur].b), nc = __ldg(&nodes[cur].c);
-                const int2 nd = __ldg((const int2 *)&nodes[cur].d);
+                float4 na, nb, nc;
+                int2 nd;
+                load_node(&nodes[cur], na, nb, nc, nd);
                 if (STATS) ++cn.nodes;
                 float tn0, tn1;
                 const bool h0 = slab_walk(na.x, na.y, na.z, na.w, nc.x, nc.y, r, k.t_min, t_cull, tn0);
