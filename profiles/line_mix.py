@@ -1,9 +1,10 @@
 #!/usr/bin/env python
 """Per-source-line executed warp-instructions and active threads from an .ncu-rep (needs -lineinfo + --import-source on).
-Usage: python profiles/line_mix.py report.ncu-rep [top]"""
+Usage: python profiles/line_mix.py report.ncu-rep [top [launch-skip]]   (one launch: the one after `launch-skip` others)"""
 import collections, csv, io, subprocess, sys
 rep = sys.argv[1]; top = int(sys.argv[2]) if len(sys.argv) > 2 else 40
-out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "sass,cuda"], capture_output=True, text=True).stdout
+sel = ["--launch-skip", sys.argv[3], "--launch-count", "1"] if len(sys.argv) > 3 else []
+out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "sass,cuda"] + sel, capture_output=True, text=True).stdout
 lines = out.split("\n")
 start = next(i for i, l in enumerate(lines) if l.startswith('"Line No"'))
 rows = list(csv.reader(io.StringIO("\n".join(lines[start:]))))
