@@ -3,6 +3,7 @@
 // Shared by scene.cu (C-ABI glue), scene_build.cu (GPU LBVH build) and kernels_scene.cu (wavefront
 // path tracer).  Not part of the public ABI.
 #pragma once
+#include <cstddef>
 #include <cstdint>
 #include <cuda_runtime.h>
 
@@ -11,7 +12,7 @@
 
 namespace ptb {
 
-// 64-byte two-child node, four 16 B vector loads:
+// 64-byte two-child node (fetched as two 256-bit loads):
 //   a = (c0.lo.x, c0.hi.x, c0.lo.y, c0.hi.y)
 //   b = (c1.lo.x, c1.hi.x, c1.lo.y, c1.hi.y)
 //   c = (c0.lo.z, c0.hi.z, c1.lo.z, c1.hi.z)
@@ -23,6 +24,9 @@ struct __align__(16) BvhNode {
     int4 d;
 };
 static_assert(sizeof(BvhNode) == 64, "node must be 64 bytes");
+// kernels_scene.cu load_node() reads a node as two 32 B-aligned 256-bit loads (a|b, c|d): node arrays come from cudaMalloc
+// (256 B aligned) and are indexed in whole nodes
+static_assert(offsetof(BvhNode, c) == 32, "second half of a node must start at byte 32");
 
 constexpr uint32_t LEAF_FIRST_MASK = 0x07FFFFFFu;
 constexpr int LEAF_COUNT_SHIFT = 27;
