@@ -52,6 +52,7 @@ for name, sc, depth in (("mixed", scenes.mixed_small(width=w, height=h), 6),
         rng = np.random.Generator(np.random.PCG64(2))
         o = rng.uniform(-4, 4, (3000, 3)).astype(np.float32); d = rng.normal(size=(3000, 3)).astype(np.float32)
         t.trace_rays(o, d, 1e-3, 1e30); t.trace_rays(o, d, 1e-3, 5.0, any_hit=True)
+        t.trace_rays_static(o, d, 1e-3, 1e30); t.trace_rays_static(o, d, 1e-3, 5.0, any_hit=True)   # static device staging
         t.read_bvh(0); t.read_bvh(1); t.scene_queue_sizes()
         print(name, "ok", t.scene_info()["triangle_nodes"], flush=True)
 
