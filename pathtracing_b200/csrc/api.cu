@@ -356,11 +356,14 @@ int ptb_read_rgba8_async(ptb_context *ctx, void *host_dst, size_t pitch_bytes)
     // engine sustains ~40 GB/s device-to-host on these hosts, which made the 8.3 MB frame of a 1080p step (205 us) the
     // bottleneck of the multi-GPU end-to-end loop; 2 / 4 bands: 179 / 175 us per step next to a 172 us render
     // (experiments/peer_timing.py; PTB200_COPY_SPLIT = 1..4 for A/B runs).  Small images stay on one stream.
-    static const int split = [] {
+    // A context on its own keeps ONE stream: there the copy overlaps the next frame and only its throughput counts — one
+    // stream 50.8 GB/s (e2e 812 k Msamples/s on c2), 4 bands 49.4 GB/s (790 k): the bands only add per-copy overheads.
+    static const int split_env = [] {
         const char *e = std::getenv("PTB200_COPY_SPLIT");
-        const int v = e ? std::atoi(e) : 4;
-        return v >= 1 && v <= 4 ? v : 4;
+        const int v = e ? std::atoi(e) : 0;
+        return v >= 1 && v <= 4 ? v : 0;
     }();
+    const int split = split_env ? split_env : (pg && pg->bound ? 4 : 1);
     const uint32_t H = ctx->cfg.height;
     const int parts = (row * H >= (1u << 20)) ? (int)std::min<uint32_t>((uint32_t)split, H) : 1;
     if (parts > 1) {
