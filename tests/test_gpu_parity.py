@@ -394,6 +394,36 @@ def test_async_readback_is_ordered_and_matches_sync(oracle):
     assert np.array_equal(sync, bufs[2])
 
 
+@pytest.mark.parametrize("split", ["1", "3", "4"])
+def test_banded_async_readback_equals_the_plain_read(split):
+    """ptb_read_rgba8_async in 1 / 3 / 4 row bands on as many copy streams (PTB200_COPY_SPLIT; the default is one stream for
+    a context on its own and four bands in a bound peer group).  The variable is read once per process, hence a child."""
+    import os, subprocess, sys
+    code = (
+        "import numpy as np\n"
+        "from pathtracing_b200 import NativeTracer\n"
+        "w, h = 1920, 1080\n"
+        "with NativeTracer(w, h, seed=3) as t:\n"
+        "    frames, bufs = [], [np.zeros((h, w, 4), np.uint8) for _ in range(3)]\n"
+        "    for i, buf in enumerate(bufs):\n"
+        "        t.render_resolve(5 * i, 5)\n"
+        "        t.read_rgba8_async(buf.ctypes.data)\n"
+        "        if i == 1: t.wait(); frames.append(t.read_rgba8())\n"
+        "    t.wait()\n"
+        "    last = t.read_rgba8()\n"
+        "    assert np.array_equal(bufs[1], frames[0]) and np.array_equal(bufs[2], last)\n"
+        "    assert not np.array_equal(bufs[0], bufs[2])\n"
+        "    pitch = w * 4 + 64\n"
+        "    c = np.zeros((h, pitch), np.uint8)\n"
+        "    t.read_rgba8_async(c.ctypes.data, pitch); t.wait()\n"
+        "    assert np.array_equal(c[:, :w * 4].reshape(h, w, 4), last) and not c[:, w * 4:].any()\n"
+        "print('banded ok')\n")
+    env = dict(os.environ, PTB200_COPY_SPLIT=split)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "banded ok" in r.stdout, r.stdout + r.stderr
+
+
 @pytest.mark.parametrize("size", [(640, 360), (333, 77), (1920, 1080)])
 @pytest.mark.parametrize("jitter", [True, False])
 def test_fused_render_resolve_equals_the_two_calls(oracle, size, jitter):
