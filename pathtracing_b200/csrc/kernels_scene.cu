@@ -251,7 +251,7 @@ __device__ __noinline__ int *short_stack_base()
 }
 #endif
 
-template <int CLS, bool ANY, bool STATS, bool FMA_SLAB>
+template <int CLS, bool ANY, bool STATS, bool FMA_SLAB, bool BRANCH_FREE = false>
 __device__ __forceinline__ bool traverse(const SceneK &k, const RayT &r, float t_min, float t_max, bool active, Best &best,
                                          Counters &cn, uint32_t *error_flag)
 {
@@ -260,9 +260,59 @@ __device__ __forceinline__ bool traverse(const SceneK &k, const RayT &r, float t
     if (root == EMPTY_REF) return false;               // launch-uniform
     int cur = active ? root : EMPTY_REF;               // node (>= 0), leaf (< 0) or EMPTY_REF = finished
     int stack[STACK_N];
-    int sp = 0;
     uint32_t prims = 0;
     bool found = false;
+    if (BRANCH_FREE) {
+        // Branch-free node step, for walks whose lanes disagree about the outcome of most steps (scattered rays in a
+        // hierarchy of overlapping boxes: the sphere class behind the camera rays).  stack[0] is a sentinel — popping it
+        // ends the walk, so a pop needs no emptiness test —, a push is one predicated store, a pop one predicated load,
+        // and the three outcomes of a step (both children hit / one / none) are selects instead of three branches that a
+        // divergent warp runs one after the other: 18 instructions behind the box decision for everybody, against 4 / 8 / 9
+        // per outcome PRESENT in the warp.  Measured (profiles/r02_notes.md section 12): c3 +11 % with every launch on the
+        // chunk schedule, but the coherent camera rays and the well-separated boxes of the terrain mostly see one outcome
+        // per step and lose (c4 -17 %), hence the template switch.  The stack position is clamped to the last slot
+        // (memory-safe); a walk that reached it is reported behind the loop, one level early.
+        stack[0] = EMPTY_REF;
+        int sp = 1, max_sp = 1;                        // sp: next free slot
+        for (;;) {
+            while (cur >= 0) {
+                PTB_CHK(error_flag, (uint32_t)cur < (CLS == 0 ? k.n_sph_nodes : k.n_tri_nodes), CHK_NODE);
+                float4 na, nb, nc;
+                int2 nd;
+                load_node(&nodes[cur], na, nb, nc, nd);
+                if (STATS) ++cn.nodes;
+                const float t_far = ANY ? t_max : best.t_cull;
+                float tn0, tn1;
+                const bool h0 = slab<FMA_SLAB>(na.x, na.y, na.z, na.w, nc.x, nc.y, r, t_min, t_far, tn0);
+                const bool h1 = slab<FMA_SLAB>(nb.x, nb.y, nb.z, nb.w, nc.z, nc.w, r, t_min, t_far, tn1) && nd.y != EMPTY_REF;
+                const bool both = h0 && h1, none = !(h0 || h1);
+                const bool second_first = both ? tn1 < tn0 : !h0;      // descend into child 1 (both hit: the nearer one)
+                int nxt = second_first ? nd.y : nd.x;
+                const int other = second_first ? nd.x : nd.y;
+                if (both) stack[sp] = other;
+                if (both) ++sp;
+                sp = min(sp, STACK_N - 1);
+                max_sp = max(max_sp, sp);
+                if (none) --sp;
+                if (none) nxt = stack[sp];
+                cur = nxt;
+            }
+            if (cur == EMPTY_REF) break;
+            if (test_leaf<CLS, ANY>(k, cur, r, t_min, t_max, best, prims, error_flag)) {
+                found = true;
+                break;
+            }
+            --sp;
+            cur = stack[sp];
+        }
+        if (max_sp >= STACK_N - 1) atomicOr(error_flag, 1u);
+        if (STATS) {
+            cn.max_stack = max(cn.max_stack, (uint32_t)(max_sp - 1));
+            cn.prims += prims;
+        }
+        return ANY ? found : best.id >= 0;
+    }
+    int sp = 0;
 
     // A/B build (-DPTB_CHUNK_SMEM_STACK=N, experiments/build_variant.sh): the first N stack levels in shared memory, one
     // 4-byte column per thread ([level][thread]: conflict-free whatever the lanes' depths), deeper levels in local memory
@@ -318,7 +368,8 @@ __device__ __forceinline__ bool traverse(const SceneK &k, const RayT &r, float t
 }
 
 // closest hit over both hierarchies (active = false for lanes without a ray)
-template <bool STATS, bool FMA_SLAB>
+// SECONDARY: the rays are scattered ones (not camera rays): the sphere class then walks with the branch-free node step
+template <bool STATS, bool FMA_SLAB, bool SECONDARY = false>
 __device__ __forceinline__ bool closest_hit(const SceneK &k, const RayT &r, float t_min, float t_max, bool active, Best &best,
                                             Counters &cn, uint32_t *error_flag)
 {
@@ -327,7 +378,7 @@ __device__ __forceinline__ bool closest_hit(const SceneK &k, const RayT &r, floa
     best.id = -1;
     best.pos = 0;
     best.cls = 0;
-    traverse<0, false, STATS, FMA_SLAB>(k, r, t_min, t_max, active, best, cn, error_flag);
+    traverse<0, false, STATS, FMA_SLAB, SECONDARY>(k, r, t_min, t_max, active, best, cn, error_flag);
     traverse<1, false, STATS, FMA_SLAB>(k, r, t_min, t_max, active, best, cn, error_flag);
     return best.id >= 0;
 }
@@ -615,7 +666,7 @@ __global__ void __launch_bounds__(256, PTB_BOUNCE_MIN_BLOCKS) bounce_kernel_chun
         RayT r;
         make_ray(r, ox, oy, oz, dx, dy, dz);
         Best best;
-        const bool hit = closest_hit<STATS, true>(k, r, k.t_min, __int_as_float(0x7F800000) /* +inf */, alive, best, cn, w.error_flag);
+        const bool hit = closest_hit<STATS, true, !DEPTH0>(k, r, k.t_min, __int_as_float(0x7F800000) /* +inf */, alive, best, cn, w.error_flag);
         __syncwarp();
         const bool shaded = alive;
         bool need_shadow = false;                  // sun: this hit's direct light is added if the shadow ray finds nothing
@@ -1322,23 +1373,30 @@ cudaError_t launch_scene_wave(const SceneK &k, SceneState *st, float4 *accum, in
     const bool use_slices = batch > 1u || k.sun_on;
     if (use_slices && !st->slices) return cudaErrorInvalidValue;
     // bounces >= tail_depth run inside ONE launch (0 disables): queues that deep are too small to fill the GPU.  With the
-    // queue schedule in the tail launch (default) the tail starts at bounce 3 (c3: 2, 3, 4, 6 -> 4,147 / 4,149 / 4,128 / 4,061
-    // Msamples/s); with the chunk schedule there, at 4, or 6 for big batched waves (>= 8 Mi camera rays), whose queues stay
-    // large two bounces longer.  PTB200_TAIL_DEPTH overrides for A/B runs.
+    // queue schedule in the tail launch the tail starts at bounce 3 (c4: 3, 4, 5, 6 -> 1,433 / 1,422 / 1,415 / 1,412
+    // Msamples/s); with the chunk schedule there, see below.  PTB200_TAIL_DEPTH overrides for A/B runs.
     const char *e_tail = std::getenv("PTB200_TAIL_DEPTH");
     const int tail_env = e_tail ? std::atoi(e_tail) : -1;
     // A/B switches for profiling runs: PTB200_BOUNCE=chunk selects the 32-paths-per-warp schedule, PTB200_REFILL the number
     // of walking lanes below which a warp pauses to shade and refetch (0: never).
     const char *e_bounce = std::getenv("PTB200_BOUNCE"), *e_refill = std::getenv("PTB200_REFILL");
     // PTB200_BOUNCE: "chunk" = every launch with the chunk schedule, "queue" = bounces >= 1 with the queue schedule,
-    // "tail" = only the tail launch with the queue schedule
-    // (the default: it wins there — a path that scatters stays in its lane — and loses 1-5 % on the big early bounces,
-    // where its node step costs 2.4x the instructions of the chunk schedule's for 1.5-2x the active lanes; profiles/r02_notes.md)
-    const bool q_all = e_bounce && e_bounce[0] == 'q', q_tail = !e_bounce || q_all || e_bounce[0] == 't';
+    // "tail" = only the tail launch with the queue schedule (there a path that scatters stays in its lane; on the big
+    // early bounces its node step costs twice the instructions of the chunk schedule's for 1.5-2x the active lanes;
+    // profiles/r02_notes.md)
+    // Unset: by scene.  With triangles, the tail launch runs the queue schedule (c4 1,433 against 1,407-1,413 Msamples/s with
+    // chunks everywhere).  A scene of spheres only stays on the chunk schedule throughout: since the sphere class walks its
+    // scattered rays with the branch-free node step (traverse<>), chunks beat the queue-schedule tail at every wave size
+    // (c3, 1 / 2 / 4 / 8 / 32 samples per wave: 3,594 / 4,048 / 4,364 / 4,565 / 4,686 against 3,281 / 3,763 / 4,159 / 4,377 / 4,511).
+    const bool spheres_only = k.n_tris == 0u;
+    const bool q_all = e_bounce && e_bounce[0] == 'q';
+    const bool q_tail = e_bounce ? (q_all || e_bounce[0] == 't') : !spheres_only;
     const bool chunk_d0 = !std::getenv("PTB200_D0_QUEUE");
     const int refill_i = e_refill ? std::atoi(e_refill) : PTB_REFILL_DEFAULT;
     const uint32_t refill = (uint32_t)(refill_i < 0 ? 0 : refill_i > 32 ? 32 : refill_i);
-    const uint32_t tail_depth = tail_env >= 0 ? (uint32_t)tail_env : (q_tail ? 3u : ((uint64_t)n0_pixels * batch >= (8u << 20) ? 6u : 4u));
+    // chunk-schedule tail: from bounce 6, or 8 for waves of >= 16 Mi camera rays, whose queues stay large to the end
+    // (c3, tail from 4 / 6 / never: 1 sample per wave 3,598 / 3,594 / 3,471, 8 per wave 4,523 (6) / 4,565 (never))
+    const uint32_t tail_depth = tail_env >= 0 ? (uint32_t)tail_env : (q_tail ? 3u : ((uint64_t)n0_pixels * batch >= (16u << 20) ? 8u : 6u));
     // counters: [0, depths] queue sizes, [depths+1, 2*depths+1] work cursors
     cudaError_t e = cudaMemsetAsync(st->counts, 0, sizeof(uint32_t) * st->counts_len, s);
     if (e != cudaSuccess) return e;
