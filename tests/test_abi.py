@@ -47,6 +47,22 @@ def test_csharp_binding_declares_every_entry_point():
         assert f"public struct {struct}" in cs
 
 
+def test_static_scratch_limit_is_stated_once():
+    """ptb_trace_rays_static: the limit the header states is the one the Python mirror and the C# wrapper quote, and the
+    entry point refuses a larger batch before it touches the device (no GPU needed: the context argument is checked first)."""
+    src = open(os.path.join(ROOT, "include", "ptb200.h")).read()
+    m = re.search(r"#define\s+PTB_TRACE_RAYS_STATIC_MAX\s+(\d+)u", src)
+    assert m, "PTB_TRACE_RAYS_STATIC_MAX not defined in include/ptb200.h"
+    limit = int(m.group(1))
+    from pathtracing_b200 import NativeTracer
+    assert NativeTracer.TRACE_RAYS_STATIC_MAX == limit
+    assert limit * 32 <= 4 << 20, "the static staging array is meant to stay modest (32 B per ray)"
+    cs = open(os.path.join(ROOT, "pathtracing_b200", "cs", "NativeTracer.cs")).read()
+    assert f"{limit:,}" in cs
+    lib = _lib.load()
+    assert lib.ptb_trace_rays_static(None, 1, None, None, 0.0, 1.0, 0, None, None) != 0      # NULL context: an error, not a crash
+
+
 def test_only_c_abi_types_in_header():
     src = open(os.path.join(ROOT, "include", "ptb200.h")).read()
     assert 'extern "C"' in src
